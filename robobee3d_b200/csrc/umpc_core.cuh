@@ -1,0 +1,355 @@
+// robobee3d_b200/csrc/umpc_core.cuh
+//
+// UprightMPC2 controller update for ONE environment, written so that a CUDA
+// thread owns one QP (all indices compile-time, vectors in registers, the
+// per-QP factor in a caller-provided store -- shared memory in the kernels).
+//
+// What it computes (reference file:line, all under template/):
+//   template projection        uprightmpc2/uprightmpc2.c:214-241
+//   l,u,Ax data                uprightmpc2/uprightmpc2.c:126-180  (template_controllers.py:65-125)
+//   Px,q                       uprightmpc2/uprightmpc2.c:182-207  (template_controllers.py:127-143)
+//   constraint types / rho     uprightmpc2/auxil.c:103-146
+//   Ruiz equilibration x10     uprightmpc2/scaling.c:44-156
+//   ADMM iterations            uprightmpc2/osqp.c:288-641, auxil.c:164-228, proj.c:4-14
+//   residuals / status         uprightmpc2/auxil.c:243-361,567-633,684-790
+//   solution un-scaling        uprightmpc2/scaling.c:177-192
+//   uquad / accdes extraction  uprightmpc2/uprightmpc2.c:252-269
+//
+// Formulation.  OSQP iterates on the Ruiz-scaled problem (x_s = D^-1 x,
+// z_s = E z, y_s = c E^-1 y ...).  We carry the SAME iterates in un-scaled
+// ("hatted") coordinates  xh = D x_s, zh = E^-1 z_s, yh = E y_s, in which the
+// scaled ADMM step becomes an ADMM step on the UNSCALED matrix A0 with a
+// per-row penalty W = rho .* E^2, a per-variable regulariser sigma / D^2 and the
+// cost multiplied by c:
+//     K xt = sigma D^-2 xh - c q0 + A0'(W zh - yh),   K = c P0 + sigma D^-2 + A0' W A0
+//     zt = A0 xt ; xh+ = a xt + (1-a) xh ; zh+ = clip(a zt + (1-a) zh + yh/W, l0, u0)
+//     yh+ = yh + W (a zt + (1-a) zh - zh+)
+// which is algebraically identical to auxil.c:164-228 + qdldl_interface.c:343-369
+// (eliminate nu from the quasi-definite KKT system) and needs neither the
+// scaled copies of P and A nor the 84x84 factor.  The warm start is kept in
+// HBM in OSQP's own scaled coordinates and, like the reference (no
+// osqp_warm_start call in uprightmpc2.c), is NOT rescaled when D, E change.
+#pragma once
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define UMPC_HD __host__ __device__ __forceinline__
+#else
+#define UMPC_HD inline
+#endif
+
+#define UMPC_NX 45
+#define UMPC_NC 39
+#define UMPC_NEQ 36
+
+// OSQP status values (uprightmpc2/constants.h:17-31)
+#define UMPC_ST_SOLVED 1
+#define UMPC_ST_SOLVED_INACCURATE 2
+#define UMPC_ST_MAX_ITER (-2)
+#define UMPC_ST_NON_CVX (-7)
+#define UMPC_ST_UNSOLVED (-10)
+
+// Controller parameters (what umpcInit derives, uprightmpc2.c:19-63,116-117) plus the
+// OSQP settings baked into the generated workspace (uprightmpc2/workspace.c:561).
+struct UmpcParams {
+  float dt, g, Tmax;
+  float Qyr[6], Qyf[6], Qdyr[6], Qdyf[6], R[3];
+  float Ibi[3];
+  int max_iter;
+  float rho, sigma, alpha, eps_abs, eps_rel;
+  int scaling_iters;
+};
+
+// unscaled A0 values that change per update (Ax_data, uprightmpc2.c:160-179)
+struct UmpcAVals {
+  float dt, dtT0, ds[3], db[6];
+  float abs_dt, abs_dtT0, abs_ds0, abs_ds1, abs_ds2, abs_db0, abs_db1, abs_db2, abs_db3, abs_db4, abs_db5;
+};
+
+#include "umpc_gen.cuh"
+
+UMPC_HD float umpc_limit_scaling(float v) {
+  v = v < 1e-4f ? 1.0f : v;   // MIN_SCALING (constants.h:98)
+  return v > 1e4f ? 1e4f : v; // MAX_SCALING
+}
+
+// diagonal of P0 (updateObjective, uprightmpc2.c:182-207)
+UMPC_HD float umpc_px(const UmpcParams& par, int j) {
+  if (j < 12) return par.Qyr[j % 6];
+  if (j < 18) return par.Qyf[j % 6];
+  if (j < 30) return par.Qdyr[j % 6];
+  if (j < 36) return par.Qdyf[j % 6];
+  return par.R[(j - 36) % 3];
+}
+
+// QP data of one update in unscaled form: A0 values, bounds, references.
+struct UmpcQP {
+  UmpcAVals a;
+  float lo[UMPC_NC];  // l (== u on rows 0..35)
+  float hi_thr;       // u on rows 36..38
+  float yd[6], dyd[6];
+};
+
+// template projection (uprightmpc2.c:219-241) + umpcUpdateConstraint (uprightmpc2.c:126-180)
+UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const float p0[3], const float R0[9], const float dq0[6],
+                        const float pdes[3], const float dpdes[3], const float sdes[3], float T0) {
+  const float dt = par.dt;
+  float s0[3], ds0[3], y0[6], dy0[6], y1[6];
+  UmpcAVals& a = qp.a;
+  const float w0 = dq0[3], w1 = dq0[4];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    s0[i] = R0[6 + i];
+    // e3h*w = (-w1, w0, 0); ds0 = -R0 * (e3h w)
+    ds0[i] = -(R0[i] * (-w1) + R0[3 + i] * w0);
+    // Btau = (-R0 e3h Ibi)[:, :2]; e3h Ibi has (1,0)=Ibi0, (0,1)=-Ibi1
+    a.db[i] = dt * (-(R0[3 + i] * par.Ibi[0]));
+    a.db[3 + i] = dt * (R0[i] * par.Ibi[1]);
+    a.ds[i] = dt * s0[i];
+    y0[i] = p0[i]; y0[3 + i] = s0[i];
+    dy0[i] = dq0[i]; dy0[3 + i] = ds0[i];
+    qp.yd[i] = pdes[i]; qp.yd[3 + i] = sdes[i];
+    qp.dyd[i] = dpdes[i]; qp.dyd[3 + i] = 0.0f;
+  }
+  a.dt = dt; a.dtT0 = dt * T0;
+  a.abs_dt = fabsf(a.dt); a.abs_dtT0 = fabsf(a.dtT0);
+  a.abs_ds0 = fabsf(a.ds[0]); a.abs_ds1 = fabsf(a.ds[1]); a.abs_ds2 = fabsf(a.ds[2]);
+  a.abs_db0 = fabsf(a.db[0]); a.abs_db1 = fabsf(a.db[1]); a.abs_db2 = fabsf(a.db[2]);
+  a.abs_db3 = fabsf(a.db[3]); a.abs_db4 = fabsf(a.db[4]); a.abs_db5 = fabsf(a.db[5]);
+#pragma unroll
+  for (int i = 0; i < UMPC_NC; ++i) qp.lo[i] = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    y1[i] = y0[i] + dt * dy0[i];
+    qp.lo[i] = -y1[i];
+  }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const float c0 = (i == 2) ? -par.g : 0.0f;
+    const float A0y0 = i < 3 ? T0 * y0[i + 3] : 0.0f;
+    const float A0y1 = i < 3 ? T0 * y1[i + 3] : 0.0f;
+    qp.lo[18 + i] = -dy0[i] - dt * A0y0 - dt * c0;
+    qp.lo[24 + i] = -dt * A0y1 - dt * c0;
+    qp.lo[30 + i] = -dt * c0;
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) qp.lo[36 + k] = -T0;
+  qp.hi_thr = par.Tmax - T0;
+}
+
+// the reference's public QP vectors (UprightMPC_t.l/u/q/Px_data/Ax_data, uprightmpc2.h:36-40),
+// out = l[39] u[39] q[45] Px[45] Ax_data[48]  (vectors()/matrices(), py/uprightmpc2py.cpp:46-51)
+UMPC_HD void umpc_qpdata(const UmpcParams& par, const UmpcQP& qp, float* out) {
+  for (int i = 0; i < UMPC_NC; ++i) {
+    out[i] = qp.lo[i];
+    out[UMPC_NC + i] = i < UMPC_NEQ ? qp.lo[i] : qp.hi_thr;
+  }
+  float* q = out + 2 * UMPC_NC;
+  float* Px = q + UMPC_NX;
+  float* Ax = Px + UMPC_NX;
+  for (int j = 0; j < UMPC_NX; ++j) {
+    Px[j] = umpc_px(par, j);
+    q[j] = j < 36 ? -Px[j] * (j < 18 ? qp.yd[j % 6] : qp.dyd[j % 6]) : 0.0f;
+  }
+  int o = 0;
+  for (int i = 0; i < 3; ++i) Ax[o++] = qp.a.dtT0;
+  for (int i = 0; i < 18; ++i) Ax[o++] = qp.a.dt;
+  for (int k = 0; k < 3; ++k) for (int i = 0; i < 3; ++i) Ax[o++] = qp.a.ds[i];
+  for (int k = 0; k < 3; ++k) for (int i = 0; i < 6; ++i) Ax[o++] = qp.a.db[i];
+}
+
+struct UmpcInfo {
+  int iter, status;
+  float pri_res, dua_res;
+};
+
+// Per-QP scratch the iterations re-read every pass.  The kernels back it with
+// shared memory laid out [entry][thread]; the host check backs it with arrays.
+//   L(n) n<167, Di(k) k<45 : factor of K        W(i), Wi(i) i<39 : penalty and inverse
+//   Sg(j) j<45 : sigma / D_j^2                  Lo(i) i<39, Hi(t) t<3 : bounds l0 / thrust u0
+//
+// xs/zs/ys: OSQP's scaled iterates (in: warm start, out: for the next call).
+// Eold: E of the previous call for the 3 thrust rows (constraint-type test uses
+// the bounds scaled with the OLD E, osqp.c:784-832 + auxil.c:103-146).
+template <class ST>
+UMPC_HD void umpc_update(const UmpcParams& par, ST& st, float uquad[3], float accdes[6], const float p0[3],
+                         const float R0[9], const float dq0[6], const float pdes[3], const float dpdes[3],
+                         const float sdes[3], float actualT0, float& T0, float (&xs)[UMPC_NX],
+                         float (&zs)[UMPC_NC], float (&ys)[UMPC_NC], float (&Eold)[3], float (&solx)[UMPC_NX],
+                         float (&soly)[UMPC_NC], UmpcInfo& info) {
+  const float dt = par.dt;
+  if (actualT0 >= 0.0f) T0 = actualT0;
+  UmpcQP qp;
+  umpc_build(par, qp, p0, R0, dq0, pdes, dpdes, sdes, T0);
+  const UmpcAVals& a = qp.a;
+  const float lo_thr = qp.lo[36], hi_thr = qp.hi_thr;
+  float yd[6], dyd[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
+#pragma unroll
+  for (int i = 0; i < UMPC_NC; ++i) st.Lo(i) = qp.lo[i];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) st.Hi(k) = hi_thr;
+  // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
+  float rho_thr[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float ls_ = Eold[k] * lo_thr, us_ = Eold[k] * hi_thr;
+    rho_thr[k] = (us_ - ls_ < 1e-4f) ? 1e3f * par.rho : par.rho;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ
+  }
+  const float rho_eq = 1e3f * par.rho;
+
+  // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
+  float c = 1.0f;
+  {
+    float D[UMPC_NX], E[UMPC_NC];
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) D[j] = 1.0f;
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) E[i] = 1.0f;
+    for (int it = 0; it < par.scaling_iters; ++it) {
+      float cn[UMPC_NX], rn[UMPC_NC];
+      umpc_gen_norms(cn, rn, D, E, a);
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const float pc = c * umpc_px(par, j) * D[j] * D[j];
+        const float nj = fmaxf(pc, cn[j] * D[j]);
+        D[j] *= 1.0f / sqrtf(umpc_limit_scaling(nj));
+      }
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) E[i] *= 1.0f / sqrtf(umpc_limit_scaling(rn[i] * E[i]));
+      // cost normalisation (scaling.c:100-131)
+      float psum = 0.0f, nq = 0.0f;
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const float px = umpc_px(par, j);
+        psum += c * px * D[j] * D[j];
+        if (j < 36) {
+          const float ydj = j < 18 ? yd[j % 6] : dyd[j % 6];
+          nq = fmaxf(nq, fabsf(c * D[j] * px * ydj));
+        }
+      }
+      float ct = psum * (1.0f / UMPC_NX);
+      ct = fmaxf(ct, umpc_limit_scaling(nq));
+      ct = umpc_limit_scaling(ct);
+      c *= 1.0f / ct;
+    }
+    // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
+    float G[UMPC_NX], W[UMPC_NC];
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) {
+      const float sg = par.sigma / (D[j] * D[j]);
+      st.Sg(j) = sg;
+      G[j] = c * umpc_px(par, j) + sg;
+    }
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) {
+      const float rho_i = i < UMPC_NEQ ? rho_eq : rho_thr[i - UMPC_NEQ];
+      W[i] = rho_i * E[i] * E[i];
+      st.W(i) = W[i];
+      st.Wi(i) = 1.0f / W[i];
+    }
+    umpc_gen_factor(G, W, a, st);
+    // ---- warm start into hatted coordinates; remember D, E for the way back ------------
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) { xs[j] *= D[j]; st.Dsc(j) = D[j]; }
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) { zs[i] /= E[i]; ys[i] *= E[i]; st.Esc(i) = E[i]; }
+  }
+  // from here xs, zs, ys hold xh, zh, yh
+  // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
+  const float alpha = par.alpha, oma = 1.0f - par.alpha;
+  float cyd[6], cdyd[6];  // c * ydes, c * dydes  ->  c q0_j = -Px_j * (c yd)
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { cyd[i] = c * yd[i]; cdyd[i] = c * dyd[i]; }
+  for (int it = 0; it < par.max_iter; ++it) {
+    float r[UMPC_NX], zt[UMPC_NC];
+    {
+      float v[UMPC_NC];
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) v[i] = st.W(i) * zs[i] - ys[i];
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) {
+        float rj = st.Sg(j) * xs[j];
+        if (j < 36) rj += umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]);
+        r[j] = rj;
+      }
+      umpc_gen_ATv_add(r, v, a);
+    }
+    umpc_gen_solve(r, st);
+    umpc_gen_Ax(zt, r, a);
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) xs[j] = alpha * r[j] + oma * xs[j];
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) {
+      const float t = alpha * zt[i] + oma * zs[i];
+      const float lo = st.Lo(i);
+      const float hi = i < UMPC_NEQ ? lo : st.Hi(i - UMPC_NEQ);
+      const float zn = fminf(fmaxf(t + st.Wi(i) * ys[i], lo), hi);
+      ys[i] += st.W(i) * (t - zn);
+      zs[i] = zn;
+    }
+  }
+  // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
+  {
+    float Ax[UMPC_NC], Aty[UMPC_NX];
+    umpc_gen_Ax(Ax, xs, a);
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
+    umpc_gen_ATv_add(Aty, ys, a);
+    float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) {
+      pri = fmaxf(pri, fabsf(Ax[i] - zs[i]));
+      nz = fmaxf(nz, fabsf(zs[i]));
+      nAx = fmaxf(nAx, fabsf(Ax[i]));
+    }
+    float dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f;
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) {
+      const float px = c * umpc_px(par, j) * xs[j];
+      const float qj = j < 36 ? -umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]) : 0.0f;
+      dua = fmaxf(dua, fabsf(px + qj + Aty[j]));
+      nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
+    }
+    const float cinv = 1.0f / c;
+    dua *= cinv;
+    info.iter = par.max_iter; info.pri_res = pri; info.dua_res = dua;
+    const float nd = cinv * fmaxf(fmaxf(nq, nAty), nPx), np_ = fmaxf(nz, nAx);
+    int status = UMPC_ST_UNSOLVED;
+    if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;
+    else if (pri < par.eps_abs + par.eps_rel * np_ && dua < par.eps_abs + par.eps_rel * nd) status = UMPC_ST_SOLVED;
+    else if (pri < 10.0f * (par.eps_abs + par.eps_rel * np_) && dua < 10.0f * (par.eps_abs + par.eps_rel * nd))
+      status = UMPC_ST_SOLVED_INACCURATE;
+    else status = UMPC_ST_MAX_ITER;
+    info.status = status;
+    // ---- store_solution (auxil.c:527-562) and warm start back to scaled coordinates ------
+    if (status == UMPC_ST_NON_CVX) {
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) { solx[j] = nanf(""); xs[j] = 0.0f; }
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) { soly[i] = nanf(""); zs[i] = 0.0f; ys[i] = 0.0f; }
+    } else {
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) { solx[j] = xs[j]; xs[j] = xs[j] / st.Dsc(j); }
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) {
+        const float e = st.Esc(i);
+        soly[i] = ys[i] * cinv;
+        zs[i] *= e; ys[i] /= e;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) Eold[k] = st.Esc(UMPC_NEQ + k);
+  }
+  // ---- extraction (uprightmpc2.c:252-269) ---------------------------------------------------
+  T0 += solx[36];
+  uquad[0] = T0; uquad[1] = solx[37]; uquad[2] = solx[38];
+  {
+    const float t0 = R0[0] * solx[21] + R0[1] * solx[22] + R0[2] * solx[23];
+    const float t1 = R0[3] * solx[21] + R0[4] * solx[22] + R0[5] * solx[23];
+    const float dq1[6] = {solx[18], solx[19], solx[20], -t1, t0, 0.0f};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0[i]) / dt;
+  }
+}
