@@ -163,44 +163,61 @@ struct UmpcInfo {
   float pri_res, dua_res;
 };
 
-// Per-QP scratch the iterations re-read every pass.  The kernels back it with
+// Per-QP scratch the iterations re-read every pass (ST).  The kernels back it with
 // shared memory laid out [entry][thread]; the host check backs it with arrays.
-//   L(n) n<167, Di(k) k<45 : factor of K        W(i), Wi(i) i<39 : penalty and inverse
-//   Sg(j) j<45 : sigma / D_j^2                  Lo(i) i<39, Hi(t) t<3 : bounds l0 / thrust u0
+//   L(n) n<167, Di(k) k<45 : factor of K      aW(i) i<36 : alpha * W_i of the equality rows
+//   Sg(j) j<45 : sigma / D_j^2                Lo(i) i<36 : l0 (== u0) of the equality rows
+//   Vf(i) i<36 : first-iteration fix-up (see below)
+// Per-env persistent state (IO; global memory, SoA): OSQP's scaled iterates xs/zs/ys (the
+// warm start, never rescaled), the last D, E (E of the thrust rows decides their
+// constraint type on the next call: bounds are scaled with the OLD E before the
+// re-equilibration, osqp.c:784-832 + auxil.c:103-146), and the solution.
 //
-// xs/zs/ys: OSQP's scaled iterates (in: warm start, out: for the next call).
-// Eold: E of the previous call for the 3 thrust rows (constraint-type test uses
-// the bounds scaled with the OLD E, osqp.c:784-832 + auxil.c:103-146).
-template <class ST>
-UMPC_HD void umpc_update(const UmpcParams& par, ST& st, float uquad[3], float accdes[6], const float p0[3],
+// Equality rows (l == u).  After the first projection z_i == l_i exactly (proj.c:4-14), so
+// for those 36 rows only the combination the right-hand side needs is carried:
+//     v_i = W_i zh_i - yh_i ,   v_i+ = v_i - alpha W_i (zt_i - l_i)          (iterations >= 2)
+// and yh_i = W_i l_i - v_i is recovered at the end.  In the first iteration zh_i is the
+// stale warm start, which only changes the constant: v_i <- Vf_i before the same update,
+// Vf_i = (2 - alpha) W_i l_i - yh0_i - (1 - alpha) W_i zh0_i.
+UMPC_HD float umpc_lo_eq(const UmpcParams& par, int i, float stored) {
+  // rows 6..17 are 0 and rows 30..35 are -dt*c0 (uprightmpc2.c:139-152): no load needed
+  if (i >= 6 && i < 18) return 0.0f;
+  if (i >= 30) return i == 32 ? par.dt * par.g : 0.0f;
+  return stored;
+}
+
+template <class ST, class IO>
+UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], float accdes[6], const float p0[3],
                          const float R0[9], const float dq0[6], const float pdes[3], const float dpdes[3],
-                         const float sdes[3], float actualT0, float& T0, float (&xs)[UMPC_NX],
-                         float (&zs)[UMPC_NC], float (&ys)[UMPC_NC], float (&Eold)[3], float (&solx)[UMPC_NX],
-                         float (&soly)[UMPC_NC], UmpcInfo& info) {
+                         const float sdes[3], float actualT0, float& T0, UmpcInfo& info) {
   const float dt = par.dt;
   if (actualT0 >= 0.0f) T0 = actualT0;
-  UmpcQP qp;
-  umpc_build(par, qp, p0, R0, dq0, pdes, dpdes, sdes, T0);
-  const UmpcAVals& a = qp.a;
-  const float lo_thr = qp.lo[36], hi_thr = qp.hi_thr;
-  float yd[6], dyd[6];
+  UmpcAVals a;
+  float yd[6], dyd[6], lo_thr, hi_thr;
+  {
+    UmpcQP qp;
+    umpc_build(par, qp, p0, R0, dq0, pdes, dpdes, sdes, T0);
+    a = qp.a;
+    lo_thr = qp.lo[36]; hi_thr = qp.hi_thr;
 #pragma unroll
-  for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
+    for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
 #pragma unroll
-  for (int i = 0; i < UMPC_NC; ++i) st.Lo(i) = qp.lo[i];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) st.Hi(k) = hi_thr;
+    for (int i = 0; i < UMPC_NEQ; ++i) st.Lo(i) = qp.lo[i];
+  }
   // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
-  float rho_thr[3];
+  float W3[3], Wi3[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    const float ls_ = Eold[k] * lo_thr, us_ = Eold[k] * hi_thr;
-    rho_thr[k] = (us_ - ls_ < 1e-4f) ? 1e3f * par.rho : par.rho;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ
+    const float eo = io.ld_E(UMPC_NEQ + k);
+    const float ls_ = eo * lo_thr, us_ = eo * hi_thr;
+    W3[k] = (us_ - ls_ < 1e-4f) ? 1e3f * par.rho : par.rho;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ (constants.h:69-71)
   }
   const float rho_eq = 1e3f * par.rho;
+  const float alpha = par.alpha, oma = 1.0f - par.alpha;
 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
   float c = 1.0f;
+  float xs[UMPC_NX], v[UMPC_NEQ], z3[3], y3[3];
   {
     float D[UMPC_NX], E[UMPC_NC];
 #pragma unroll
@@ -235,120 +252,158 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, float uquad[3], float ac
       c *= 1.0f / ct;
     }
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
-    float G[UMPC_NX], W[UMPC_NC];
+    {
+      float G[UMPC_NX], W[UMPC_NC];
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) {
-      const float sg = par.sigma / (D[j] * D[j]);
-      st.Sg(j) = sg;
-      G[j] = c * umpc_px(par, j) + sg;
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const float sg = par.sigma / (D[j] * D[j]);
+        st.Sg(j) = sg;
+        G[j] = c * umpc_px(par, j) + sg;
+        io.st_D(j, D[j]);
+      }
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) {
+        const float rho_i = i < UMPC_NEQ ? rho_eq : W3[i - UMPC_NEQ];
+        W[i] = rho_i * E[i] * E[i];
+        io.st_E(i, E[i]);
+      }
+      umpc_gen_factor(G, W, a, st);
+      // ---- warm start -> hatted coordinates (x D, z / E, y E) ----------------------------
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) {
+        const float zh = io.ld_zs(i) / E[i], yh = io.ld_ys(i) * E[i];
+        const float lo = umpc_lo_eq(par, i, st.Lo(i));
+        v[i] = W[i] * zh - yh;
+        st.Vf(i) = (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh;
+        st.aW(i) = alpha * W[i];
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        z3[k] = io.ld_zs(UMPC_NEQ + k) / E[UMPC_NEQ + k];
+        y3[k] = io.ld_ys(UMPC_NEQ + k) * E[UMPC_NEQ + k];
+        W3[k] = W[UMPC_NEQ + k];
+        Wi3[k] = 1.0f / W3[k];
+      }
     }
 #pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) {
-      const float rho_i = i < UMPC_NEQ ? rho_eq : rho_thr[i - UMPC_NEQ];
-      W[i] = rho_i * E[i] * E[i];
-      st.W(i) = W[i];
-      st.Wi(i) = 1.0f / W[i];
-    }
-    umpc_gen_factor(G, W, a, st);
-    // ---- warm start into hatted coordinates; remember D, E for the way back ------------
-#pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) { xs[j] *= D[j]; st.Dsc(j) = D[j]; }
-#pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) { zs[i] /= E[i]; ys[i] *= E[i]; st.Esc(i) = E[i]; }
+    for (int j = 0; j < UMPC_NX; ++j) xs[j] = io.ld_xs(j) * D[j];
   }
-  // from here xs, zs, ys hold xh, zh, yh
   // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
-  const float alpha = par.alpha, oma = 1.0f - par.alpha;
-  float cyd[6], cdyd[6];  // c * ydes, c * dydes  ->  c q0_j = -Px_j * (c yd)
+  float cyd[6], cdyd[6];  // c * ydes, c * dydes  ->  -c q0_j = Px_j * (c yd)
 #pragma unroll
   for (int i = 0; i < 6; ++i) { cyd[i] = c * yd[i]; cdyd[i] = c * dyd[i]; }
-  for (int it = 0; it < par.max_iter; ++it) {
-    float r[UMPC_NX], zt[UMPC_NC];
+  const int niter = par.max_iter < 1 ? 1 : par.max_iter;
+  for (int it = 0; it < niter; ++it) {
+    float r[UMPC_NX];
     {
-      float v[UMPC_NC];
+      float vv[UMPC_NC];
 #pragma unroll
-      for (int i = 0; i < UMPC_NC; ++i) v[i] = st.W(i) * zs[i] - ys[i];
+      for (int i = 0; i < UMPC_NEQ; ++i) vv[i] = v[i];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) vv[UMPC_NEQ + k] = W3[k] * z3[k] - y3[k];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
         float rj = st.Sg(j) * xs[j];
         if (j < 36) rj += umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]);
         r[j] = rj;
       }
-      umpc_gen_ATv_add(r, v, a);
+      umpc_gen_ATv_add(r, vv, a);
+    }
+    if (it == 0) {
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) v[i] = st.Vf(i);
     }
     umpc_gen_solve(r, st);
-    umpc_gen_Ax(zt, r, a);
+    {
+      float zt[UMPC_NC];
+      umpc_gen_Ax(zt, r, a);
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) xs[j] = alpha * r[j] + oma * xs[j];
+      for (int i = 0; i < UMPC_NEQ; ++i) v[i] -= st.aW(i) * (zt[i] - umpc_lo_eq(par, i, st.Lo(i)));
 #pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) {
-      const float t = alpha * zt[i] + oma * zs[i];
-      const float lo = st.Lo(i);
-      const float hi = i < UMPC_NEQ ? lo : st.Hi(i - UMPC_NEQ);
-      const float zn = fminf(fmaxf(t + st.Wi(i) * ys[i], lo), hi);
-      ys[i] += st.W(i) * (t - zn);
-      zs[i] = zn;
-    }
-  }
-  // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
-  {
-    float Ax[UMPC_NC], Aty[UMPC_NX];
-    umpc_gen_Ax(Ax, xs, a);
-#pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
-    umpc_gen_ATv_add(Aty, ys, a);
-    float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
-#pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) {
-      pri = fmaxf(pri, fabsf(Ax[i] - zs[i]));
-      nz = fmaxf(nz, fabsf(zs[i]));
-      nAx = fmaxf(nAx, fabsf(Ax[i]));
-    }
-    float dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f;
-#pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) {
-      const float px = c * umpc_px(par, j) * xs[j];
-      const float qj = j < 36 ? -umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]) : 0.0f;
-      dua = fmaxf(dua, fabsf(px + qj + Aty[j]));
-      nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
-    }
-    const float cinv = 1.0f / c;
-    dua *= cinv;
-    info.iter = par.max_iter; info.pri_res = pri; info.dua_res = dua;
-    const float nd = cinv * fmaxf(fmaxf(nq, nAty), nPx), np_ = fmaxf(nz, nAx);
-    int status = UMPC_ST_UNSOLVED;
-    if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;
-    else if (pri < par.eps_abs + par.eps_rel * np_ && dua < par.eps_abs + par.eps_rel * nd) status = UMPC_ST_SOLVED;
-    else if (pri < 10.0f * (par.eps_abs + par.eps_rel * np_) && dua < 10.0f * (par.eps_abs + par.eps_rel * nd))
-      status = UMPC_ST_SOLVED_INACCURATE;
-    else status = UMPC_ST_MAX_ITER;
-    info.status = status;
-    // ---- store_solution (auxil.c:527-562) and warm start back to scaled coordinates ------
-    if (status == UMPC_ST_NON_CVX) {
-#pragma unroll
-      for (int j = 0; j < UMPC_NX; ++j) { solx[j] = nanf(""); xs[j] = 0.0f; }
-#pragma unroll
-      for (int i = 0; i < UMPC_NC; ++i) { soly[i] = nanf(""); zs[i] = 0.0f; ys[i] = 0.0f; }
-    } else {
-#pragma unroll
-      for (int j = 0; j < UMPC_NX; ++j) { solx[j] = xs[j]; xs[j] = xs[j] / st.Dsc(j); }
-#pragma unroll
-      for (int i = 0; i < UMPC_NC; ++i) {
-        const float e = st.Esc(i);
-        soly[i] = ys[i] * cinv;
-        zs[i] *= e; ys[i] /= e;
+      for (int k = 0; k < 3; ++k) {
+        const float t = alpha * zt[UMPC_NEQ + k] + oma * z3[k];
+        const float zn = fminf(fmaxf(t + Wi3[k] * y3[k], lo_thr), hi_thr);
+        y3[k] += W3[k] * (t - zn);
+        z3[k] = zn;
       }
     }
 #pragma unroll
-    for (int k = 0; k < 3; ++k) Eold[k] = st.Esc(UMPC_NEQ + k);
+    for (int j = 0; j < UMPC_NX; ++j) xs[j] = alpha * r[j] + oma * xs[j];
+  }
+  // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
+  float solx_u[3], solx_dy1[6];
+  {
+    float zs[UMPC_NC], ys[UMPC_NC];
+    const float ialpha = 1.0f / alpha;
+#pragma unroll
+    for (int i = 0; i < UMPC_NEQ; ++i) {
+      zs[i] = umpc_lo_eq(par, i, st.Lo(i));
+      ys[i] = st.aW(i) * (zs[i] * ialpha) - v[i];
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { zs[UMPC_NEQ + k] = z3[k]; ys[UMPC_NEQ + k] = y3[k]; }
+    float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
+    {
+      float Ax[UMPC_NC];
+      umpc_gen_Ax(Ax, xs, a);
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) {
+        pri = fmaxf(pri, fabsf(Ax[i] - zs[i]));
+        nz = fmaxf(nz, fabsf(zs[i]));
+        nAx = fmaxf(nAx, fabsf(Ax[i]));
+      }
+    }
+    float dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f;
+    {
+      float Aty[UMPC_NX];
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
+      umpc_gen_ATv_add(Aty, ys, a);
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const float px = c * umpc_px(par, j) * xs[j];
+        const float qj = j < 36 ? -umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]) : 0.0f;
+        dua = fmaxf(dua, fabsf(px + qj + Aty[j]));
+        nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
+      }
+    }
+    const float cinv = 1.0f / c;
+    dua *= cinv;
+    info.iter = niter; info.pri_res = pri; info.dua_res = dua;
+    const float ep = par.eps_abs + par.eps_rel * fmaxf(nz, nAx);
+    const float ed = par.eps_abs + par.eps_rel * cinv * fmaxf(fmaxf(nq, nAty), nPx);
+    int status;
+    if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;  // OSQP_INFTY (auxil.c:706-716)
+    else if (pri < ep && dua < ed) status = UMPC_ST_SOLVED;
+    else if (pri < 10.0f * ep && dua < 10.0f * ed) status = UMPC_ST_SOLVED_INACCURATE;  // osqp.c:564-568
+    else status = UMPC_ST_MAX_ITER;
+    info.status = status;
+    // ---- store_solution (auxil.c:527-562); warm start back to OSQP's scaled coordinates ---
+    const bool bad = status == UMPC_ST_NON_CVX;
+    const float nanv = nanf("");
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) {
+      const float sx = bad ? nanv : xs[j];
+      io.st_solx(j, sx);
+      io.st_xs(j, bad ? 0.0f : xs[j] / io.ld_D(j));
+      if (j >= 18 && j < 24) solx_dy1[j - 18] = sx;
+      if (j >= 36 && j < 39) solx_u[j - 36] = sx;
+    }
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) {
+      const float e = io.ld_E(i);
+      io.st_soly(i, bad ? nanv : ys[i] * cinv);
+      io.st_zs(i, bad ? 0.0f : zs[i] * e);
+      io.st_ys(i, bad ? 0.0f : ys[i] / e);
+    }
   }
   // ---- extraction (uprightmpc2.c:252-269) ---------------------------------------------------
-  T0 += solx[36];
-  uquad[0] = T0; uquad[1] = solx[37]; uquad[2] = solx[38];
+  T0 += solx_u[0];
+  uquad[0] = T0; uquad[1] = solx_u[1]; uquad[2] = solx_u[2];
   {
-    const float t0 = R0[0] * solx[21] + R0[1] * solx[22] + R0[2] * solx[23];
-    const float t1 = R0[3] * solx[21] + R0[4] * solx[22] + R0[5] * solx[23];
-    const float dq1[6] = {solx[18], solx[19], solx[20], -t1, t0, 0.0f};
+    const float t0 = R0[0] * solx_dy1[3] + R0[1] * solx_dy1[4] + R0[2] * solx_dy1[5];
+    const float t1 = R0[3] * solx_dy1[3] + R0[4] * solx_dy1[4] + R0[5] * solx_dy1[5];
+    const float dq1[6] = {solx_dy1[0], solx_dy1[1], solx_dy1[2], -t1, t0, 0.0f};
 #pragma unroll
     for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0[i]) / dt;
   }

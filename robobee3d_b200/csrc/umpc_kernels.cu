@@ -1,0 +1,1043 @@
+// robobee3d_b200/csrc/umpc_kernels.cu -- CUDA kernels (sm_100a) + C-ABI of libumpc_b200.so.
+//
+// Mapping: ONE THREAD PER ENVIRONMENT.  Every QP has the same sparsity, so the whole
+// update is straight-line code with compile-time indices (umpc_gen.cuh); the ADMM
+// vectors live in registers, the per-QP factor of K (167 + 45 values), alpha*W, sigma/D^2
+// and the bounds live in shared memory laid out [entry][thread] (bank = thread, conflict
+// free), and the warm start / plant state live in HBM as struct-of-arrays [k][B] so that
+// a warp's loads of one component are one 128-byte line.  There is no inter-thread
+// communication at all; the kernels are bound by the FP32 pipe and shared-memory
+// bandwidth, not by HBM (DESIGN.md has the byte/flop accounting).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <map>
+#include <mutex>
+
+#include "umpc_core.cuh"
+#include "sim_core.cuh"
+#include "wl_core.cuh"
+#include "../../include/umpc_b200.h"
+
+// ---- shared-memory store: [entry][thread] ---------------------------------------------------
+#define SM_OFF_L 0
+#define SM_OFF_DI (SM_OFF_L + UMPC_GEN_NNZL)
+#define SM_OFF_AW (SM_OFF_DI + UMPC_NX)
+#define SM_OFF_SG (SM_OFF_AW + UMPC_NEQ)
+#define SM_OFF_LO (SM_OFF_SG + UMPC_NX)
+#define SM_FLOATS_PER_THREAD (SM_OFF_LO + 18)
+
+struct SmemStore {
+  float* base;  // &smem[threadIdx.x]
+  int nt;       // blockDim.x
+  float* vf;    // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
+  int B;
+  __device__ __forceinline__ float& L(int n) { return base[(SM_OFF_L + n) * nt]; }
+  __device__ __forceinline__ float L(int n) const { return base[(SM_OFF_L + n) * nt]; }
+  __device__ __forceinline__ float& Di(int k) { return base[(SM_OFF_DI + k) * nt]; }
+  __device__ __forceinline__ float Di(int k) const { return base[(SM_OFF_DI + k) * nt]; }
+  __device__ __forceinline__ float& aW(int i) { return base[(SM_OFF_AW + i) * nt]; }
+  __device__ __forceinline__ float& Sg(int j) { return base[(SM_OFF_SG + j) * nt]; }
+  // only rows 0..5 and 18..29 have run-time bounds (umpc_lo_eq); the others get a dummy slot
+  __device__ __forceinline__ float& Lo(int i) {
+    return (i < 6) ? base[(SM_OFF_LO + i) * nt] : (i >= 18 && i < 30) ? base[(SM_OFF_LO + i - 12) * nt] : dummy;
+  }
+  __device__ __forceinline__ float& Vf(int i) { return vf[(size_t)i * B]; }
+  float dummy;
+};
+
+// ---- global SoA state -------------------------------------------------------------------------
+struct DevState {
+  int B;
+  // plant
+  float *p, *R, *dq, *uq, *acc;
+  // controller
+  float *T0, *xs, *zs, *ys, *D, *E, *solx, *soly, *info, *qpdata;
+  // tasks / loop
+  int* task;
+  float *tp, *pinit, *actualT0, *metrics;
+  // WL stage
+  float *wl_u0, *wlqp;  // wlqp: 25 floats per env (WlqpState)
+};
+
+struct GlobIO {
+  const DevState& s;
+  int e;
+  __device__ __forceinline__ GlobIO(const DevState& s_, int e_) : s(s_), e(e_) {}
+  __device__ __forceinline__ float ld_xs(int j) const { return s.xs[(size_t)j * s.B + e]; }
+  __device__ __forceinline__ float ld_zs(int i) const { return s.zs[(size_t)i * s.B + e]; }
+  __device__ __forceinline__ float ld_ys(int i) const { return s.ys[(size_t)i * s.B + e]; }
+  __device__ __forceinline__ float ld_D(int j) const { return s.D[(size_t)j * s.B + e]; }
+  __device__ __forceinline__ float ld_E(int i) const { return s.E[(size_t)i * s.B + e]; }
+  __device__ __forceinline__ void st_xs(int j, float v) { s.xs[(size_t)j * s.B + e] = v; }
+  __device__ __forceinline__ void st_zs(int i, float v) { s.zs[(size_t)i * s.B + e] = v; }
+  __device__ __forceinline__ void st_ys(int i, float v) { s.ys[(size_t)i * s.B + e] = v; }
+  __device__ __forceinline__ void st_D(int j, float v) { s.D[(size_t)j * s.B + e] = v; }
+  __device__ __forceinline__ void st_E(int i, float v) { s.E[(size_t)i * s.B + e] = v; }
+  __device__ __forceinline__ void st_solx(int j, float v) { s.solx[(size_t)j * s.B + e] = v; }
+  __device__ __forceinline__ void st_soly(int i, float v) { s.soly[(size_t)i * s.B + e] = v; }
+};
+
+struct KernelParams {
+  UmpcParams mpc;
+  SimParams sim;
+};
+
+extern __shared__ float g_smem[];
+
+__device__ __forceinline__ void store_info(const DevState& s, int e, const UmpcInfo& info) {
+  s.info[(size_t)0 * s.B + e] = (float)info.iter;
+  s.info[(size_t)1 * s.B + e] = (float)info.status;
+  s.info[(size_t)2 * s.B + e] = info.pri_res;
+  s.info[(size_t)3 * s.B + e] = info.dua_res;
+}
+
+// ---- kernel 1: one umpcUpdate per environment, inputs in [B][k] (the C-ABI's layout) ---------
+__global__ void __launch_bounds__(160, 1)
+umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
+                   float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
+                   const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
+                   const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= s.B) return;
+  float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    p[i] = p0[(size_t)e * 3 + i]; pd[i] = pdes[(size_t)e * 3 + i];
+    dpd[i] = dpdes[(size_t)e * 3 + i]; sd[i] = sdes[(size_t)e * 3 + i];
+  }
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] = R0[(size_t)e * 9 + i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) dq[i] = dq0[(size_t)e * 6 + i];
+  const float aT0 = actualT0 ? actualT0[e] : -1.0f;
+  float T0 = s.T0[e];
+  if (want_qpdata) {
+    UmpcQP qp;
+    umpc_build(kp.mpc, qp, p, R, dq, pd, dpd, sd, aT0 >= 0.0f ? aT0 : T0);
+    float out[216];
+    umpc_qpdata(kp.mpc, qp, out);
+    for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
+  }
+  SmemStore st;
+  st.base = g_smem + threadIdx.x; st.nt = blockDim.x; st.vf = s.soly + e; st.B = s.B;
+  GlobIO io(s, e);
+  float uq[3], acc[6];
+  UmpcInfo info;
+  umpc_update(kp.mpc, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+  s.T0[e] = T0;
+  store_info(s, e, info);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; s.uq[(size_t)i * s.B + e] = uq[i]; }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; s.acc[(size_t)i * s.B + e] = acc[i]; }
+}
+
+// ---- kernel 2: fused closed loop (uprightmpc2.py:87-159) -------------------------------------
+// Per plant step: task -> [umpcUpdate when the host-computed schedule fires] -> [WL stage] ->
+// torque clip -> rigid-body step -> metric sums.  Plant state stays in registers for the
+// whole launch; the warm start is re-read from HBM at each solve (1 KB per ~5e4 flop).
+struct LogBuf {
+  int env, cap;
+  float *y, *u;  // [cap][12], [cap][3]
+};
+
+__device__ __forceinline__ void load_wlqp(const DevState& s, int e, WlqpState& w) {
+  const float* b = s.wlqp + e;
+  const size_t B = s.B;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    w.xs[i] = b[(0 + i) * B]; w.zs[i] = b[(4 + i) * B]; w.ys[i] = b[(8 + i) * B];
+    w.D[i] = b[(12 + i) * B]; w.E[i] = b[(16 + i) * B]; w.q0[i] = b[(21 + i) * B];
+  }
+  w.c = b[20 * B];
+}
+__device__ __forceinline__ void store_wlqp(const DevState& s, int e, const WlqpState& w) {
+  float* b = s.wlqp + e;
+  const size_t B = s.B;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    b[(0 + i) * B] = w.xs[i]; b[(4 + i) * B] = w.zs[i]; b[(8 + i) * B] = w.ys[i];
+    b[(12 + i) * B] = w.D[i]; b[(16 + i) * B] = w.E[i]; b[(21 + i) * B] = w.q0[i];
+  }
+  b[20 * B] = w.c;
+}
+
+// WL stage after an MPC update (accController, robobee_test_controllers.py:165-171)
+__device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp, const DevState& s, int e, const float R[9],
+                                      const float acc[6]) {
+  float h0[6], pdd[6], u0[4], w0[6];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    h0[i] = R[3 * i + 2] * sim.mb * sim.g; h0[3 + i] = 0.0f;
+    pdd[i] = sim.mb * acc[i]; pdd[3 + i] = sim.Ib[i] * acc[3 + i];
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) u0[i] = s.wl_u0[(size_t)i * s.B + e];
+  if (sim.wl_mode == 1) {
+    wl_con_update(wlp, u0, w0, h0, pdd);
+  } else {
+    WlqpState w;
+    load_wlqp(s, e, w);
+    wlqp_update(wlp, w, u0, w0, h0, pdd, nullptr, nullptr);
+    store_wlqp(s, e, w);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s.wl_u0[(size_t)i * s.B + e] = u0[i];
+  s.actualT0[e] = w0[2] / sim.mb;
+}
+
+__global__ void __launch_bounds__(160, 1)
+umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
+                    const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
+                    const float* __restrict__ tvals, LogBuf lg) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= s.B) return;
+  const size_t B = s.B;
+  float p[3], R[9], dq[6], uq[3], pinit[3], tp[4];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { p[i] = s.p[i * B + e]; uq[i] = s.uq[i * B + e]; pinit[i] = s.pinit[i * B + e]; }
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] = s.R[i * B + e];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) dq[i] = s.dq[i * B + e];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) tp[i] = s.tp[i * B + e];
+  const int task = s.task[e];
+  float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
+  float pert_done = s.metrics[4 * B + e];
+  SmemStore st;
+  st.base = g_smem + threadIdx.x; st.nt = blockDim.x; st.vf = s.soly + e; st.B = s.B;
+  GlobIO io(s, e);
+  for (int k = 0; k < nsteps; ++k) {
+    const float t = tvals[k];
+    float pdes[3], dpdes[3], sdes[3];
+    sim_task(task, t, pinit, tp, pdes, dpdes, sdes);
+    if (task == SIM_TASK_HELIX && kp.sim.tpert >= 0.0f && t > kp.sim.tpert && pert_done == 0.0f) {
+      dq[1] += 2.0f; pert_done = 1.0f;
+    }
+    if (fire[k]) {
+      float acc[6], T0 = s.T0[e];
+      const float aT0 = kp.sim.wl_mode ? s.actualT0[e] : -1.0f;
+      UmpcInfo info;
+      umpc_update(kp.mpc, st, io, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0, T0, info);
+      s.T0[e] = T0;
+      store_info(s, e, info);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) s.acc[i * B + e] = acc[i];
+      if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, s, e, R, acc);
+      nsolve += 1.0f;
+    }
+    uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
+    uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
+    sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
+    err += p[0] * p[0] + p[1] * p[1] + p[2] * p[2];
+    eff += uq[1] * uq[1] + uq[2] * uq[2];
+    nstep += 1.0f;
+    if (e == lg.env && step0 + k < lg.cap) {
+      float* y = lg.y + (size_t)(step0 + k) * 12;
+      float* u = lg.u + (size_t)(step0 + k) * 3;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { y[i] = p[i]; y[3 + i] = R[6 + i]; u[i] = uq[i]; }
+#pragma unroll
+      for (int i = 0; i < 6; ++i) y[6 + i] = dq[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { s.p[i * B + e] = p[i]; s.uq[i * B + e] = uq[i]; }
+#pragma unroll
+  for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
+  s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
+  s.metrics[4 * B + e] = pert_done;
+}
+
+// ---- kernel 3: WL stage alone (drop-in wlConUpdate / wlControllerUpdate, batch of B) ---------
+__global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __grid_constant__ DevState s, int mode,
+                                 float* __restrict__ u1, float* __restrict__ w0o, const float* __restrict__ h0,
+                                 const float* __restrict__ pdotdes, float* __restrict__ info2) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= s.B) return;
+  float h[6], pd[6], u0[4], w0[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { h[i] = h0[(size_t)e * 6 + i]; pd[i] = pdotdes[(size_t)e * 6 + i]; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) u0[i] = s.wl_u0[(size_t)i * s.B + e];
+  int iter = 0, status = 0;
+  if (mode == 1) {
+    wl_con_update(wlp, u0, w0, h, pd);
+  } else {
+    WlqpState w;
+    load_wlqp(s, e, w);
+    wlqp_update(wlp, w, u0, w0, h, pd, &iter, &status);
+    store_wlqp(s, e, w);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { s.wl_u0[(size_t)i * s.B + e] = u0[i]; u1[(size_t)e * 4 + i] = u0[i]; }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) w0o[(size_t)e * 6 + i] = w0[i];
+  if (info2) { info2[(size_t)e * 2] = (float)iter; info2[(size_t)e * 2 + 1] = (float)status; }
+}
+
+// ---- kernel 4: metric reduction (what ranks all-reduce at the end of a run) -------------------
+__global__ void reduce_metrics_kernel(const __grid_constant__ DevState s, double* __restrict__ out8) {
+  double a[6] = {0, 0, 0, 0, 0, 0};
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < s.B; e += gridDim.x * blockDim.x) {
+    const size_t B = s.B;
+    const float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e];
+    const float ns = s.metrics[3 * B + e];
+    bool bad = !(isfinite(err) && isfinite(eff));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) bad = bad || !isfinite(s.p[i * B + e]);
+    if (!bad) { a[0] += err; a[1] += eff; a[5] = fmax(a[5], ns > 0 ? (double)err / ns : 0.0); }
+    a[2] += s.metrics[2 * B + e]; a[3] += ns; a[4] += bad ? 1.0 : 0.0;
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+    for (int o = 16; o > 0; o >>= 1) {
+      const double v = __shfl_xor_sync(0xffffffffu, a[k], o);
+      a[k] = (k == 5) ? fmax(a[k], v) : a[k] + v;
+    }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) atomicAdd(&out8[k], a[k]);
+    // max via CAS on the bit pattern (values are non-negative)
+    unsigned long long* addr = (unsigned long long*)&out8[5];
+    unsigned long long old = *addr, assumed;
+    do {
+      assumed = old;
+      if (__longlong_as_double((long long)assumed) >= a[5]) break;
+      old = atomicCAS(addr, assumed, (unsigned long long)__double_as_longlong(a[5]));
+    } while (assumed != old);
+  }
+}
+
+// ---- kernel 5: FP32 pipe peak (independent FFMA chains in registers) --------------------------
+__global__ void fp32_peak_kernel(float* out, int iters) {
+  float a[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = 1.0f + 1e-3f * (threadIdx.x + i);
+  const float m = 0.999f, c = 1e-3f;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) a[i] = fmaf(a[i], m, c);
+  }
+  float sacc = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) sacc += a[i];
+  if (sacc == 12345.678f) out[0] = sacc;
+}
+
+// ================================ host side: C-ABI ============================================
+static thread_local std::string g_err;
+static int set_err(const char* what, cudaError_t e) {
+  char buf[512];
+  snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
+  g_err = buf;
+  return UMPC_ERR_CUDA;
+}
+#define CK(call)                                              \
+  do {                                                        \
+    cudaError_t e_ = (call);                                  \
+    if (e_ != cudaSuccess) return set_err(#call, e_);         \
+  } while (0)
+
+extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
+
+struct UmpcBatch {
+  int B = 0, device = 0, tpb = 128;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+  UmpcBatchParams bp;
+  KernelParams kp;
+  WlParams wlp;
+  DevState s;
+  float* slab = nullptr;
+  size_t slab_floats = 0;
+  // staging ([B][k] layout of the C-ABI)
+  float *d_in = nullptr, *d_out = nullptr;  // in: 28 floats/env, out: 9 floats/env
+  // rollout schedule (host-evaluated in double like numpy, uprightmpc2.py:118,136,145)
+  long long step = 0;
+  double thl = 0.0;
+  uint8_t* d_fire = nullptr;
+  float* d_t = nullptr;
+  int sched_cap = 0;
+  double* d_sums = nullptr;
+  LogBuf lg{-1, 0, nullptr, nullptr};
+  bool have_qpdata = false;
+};
+
+extern "C" void umpcBatchDefaults(UmpcBatchParams* p) {
+  memset(p, 0, sizeof(*p));
+  // createMPC defaults (template_controllers.py:260-280)
+  p->dt = 5.0f; p->g = 9.81e-3f; p->TtoWmax = 2.0f; p->ws = 1e1f; p->wds = 1e3f; p->wpr = 1.0f; p->wpf = 5.0f;
+  p->wvr = 1e3f; p->wvf = 2e3f; p->wthrust = 1e-1f; p->wmom = 1e-2f;
+  p->Ib[0] = 3333.0f; p->Ib[1] = 3333.0f; p->Ib[2] = 1000.0f; p->maxIter = 50;
+  // controlTest defaults (uprightmpc2.py:87)
+  p->dtsim = 0.2; p->hlInterval = -1.0; p->taulim = 100.0f; p->tpert = -1.0f; p->mb = 100.0f;
+  p->wlMode = 0;
+  // WaypointHover WLCon limits (robobee_test_controllers.py:76); popts must be supplied by the caller
+  const float u0[4] = {140.0f, 0.0f, 0.0f, 0.0f}, umin[4] = {90.0f, -0.5f, -0.2f, -0.1f};
+  const float umax[4] = {240.0f, 0.5f, 0.2f, 0.1f}, dumax[4] = {5e3f, 10.0f, 10.0f, 10.0f};
+  const float Qw[6] = {1.0f, 1.0f, 1.0f, 0.1f, 0.1f, 0.1f};
+  memcpy(p->wl_u0, u0, sizeof(u0)); memcpy(p->wl_umin, umin, sizeof(umin)); memcpy(p->wl_umax, umax, sizeof(umax));
+  memcpy(p->wl_dumax, dumax, sizeof(dumax)); memcpy(p->wl_Qw, Qw, sizeof(Qw));
+  p->wl_controlRate = 1000.0f;
+  p->wlqpCheckTermination = 25;
+}
+
+static void fill_kernel_params(UmpcBatch* b) {
+  const UmpcBatchParams& p = b->bp;
+  UmpcParams& m = b->kp.mpc;
+  memset(&b->kp, 0, sizeof(b->kp));
+  m.dt = p.dt; m.g = p.g; m.Tmax = p.TtoWmax * p.g;
+  for (int i = 0; i < 3; ++i) {
+    m.Qyr[i] = p.wpr; m.Qyf[i] = p.wpf; m.Qyr[3 + i] = m.Qyf[3 + i] = p.ws;
+    m.Qdyr[i] = p.wvr; m.Qdyf[i] = p.wvf; m.Qdyr[3 + i] = m.Qdyf[3 + i] = p.wds;
+    m.Ibi[i] = 1.0f / p.Ib[i];
+  }
+  m.R[0] = p.wthrust; m.R[1] = m.R[2] = p.wmom;
+  // generated settings (uprightmpc2/workspace.c:561) + uprightmpc2.c:116-117
+  m.max_iter = p.maxIter; m.rho = 0.1f; m.sigma = 1e-6f; m.alpha = 1.6f; m.eps_abs = 1e-4f; m.eps_rel = 1e-4f;
+  m.scaling_iters = 10;
+  SimParams& sm = b->kp.sim;
+  sm.dtsim = (float)p.dtsim; sm.hl_interval = (float)p.hlInterval; sm.taulim = p.taulim; sm.tpert = p.tpert;
+  for (int i = 0; i < 3; ++i) sm.Ib[i] = p.Ib[i];
+  sm.g = p.g; sm.mb = p.mb; sm.wl_mode = p.wlMode;
+  WlParams& w = b->wlp;
+  memset(&w, 0, sizeof(w));
+  memcpy(w.popts, p.wl_popts, sizeof(w.popts));
+  for (int i = 0; i < 4; ++i) {
+    w.umin[i] = p.wl_umin[i]; w.umax[i] = p.wl_umax[i];
+    w.dumax[i] = p.wl_controlRate > 0 ? p.wl_dumax[i] / p.wl_controlRate : 0.0f;
+  }
+  for (int i = 0; i < 6; ++i) w.Qw[i] = p.wl_Qw[i];
+  // wlqp/workspace.c:84 + osqp_set_default_settings (eps 1e-3, constants.h:62-63) + max_iter 40 (wlqp.c:43-46)
+  w.rho = 0.1f; w.sigma = 1e-6f; w.alpha = 1.6f; w.eps_abs = 1e-3f; w.eps_rel = 1e-3f;
+  w.max_iter = 40; w.check_termination = p.wlqpCheckTermination; w.scaling_iters = 10;
+}
+
+static size_t smem_bytes(int tpb) { return (size_t)SM_FLOATS_PER_THREAD * tpb * sizeof(float); }
+
+extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
+  if (!b || tpb < 32 || tpb > 160 || (tpb % 32)) { g_err = "threads_per_block must be 32..160, multiple of 32"; return UMPC_ERR_ARG; }
+  b->tpb = tpb;
+  return UMPC_OK;
+}
+
+static int reset_state(UmpcBatch* b) {
+  CK(cudaMemsetAsync(b->slab, 0, b->slab_floats * sizeof(float), b->stream));
+  // D = E = 1 ; WL u0 ; wlqp D = E = c = 1 ; actualT0 = -1
+  std::vector<float> ones((size_t)b->B * 45, 1.0f);
+  CK(cudaMemcpyAsync(b->s.D, ones.data(), (size_t)45 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->s.E, ones.data(), (size_t)39 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->s.wlqp + (size_t)12 * b->B, ones.data(), (size_t)9 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  std::vector<float> tmp((size_t)b->B * 4);
+  for (int i = 0; i < 4; ++i) for (int e = 0; e < b->B; ++e) tmp[(size_t)i * b->B + e] = b->bp.wl_u0[i];
+  CK(cudaMemcpyAsync(b->s.wl_u0, tmp.data(), (size_t)4 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  for (int e = 0; e < b->B; ++e) tmp[e] = -1.0f;
+  CK(cudaMemcpyAsync(b->s.actualT0, tmp.data(), (size_t)b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  b->step = 0; b->thl = 0.0;
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchReset(UmpcBatch* b) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  return reset_state(b);
+}
+
+extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const UmpcBatchParams* par) {
+  if (!out || nenv <= 0 || !par) { g_err = "umpcBatchCreate: bad argument"; return UMPC_ERR_ARG; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_err = std::string("umpcBatchCreate: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path";
+    return UMPC_ERR_CUDA;
+  }
+  CK(cudaSetDevice(device));
+  UmpcBatch* b = new UmpcBatch();
+  b->B = nenv; b->device = device; b->bp = *par;
+  fill_kernel_params(b);
+  CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&b->ev0));
+  CK(cudaEventCreate(&b->ev1));
+  // one slab, SoA rows of B floats
+  const int rows = 3 + 9 + 6 + 3 + 6 /*plant*/ + 1 + 45 + 39 + 39 + 45 + 39 + 45 + 39 + 4 /*ctrl*/ + 1 /*task*/ + 4 + 3 + 1 + 5 +
+                   4 + 25;
+  b->slab_floats = (size_t)rows * nenv;
+  CK(cudaMalloc(&b->slab, b->slab_floats * sizeof(float)));
+  float* q = b->slab;
+  auto take = [&](int r) { float* t = q; q += (size_t)r * nenv; return t; };
+  DevState& s = b->s;
+  s.B = nenv;
+  s.p = take(3); s.R = take(9); s.dq = take(6); s.uq = take(3); s.acc = take(6);
+  s.T0 = take(1); s.xs = take(45); s.zs = take(39); s.ys = take(39); s.D = take(45); s.E = take(39);
+  s.solx = take(45); s.soly = take(39); s.info = take(4);
+  s.task = (int*)take(1); s.tp = take(4); s.pinit = take(3); s.actualT0 = take(1); s.metrics = take(5);
+  s.wl_u0 = take(4); s.wlqp = take(25);
+  s.qpdata = nullptr;
+  CK(cudaMalloc(&b->d_in, (size_t)28 * nenv * sizeof(float)));
+  CK(cudaMalloc(&b->d_out, (size_t)10 * nenv * sizeof(float)));
+  CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
+  CK(cudaFuncSetAttribute(umpc_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(160)));
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(160)));
+  b->tpb = nenv < 128 ? 32 : 128;
+  int rc = reset_state(b);
+  if (rc) return rc;
+  *out = b;
+  return UMPC_OK;
+}
+
+extern "C" void umpcBatchDestroy(UmpcBatch* b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  cudaStreamSynchronize(b->stream);
+  cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums);
+  cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
+  cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
+  cudaStreamDestroy(b->stream);
+  delete b;
+}
+
+extern "C" int umpcBatchSize(const UmpcBatch* b) { return b ? b->B : 0; }
+extern "C" int umpcBatchSync(UmpcBatch* b) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+extern "C" float umpcBatchLastKernelMs(UmpcBatch* b) {
+  if (!b || !b->timed) return -1.0f;
+  float ms = -1.0f;
+  if (cudaEventSynchronize(b->ev1) != cudaSuccess) return -1.0f;
+  cudaEventElapsedTime(&ms, b->ev0, b->ev1);
+  return ms;
+}
+
+static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0, const float* dq0,
+                         const float* pdes, const float* dpdes, const float* sdes, const float* aT0) {
+  const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  umpc_update_kernel<<<grid, tpb, smem_bytes(tpb), b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes,
+                                                                 aT0, b->have_qpdata ? 1 : 0);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(b->ev1, b->stream));
+  b->timed = true;
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchUpdateDev(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0,
+                                  const float* dq0, const float* pdes, const float* dpdes, const float* sdes,
+                                  const float* actualT0) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  return launch_update(b, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0);
+}
+
+extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0,
+                               const float* dq0, const float* pdes, const float* dpdes, const float* sdes,
+                               const float* actualT0) {
+  if (!b || !uquad || !accdes || !p0 || !R0 || !dq0 || !pdes || !dpdes || !sdes) { g_err = "umpcBatchUpdate: NULL argument"; return UMPC_ERR_ARG; }
+  CK(cudaSetDevice(b->device));
+  const size_t B = b->B;
+  float* d = b->d_in;
+  float *dp = d, *dR = dp + 3 * B, *ddq = dR + 9 * B, *dpd = ddq + 6 * B, *ddp = dpd + 3 * B, *dsd = ddp + 3 * B, *daT = dsd + 3 * B;
+  CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dpd, pdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
+  float *duq = b->d_out, *dacc = duq + 3 * B;
+  int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaMemcpyAsync(accdes, dacc, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+// SoA [k][B] on device <-> [B][k] on host (diagnostics / state exchange; not on the hot path)
+static int get_rows(UmpcBatch* b, const float* dev, int k, float* host) {
+  if (!host) return UMPC_OK;
+  const size_t B = b->B;
+  std::vector<float> tmp(B * k);
+  CK(cudaMemcpyAsync(tmp.data(), dev, B * k * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  for (size_t e = 0; e < B; ++e)
+    for (int i = 0; i < k; ++i) host[e * k + i] = tmp[(size_t)i * B + e];
+  return UMPC_OK;
+}
+static int put_rows(UmpcBatch* b, float* dev, int k, const float* host) {
+  const size_t B = b->B;
+  std::vector<float> tmp(B * k);
+  for (size_t e = 0; e < B; ++e)
+    for (int i = 0; i < k; ++i) tmp[(size_t)i * B + e] = host[e * k + i];
+  CK(cudaMemcpyAsync(dev, tmp.data(), B * k * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchGetSolve(UmpcBatch* b, float* info, float* x, float* y, float* xs, float* zs, float* ys, float* D,
+                                 float* E) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = get_rows(b, b->s.info, 4, info))) return rc;
+  if ((rc = get_rows(b, b->s.solx, 45, x))) return rc;
+  if ((rc = get_rows(b, b->s.soly, 39, y))) return rc;
+  if ((rc = get_rows(b, b->s.xs, 45, xs))) return rc;
+  if ((rc = get_rows(b, b->s.zs, 39, zs))) return rc;
+  if ((rc = get_rows(b, b->s.ys, 39, ys))) return rc;
+  if ((rc = get_rows(b, b->s.D, 45, D))) return rc;
+  return get_rows(b, b->s.E, 39, E);
+}
+
+extern "C" int umpcBatchGetQPData(UmpcBatch* b, float* qp) {
+  if (!b || !qp) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  if (!b->have_qpdata) {
+    // first request: allocate; data is produced by the NEXT update
+    CK(cudaMalloc(&b->s.qpdata, (size_t)216 * b->B * sizeof(float)));
+    CK(cudaMemset(b->s.qpdata, 0, (size_t)216 * b->B * sizeof(float)));
+    b->have_qpdata = true;
+  }
+  return get_rows(b, b->s.qpdata, 216, qp);
+}
+
+extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, const float* dq, const int* task,
+                                 const float* tp) {
+  if (!b || !p || !R || !dq) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = put_rows(b, b->s.p, 3, p))) return rc;
+  if ((rc = put_rows(b, b->s.pinit, 3, p))) return rc;
+  if ((rc = put_rows(b, b->s.R, 9, R))) return rc;
+  if ((rc = put_rows(b, b->s.dq, 6, dq))) return rc;
+  if (task) CK(cudaMemcpy(b->s.task, task, (size_t)b->B * sizeof(int), cudaMemcpyHostToDevice));
+  else CK(cudaMemset(b->s.task, 0, (size_t)b->B * sizeof(int)));
+  if (tp) { if ((rc = put_rows(b, b->s.tp, 4, tp))) return rc; }
+  else CK(cudaMemset(b->s.tp, 0, (size_t)4 * b->B * sizeof(float)));
+  CK(cudaMemset(b->s.uq, 0, (size_t)3 * b->B * sizeof(float)));
+  CK(cudaMemset(b->s.metrics, 0, (size_t)5 * b->B * sizeof(float)));
+  b->step = 0; b->thl = 0.0;
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchGetState(UmpcBatch* b, float* p, float* R, float* dq, float* uquad) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = get_rows(b, b->s.p, 3, p))) return rc;
+  if ((rc = get_rows(b, b->s.R, 9, R))) return rc;
+  if ((rc = get_rows(b, b->s.dq, 6, dq))) return rc;
+  return get_rows(b, b->s.uq, 3, uquad);
+}
+
+extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
+  if (!b || nsteps <= 0) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  if (nsteps > b->sched_cap) {
+    // wait for any launch still reading the old schedule buffers
+    CK(cudaStreamSynchronize(b->stream));
+    cudaFree(b->d_fire); cudaFree(b->d_t);
+    b->sched_cap = nsteps < 4096 ? 4096 : nsteps;
+    CK(cudaMalloc(&b->d_fire, b->sched_cap));
+    CK(cudaMalloc(&b->d_t, (size_t)b->sched_cap * sizeof(float)));
+  } else {
+    CK(cudaStreamSynchronize(b->stream));  // host staging vectors below are reused per call
+  }
+  // firing schedule in double, like numpy: t = ti*dtsim ; fire when hlInterval is None or t - thlPrev > hlInterval
+  std::vector<uint8_t> fire(nsteps);
+  std::vector<float> tv(nsteps);
+  const double dts = b->bp.dtsim, hl = b->bp.hlInterval;
+  for (int k = 0; k < nsteps; ++k) {
+    const double t = (double)(b->step + k) * dts;
+    const bool f = hl < 0.0 || (t - b->thl > hl);
+    if (f) b->thl = t;
+    fire[k] = f ? 1 : 0;
+    tv[k] = (float)t;
+  }
+  CK(cudaMemcpyAsync(b->d_fire, fire.data(), nsteps, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->d_t, tv.data(), (size_t)nsteps * sizeof(float), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  umpc_rollout_kernel<<<grid, tpb, smem_bytes(tpb), b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t,
+                                                                  b->lg);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(b->ev1, b->stream));
+  b->timed = true;
+  b->step += nsteps;
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchGetMetrics(UmpcBatch* b, float* metrics) {
+  if (!b || !metrics) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  return get_rows(b, b->s.metrics, 4, metrics);
+}
+
+extern "C" int umpcBatchReduceMetrics(UmpcBatch* b, double* sums8) {
+  if (!b || !sums8) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  CK(cudaMemsetAsync(b->d_sums, 0, 8 * sizeof(double), b->stream));
+  int grid = (b->B + 255) / 256;
+  if (grid > 148 * 4) grid = 148 * 4;
+  reduce_metrics_kernel<<<grid, 256, 0, b->stream>>>(b->s, b->d_sums);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(sums8, b->d_sums, 8 * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchSetLog(UmpcBatch* b, int env, int cap) {
+  if (!b || env >= b->B) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  cudaFree(b->lg.y); cudaFree(b->lg.u);
+  b->lg = LogBuf{-1, 0, nullptr, nullptr};
+  if (env < 0 || cap <= 0) return UMPC_OK;
+  CK(cudaMalloc(&b->lg.y, (size_t)cap * 12 * sizeof(float)));
+  CK(cudaMalloc(&b->lg.u, (size_t)cap * 3 * sizeof(float)));
+  CK(cudaMemset(b->lg.y, 0, (size_t)cap * 12 * sizeof(float)));
+  CK(cudaMemset(b->lg.u, 0, (size_t)cap * 3 * sizeof(float)));
+  b->lg.env = env; b->lg.cap = cap;
+  return UMPC_OK;
+}
+
+extern "C" int umpcBatchGetLog(UmpcBatch* b, float* y, float* u, int nsteps) {
+  if (!b || b->lg.env < 0 || nsteps > b->lg.cap) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  if (y) CK(cudaMemcpy(y, b->lg.y, (size_t)nsteps * 12 * sizeof(float), cudaMemcpyDeviceToHost));
+  if (u) CK(cudaMemcpy(u, b->lg.u, (size_t)nsteps * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+  return UMPC_OK;
+}
+
+extern "C" void* umpcBatchDevPtr(UmpcBatch* b, const char* name) {
+  if (!b || !name) return nullptr;
+  const DevState& s = b->s;
+  struct { const char* n; void* p; } tab[] = {
+      {"p", s.p}, {"R", s.R}, {"dq", s.dq}, {"uq", s.uq}, {"acc", s.acc}, {"T0", s.T0}, {"xs", s.xs}, {"zs", s.zs},
+      {"ys", s.ys}, {"D", s.D}, {"E", s.E}, {"solx", s.solx}, {"soly", s.soly}, {"info", s.info}, {"task", s.task},
+      {"tp", s.tp}, {"pinit", s.pinit}, {"actualT0", s.actualT0}, {"metrics", s.metrics}, {"wl_u0", s.wl_u0},
+      {"wlqp", s.wlqp}, {"stage_in", b->d_in}, {"stage_out", b->d_out}, {"stream", (void*)b->stream}};
+  for (auto& t : tab)
+    if (!strcmp(t.n, name)) return t.p;
+  return nullptr;
+}
+
+extern "C" double umpcMeasureFp32Peak(int device, int iters) {
+  if (cudaSetDevice(device) != cudaSuccess) return -1.0;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1.0;
+  float* d = nullptr;
+  if (cudaMalloc(&d, 4) != cudaSuccess) return -1.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int grid = prop.multiProcessorCount * 8, tpb = 256;
+  fp32_peak_kernel<<<grid, tpb>>>(d, 16);  // warm-up
+  double best = 0.0;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0);
+    fp32_peak_kernel<<<grid, tpb>>>(d, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double flop = 2.0 * 16 * 8 * (double)iters * grid * tpb;
+    const double tf = flop / (ms * 1e-3) * 1e-12;
+    if (tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  return best;
+}
+
+// ======================= reference-compatible single-controller API ==========================
+// The reference keeps ONE process-global OSQP workspace (workspace.c:2620); here each
+// UprightMPC_t owns a batch of 1 on the current device, found by the struct's address.
+static std::mutex g_mu;
+static std::map<const void*, UmpcBatch*> g_single;
+
+static UmpcBatch* find_single(const void* key) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_single.find(key);
+  return it == g_single.end() ? nullptr : it->second;
+}
+
+extern "C" void umpcFree(UprightMPC_t* up) {
+  UmpcBatch* b = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_single.find(up);
+    if (it != g_single.end()) { b = it->second; g_single.erase(it); }
+  }
+  umpcBatchDestroy(b);
+}
+
+// CSC position of entry (row, col) of A (pattern of initConstraint, template_controllers.py:28-63),
+// counted column by column.  Used to fill the public Ax_idx field (uprightmpc2.h:38).
+static int a_has(int r, int c) {
+  const int N = UMPC_N, ny = UMPC_NY, nu = UMPC_NU;
+  for (int k = 0; k < N; ++k) {
+    for (int i = 0; i < ny; ++i) {
+      const int rk = k * ny + i, rd = N * ny + k * ny + i;
+      if (r == rk && (c == k * ny + i || c == N * ny + k * ny + i || (k > 0 && c == (k - 1) * ny + i))) return 1;
+      if (r == rd) {
+        if (c == N * ny + k * ny + i || (k > 0 && c == N * ny + (k - 1) * ny + i)) return 1;
+        if (i < 3 && c == 2 * N * ny + k * nu) return 1;
+        if (i >= 3 && (c == 2 * N * ny + k * nu + 1 || c == 2 * N * ny + k * nu + 2)) return 1;
+        if (k > 1 && i < 3 && c == (k - 2) * ny + 3 + i) return 1;
+      }
+    }
+    if (r == 2 * N * ny + k && c == 2 * N * ny + nu * k) return 1;
+  }
+  return 0;
+}
+static int a_csc_index(int r, int c) {
+  int n = 0;
+  for (int cc = 0; cc < UMPC_NX; ++cc)
+    for (int rr = 0; rr < UMPC_NC; ++rr) {
+      if (rr == r && cc == c) return a_has(r, c) ? n : -1;
+      n += a_has(rr, cc);
+    }
+  return -1;
+}
+
+extern "C" void umpcInit(UprightMPC_t* up, float dt, float g, float TtoWmax, float ws, float wds, float wpr, float wpf,
+                         float wvr, float wvf, float wthrust, float wmom, const float Ib[3], int maxIter) {
+  umpcFree(up);
+  memset(up, 0, sizeof(*up));
+  up->dt = dt; up->g = g; up->Tmax = TtoWmax * g;
+  for (int i = 0; i < 3; ++i) {
+    up->Qyr[i] = wpr; up->Qyf[i] = wpf; up->Qyr[3 + i] = up->Qyf[3 + i] = ws;
+    up->Qdyr[i] = wvr; up->Qdyf[i] = wvf; up->Qdyr[3 + i] = up->Qdyf[3 + i] = wds;
+  }
+  up->R[0] = wthrust; up->R[1] = up->R[2] = wmom;
+  up->c0[2] = -g;
+  up->e3h[1] = 1.0f; up->e3h[3] = -1.0f;            // skew(e3), column-major
+  up->e3hIbi[1] = 1.0f / Ib[0]; up->e3hIbi[3] = -1.0f / Ib[1];  // e3h * diag(1/Ib)
+  // Ax_idx: positions of the time-varying entries in A.x, in Ax_data order (uprightmpc2.c:160-179)
+  int o = 0;
+  const int N = UMPC_N, ny = UMPC_NY, nu = UMPC_NU;
+  for (int k = 2; k < N; ++k)
+    for (int i = 0; i < 3; ++i) up->Ax_idx[o++] = a_csc_index(N * ny + k * ny + i, (k - 2) * ny + 3 + i);
+  up->nAxT0dt = o;
+  for (int k = 0; k < N; ++k)
+    for (int i = 0; i < ny; ++i) up->Ax_idx[o++] = a_csc_index(k * ny + i, N * ny + k * ny + i);
+  up->nAxdt = o;
+  for (int k = 0; k < N; ++k)
+    for (int i = 0; i < 3; ++i) up->Ax_idx[o++] = a_csc_index(N * ny + k * ny + i, 2 * N * ny + k * nu);
+  for (int k = 0; k < N; ++k)
+    for (int j = 0; j < 2; ++j)
+      for (int i = 0; i < 3; ++i) up->Ax_idx[o++] = a_csc_index(N * ny + k * ny + 3 + i, 2 * N * ny + k * nu + 1 + j);
+  UmpcBatchParams bp;
+  umpcBatchDefaults(&bp);
+  bp.dt = dt; bp.g = g; bp.TtoWmax = TtoWmax; bp.ws = ws; bp.wds = wds; bp.wpr = wpr; bp.wpf = wpf; bp.wvr = wvr;
+  bp.wvf = wvf; bp.wthrust = wthrust; bp.wmom = wmom; bp.maxIter = maxIter;
+  for (int i = 0; i < 3; ++i) bp.Ib[i] = Ib[i];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  UmpcBatch* b = nullptr;
+  if (umpcBatchCreate(&b, 1, dev, &bp) != UMPC_OK) {
+    fprintf(stderr, "umpcInit (libumpc_b200): %s\n", umpcLastError());
+    return;
+  }
+  std::vector<float> scratch(216);
+  umpcBatchGetQPData(b, scratch.data());  // switches the QP-data output on
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_single[up] = b;
+}
+
+extern "C" int umpcUpdate(UprightMPC_t* up, float uquad[3], float accdes[6], const float p0[3], const float R0[9],
+                          const float dq0[6], const float pdes[3], const float dpdes[3], const float sdes[3],
+                          float actualT0) {
+  UmpcBatch* b = find_single(up);
+  if (!b) {
+    fprintf(stderr, "umpcUpdate (libumpc_b200): controller not initialised on a CUDA device (no CPU path)\n");
+    for (int i = 0; i < 3; ++i) uquad[i] = nanf("");
+    for (int i = 0; i < 6; ++i) accdes[i] = nanf("");
+    return UMPC_ERR_CUDA;
+  }
+  // T0 is a public field the caller may have edited between calls (uprightmpc2.h:42)
+  if (cudaMemcpy(b->s.T0, &up->T0, sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) return UMPC_ERR_CUDA;
+  int rc = umpcBatchUpdate(b, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, &actualT0);
+  if (rc) { fprintf(stderr, "umpcUpdate (libumpc_b200): %s\n", umpcLastError()); return rc; }
+  float qp[216];
+  umpcBatchGetQPData(b, qp);
+  memcpy(up->l, qp, sizeof(up->l)); memcpy(up->u, qp + 39, sizeof(up->u)); memcpy(up->q, qp + 78, sizeof(up->q));
+  memcpy(up->Px_data, qp + 123, sizeof(up->Px_data)); memcpy(up->Ax_data, qp + 168, sizeof(up->Ax_data));
+  cudaMemcpy(&up->T0, b->s.T0, sizeof(float), cudaMemcpyDeviceToHost);
+  return 0;
+}
+
+static UprightMPC_t g_up_s;
+static int g_up_inited = 0;
+extern "C" void umpcS(float uquad[3], float accdes[6], const float p0[3], const float R0[9], const float dq0[6],
+                      const float pdes[3], const float dpdes[3], const float sdes[3], float dt, float g, float TtoWmax,
+                      float ws, float wds, float wpr, float wpf, float wvr, float wvf, float wthrust, float wmom,
+                      const float Ib[3], int maxIter, float actualT0) {
+  if (!g_up_inited) {  // lazy singleton like uprightmpc2.c:275-283
+    umpcInit(&g_up_s, dt, g, TtoWmax, ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom, Ib, maxIter);
+    g_up_inited = 1;
+  }
+  umpcUpdate(&g_up_s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0);
+}
+
+extern "C" void umpcGetInfo(const UprightMPC_t* up, float info4[4]) {
+  UmpcBatch* b = find_single(up);
+  if (!b) { for (int i = 0; i < 4; ++i) info4[i] = nanf(""); return; }
+  umpcBatchGetSolve(b, info4, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+extern "C" void umpcGetSolution(const UprightMPC_t* up, float x[45], float y[39]) {
+  UmpcBatch* b = find_single(up);
+  if (!b) return;
+  umpcBatchGetSolve(b, nullptr, x, y, nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+
+// ---- WL stage, single instance ------------------------------------------------------------------
+static UmpcBatch* g_wl_batch = nullptr;  // batch of 1 used as device scratch for the WL drop-ins
+
+static int wl_single(const WlParams& wp, int mode, float u0[4], WlqpState* qs, const float h0[6], const float pdotdes[6],
+                     float w0[6]) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_wl_batch) {
+    UmpcBatchParams bp;
+    umpcBatchDefaults(&bp);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (umpcBatchCreate(&g_wl_batch, 1, dev, &bp) != UMPC_OK) {
+      fprintf(stderr, "libumpc_b200 WL stage: %s\n", umpcLastError());
+      g_wl_batch = nullptr;
+      return UMPC_ERR_CUDA;
+    }
+  }
+  UmpcBatch* b = g_wl_batch;
+  CK(cudaSetDevice(b->device));
+  float in[12], out[10];
+  memcpy(in, h0, 24); memcpy(in + 6, pdotdes, 24);
+  CK(cudaMemcpyAsync(b->d_in, in, sizeof(in), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->s.wl_u0, u0, 16, cudaMemcpyHostToDevice, b->stream));
+  if (qs) {
+    float q[25];
+    memcpy(q, qs->xs, 16); memcpy(q + 4, qs->zs, 16); memcpy(q + 8, qs->ys, 16); memcpy(q + 12, qs->D, 16);
+    memcpy(q + 16, qs->E, 16); q[20] = qs->c; memcpy(q + 21, qs->q0, 16);
+    CK(cudaMemcpyAsync(b->s.wlqp, q, sizeof(q), cudaMemcpyHostToDevice, b->stream));
+  }
+  wl_update_kernel<<<1, 32, 0, b->stream>>>(wp, b->s, mode, b->d_out, b->d_out + 4, b->d_in, b->d_in + 6, nullptr);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, b->d_out, sizeof(out), cudaMemcpyDeviceToHost, b->stream));
+  float q[25];
+  if (qs) CK(cudaMemcpyAsync(q, b->s.wlqp, sizeof(q), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  memcpy(u0, out, 16); memcpy(w0, out + 4, 24);
+  if (qs) {
+    memcpy(qs->xs, q, 16); memcpy(qs->zs, q + 4, 16); memcpy(qs->ys, q + 8, 16); memcpy(qs->D, q + 12, 16);
+    memcpy(qs->E, q + 16, 16); qs->c = q[20]; memcpy(qs->q0, q + 21, 16);
+  }
+  return UMPC_OK;
+}
+
+extern "C" void wlConInit(WLCon_t* wl, const float u0[4], const float umin[4], const float umax[4], const float dumax[4],
+                          const float Qw[6], float controlRate, const float popts[90]) {
+  memset(wl, 0, sizeof(*wl));
+  for (int i = 0; i < NDELU; ++i) {
+    wl->u0[i] = u0[i]; wl->umin[i] = umin[i]; wl->umax[i] = umax[i]; wl->dumax[i] = dumax[i] / controlRate;
+  }
+  for (int i = 0; i < 6; ++i) {
+    wl->Qw[i + 6 * i] = Qw[i];
+    FunApprox_t& f = wl->fa[i];
+    const float* po = popts + 15 * i;
+    f.k = NDELU; f.a0 = po[0];
+    int kk = 1 + NDELU;
+    for (int r = 0; r < NDELU; ++r) f.a1[r] = po[1 + r];
+    for (int r = 0; r < NDELU; ++r)
+      for (int c = r; c < NDELU; ++c) { f.A2[r + NDELU * c] = f.A2[c + NDELU * r] = po[kk++]; }
+  }
+}
+
+static void wlparams_from_struct(const WLCon_t* wl, WlParams& wp) {
+  memset(&wp, 0, sizeof(wp));
+  for (int i = 0; i < 6; ++i) {
+    const FunApprox_t& f = wl->fa[i];
+    float* po = wp.popts + 15 * i;
+    po[0] = f.a0;
+    int kk = 1 + NDELU;
+    for (int r = 0; r < NDELU; ++r) po[1 + r] = f.a1[r];
+    for (int r = 0; r < NDELU; ++r)
+      for (int c = r; c < NDELU; ++c) po[kk++] = f.A2[r + NDELU * c];
+    wp.Qw[i] = wl->Qw[i + 6 * i];
+  }
+  for (int i = 0; i < NDELU; ++i) { wp.umin[i] = wl->umin[i]; wp.umax[i] = wl->umax[i]; wp.dumax[i] = wl->dumax[i]; }
+}
+
+extern "C" void wlConUpdate(WLCon_t* wl, float u1[4], float w0[6], const float h0[6], const float pdotdes[6]) {
+  WlParams wp;
+  wlparams_from_struct(wl, wp);
+  if (wl_single(wp, 1, wl->u0, nullptr, h0, pdotdes, w0) != UMPC_OK) {
+    for (int i = 0; i < 4; ++i) u1[i] = nanf("");
+    return;
+  }
+  for (int i = 0; i < 4; ++i) u1[i] = wl->u0[i];
+}
+
+static WLCon_t g_wl_s;
+static int g_wl_inited = 0;
+extern "C" void wlconS(float u1[4], float w0[6], const float u0init[4], const float umin[4], const float umax[4],
+                       const float dumax[4], const float Qw[6], float controlRate, const float popts[90], const float h0[6],
+                       const float pdotdes[6]) {
+  if (!g_wl_inited) {  // funapprox.c:168-177
+    wlConInit(&g_wl_s, u0init, umin, umax, dumax, Qw, controlRate, popts);
+    g_wl_inited = 1;
+  }
+  wlConUpdate(&g_wl_s, u1, w0, h0, pdotdes);
+}
+
+// true WLQP with the global lazily-initialised state of wlcontroller.c:17-45
+static float g_u0[4] = {-1.0f, 0.0f, 0.0f, 0.0f};
+static WlqpState g_wlqp_state;
+static WlParams g_wlqp_par;
+static int g_wlqp_check = 25;
+
+extern "C" void wlControllerReset(void) { g_u0[0] = -1.0f; g_u0[1] = g_u0[2] = g_u0[3] = 0.0f; }
+extern "C" void wlControllerSetCheckTermination(int k) { g_wlqp_check = k; }
+
+extern "C" void wlControllerUpdateW(float* u, float* w0, const float* u0init, const float* h0, const float* pdotdes,
+                                    const float* popts, float controlRate) {
+  if (g_u0[0] < 0.0f) {
+    UmpcBatchParams bp;
+    umpcBatchDefaults(&bp);  // wlqpInit limits (wlqp.c:17-46) == WaypointHover limits
+    UmpcBatch tmp;
+    tmp.bp = bp;
+    memcpy(tmp.bp.wl_popts, popts, sizeof(tmp.bp.wl_popts));
+    tmp.bp.wl_controlRate = controlRate;
+    tmp.bp.wlqpCheckTermination = g_wlqp_check;
+    fill_kernel_params(&tmp);
+    g_wlqp_par = tmp.wlp;
+    wlqp_state_init(g_wlqp_state);
+    for (int i = 0; i < 4; ++i) g_u0[i] = u0init[i];
+  }
+  float w0l[6];
+  if (wl_single(g_wlqp_par, 2, g_u0, &g_wlqp_state, h0, pdotdes, w0l) != UMPC_OK) {
+    for (int i = 0; i < 4; ++i) u[i] = nanf("");
+    return;
+  }
+  for (int i = 0; i < 4; ++i) u[i] = g_u0[i];
+  if (w0) memcpy(w0, w0l, sizeof(w0l));
+}
+
+extern "C" void wlControllerUpdate(float* u, const float* u0init, const float* h0, const float* pdotdes, const float* popts,
+                                   float controlRate) {
+  wlControllerUpdateW(u, nullptr, u0init, h0, pdotdes, popts, controlRate);
+}

@@ -6,24 +6,38 @@
 #include "../../robobee3d_b200/csrc/umpc_core.cuh"
 
 struct HostStore {
-  float l[UMPC_GEN_NNZL], di[UMPC_NX], w[UMPC_NC], wi[UMPC_NC], sg[UMPC_NX], lo[UMPC_NC], hi[3], d[UMPC_NX], e[UMPC_NC];
+  float l[UMPC_GEN_NNZL], di[UMPC_NX], aw[UMPC_NEQ], sg[UMPC_NX], lo[UMPC_NEQ], vf[UMPC_NEQ];
   float& L(int n) { return l[n]; }
   float L(int n) const { return l[n]; }
   float& Di(int k) { return di[k]; }
   float Di(int k) const { return di[k]; }
-  float& W(int i) { return w[i]; }
-  float& Wi(int i) { return wi[i]; }
+  float& aW(int i) { return aw[i]; }
   float& Sg(int j) { return sg[j]; }
   float& Lo(int i) { return lo[i]; }
-  float& Hi(int i) { return hi[i]; }
-  float& Dsc(int j) { return d[j]; }
-  float& Esc(int i) { return e[i]; }
+  float& Vf(int i) { return vf[i]; }
+};
+
+struct HostIO {
+  float xs[UMPC_NX], zs[UMPC_NC], ys[UMPC_NC], D[UMPC_NX], E[UMPC_NC], solx[UMPC_NX], soly[UMPC_NC];
+  float ld_xs(int j) const { return xs[j]; }
+  float ld_zs(int i) const { return zs[i]; }
+  float ld_ys(int i) const { return ys[i]; }
+  float ld_D(int j) const { return D[j]; }
+  float ld_E(int i) const { return E[i]; }
+  void st_xs(int j, float v) { xs[j] = v; }
+  void st_zs(int i, float v) { zs[i] = v; }
+  void st_ys(int i, float v) { ys[i] = v; }
+  void st_D(int j, float v) { D[j] = v; }
+  void st_E(int i, float v) { E[i] = v; }
+  void st_solx(int j, float v) { solx[j] = v; }
+  void st_soly(int i, float v) { soly[i] = v; }
 };
 
 struct HcState {
-  float T0, xs[UMPC_NX], zs[UMPC_NC], ys[UMPC_NC], Eold[3], solx[UMPC_NX], soly[UMPC_NC];
+  float T0;
   UmpcInfo info;
   HostStore st;
+  HostIO io;
 };
 
 extern "C" {
@@ -31,18 +45,18 @@ int hc_sizeof_state() { return (int)sizeof(HcState); }
 int hc_sizeof_params() { return (int)sizeof(UmpcParams); }
 void hc_init(HcState* s) {
   memset(s, 0, sizeof(*s));
-  s->Eold[0] = s->Eold[1] = s->Eold[2] = 1.0f;
+  for (int i = 0; i < UMPC_NX; ++i) s->io.D[i] = 1.0f;
+  for (int i = 0; i < UMPC_NC; ++i) s->io.E[i] = 1.0f;
 }
 int hc_update(const UmpcParams* par, HcState* s, float* uquad, float* accdes, const float* p0, const float* R0,
               const float* dq0, const float* pdes, const float* dpdes, const float* sdes, float actualT0) {
-  umpc_update(*par, s->st, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0, s->T0, s->xs, s->zs, s->ys,
-              s->Eold, s->solx, s->soly, s->info);
+  umpc_update(*par, s->st, s->io, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0, s->T0, s->info);
   return 0;
 }
 void hc_get(const HcState* s, float* solx, float* soly, float* xs, float* zs, float* ys, float* D, float* E, float* info4) {
-  memcpy(solx, s->solx, sizeof(s->solx)); memcpy(soly, s->soly, sizeof(s->soly));
-  memcpy(xs, s->xs, sizeof(s->xs)); memcpy(zs, s->zs, sizeof(s->zs)); memcpy(ys, s->ys, sizeof(s->ys));
-  memcpy(D, s->st.d, sizeof(s->st.d)); memcpy(E, s->st.e, sizeof(s->st.e));
+  memcpy(solx, s->io.solx, sizeof(s->io.solx)); memcpy(soly, s->io.soly, sizeof(s->io.soly));
+  memcpy(xs, s->io.xs, sizeof(s->io.xs)); memcpy(zs, s->io.zs, sizeof(s->io.zs)); memcpy(ys, s->io.ys, sizeof(s->io.ys));
+  memcpy(D, s->io.D, sizeof(s->io.D)); memcpy(E, s->io.E, sizeof(s->io.E));
   info4[0] = (float)s->info.iter; info4[1] = (float)s->info.status; info4[2] = s->info.pri_res; info4[3] = s->info.dua_res;
 }
 void hc_qpdata(const UmpcParams* par, const float* p0, const float* R0, const float* dq0, const float* pdes,

@@ -1,0 +1,149 @@
+"""GPU closed-loop / WL parity tests against reference-generated golden trajectories and the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import util
+from util import GOLDEN, TOL_TRAJ_P, TOL_TRAJ_S
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLDEN, "rollout_c1.npz"))
+
+
+def _ic(B):
+    from oracle.binding import control_test_ic
+    p, R, dq = control_test_ic()
+    return np.tile(p, (B, 1)), np.tile(R, (B, 1, 1)), np.tile(dq, (B, 1))
+
+
+@pytest.mark.parametrize("name,hl,tend", [("hl5", 5.0, 500.0), ("every", None, 100.0)])
+def test_config1_hover_matches_reference(cuda_required, gold, name, hl, tend):
+    """controlTest (uprightmpc2.py:87-159) from the tilted IC, hover task: trajectory within
+    0.5 mm / 1e-2 of the reference C controller + double plant, logMetric within 1%."""
+    from robobee3d_b200.batch import BatchUMPC
+    nt = int(np.ceil(tend / 0.2))
+    b = BatchUMPC(64, hlInterval=hl)
+    p, R, dq = _ic(64)
+    b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
+    b.set_log(3, nt)
+    # split the horizon over several launches: the schedule must carry over
+    for n in (1, 7, nt - 8):
+        b.rollout(n)
+    y, u = b.get_log(nt)
+    gy, gu = gold[name + "_y"], gold[name + "_u"]
+    assert np.abs(y[::10, :3] - gy[:, :3]).max() <= TOL_TRAJ_P
+    assert np.abs(y[::10, 3:6] - gy[:, 3:6]).max() <= TOL_TRAJ_S
+    m = b.metrics()
+    gm = gold[name + "_metrics"]
+    assert (m["nsolve"] == int(gm[2])).all() and (m["nstep"] == nt).all()
+    assert abs(m["err"][3] / gm[0] - 1) < 1e-2 and abs(m["eff"][3] / gm[1] - 1) < 1e-2
+    # identical ICs -> identical envs
+    assert np.ptp(m["err"]) == 0.0
+    b.close()
+
+
+@pytest.mark.parametrize("name,task", [("helix", 0), ("helixpert", 0), ("flip", 2), ("perch", 3), ("straight", 1)])
+def test_flight_tasks_match_reference(cuda_required, gold, name, task):
+    from robobee3d_b200.batch import BatchUMPC
+    nt = 1500
+    b = BatchUMPC(32, hlInterval=5.0, tpert=100.0 if name == "helixpert" else None)
+    p, R, dq = _ic(32)
+    b.set_state(p, R, dq, task=task, tp=gold[name + "_tp"])
+    b.set_log(0, nt)
+    b.rollout(nt)
+    y, u = b.get_log(nt)
+    gy = gold[name + "_y"]
+    # aggressive manoeuvres amplify round-off: scale the position tolerance with the excursion
+    tol_p = max(TOL_TRAJ_P, 2e-3 * np.abs(gy[:, :3]).max())
+    gm = gold[name + "_metrics"]
+    m = b.metrics()
+    assert m["nsolve"][0] == int(gm[2])
+    if name == "helixpert":
+        # the dq[1] += 2 mm/ms kick at t = 100 ms (uprightmpc2.py:131-133) makes the flight ill-conditioned:
+        # the float32 and float64 builds of the reference algorithm themselves differ by ~3 mm / 0.8 in s
+        # afterwards (oracle f32 vs oracle/_ref).  Tight before the kick, bounded after it.
+        k = 50  # 100 ms / (0.2 ms * 10)
+        assert np.abs(y[::10, :3][:k] - gy[:k, :3]).max() <= tol_p
+        assert np.abs(y[::10, :3] - gy[:, :3]).max() <= 10.0
+        assert abs(m["err"][0] / gm[0] - 1) < 5e-2
+        b.close()
+        return
+    assert np.abs(y[::10, :3] - gy[:, :3]).max() <= tol_p
+    assert np.abs(y[::10, 3:6] - gy[:, 3:6]).max() <= 2 * TOL_TRAJ_S
+    assert abs(m["err"][0] / gm[0] - 1) < 2e-2
+    b.close()
+
+
+def test_wl_stage_matches_reference(cuda_required):
+    """WLCon (projected gradient) and true WLQP through the drop-in classes on the scripted demand of
+    template/wlcontroller/testwlqppy.py:15-40."""
+    from robobee3d_b200 import uprightmpc2py, wlqppy
+    c = util.load_constants()
+    g = np.load(os.path.join(GOLDEN, "wl_seq.npz"))
+    wd = c["wl_defaults"]
+    for pname in ("popts_testwlqp", "popts_waypoint"):
+        con = uprightmpc2py.WLCon(wd["u0"], wd["umin"], wd["umax"], wd["dumax"], wd["Qw"], wd["controlRate"], c[pname])
+        qp = wlqppy.WLController(c[pname], 1000.0)
+        n = 200
+        Uc, Wc, Uq = [], [], []
+        for i in range(1, n + 1):
+            u1, w0 = con.update(g["h0"], g["pdotdes"][i])
+            Uc.append(u1); Wc.append(w0)
+            uq, _ = qp.update(wd["u0"], g["h0"], g["pdotdes"][i])
+            Uq.append(uq)
+        Uc, Wc, Uq = np.array(Uc), np.array(Wc), np.array(Uq)
+        scale = np.abs(g[pname + "_con_u"][:n]).max(axis=0)
+        assert (np.abs(Uc - g[pname + "_con_u"][:n]) / scale).max() < 1e-4
+        assert np.abs(Wc - g[pname + "_con_w0"][:n]).max() < 1e-3 * max(1.0, np.abs(g[pname + "_con_w0"]).max())
+        # WLQP: eps 1e-3 termination -> compare within the solver's own tolerance on du
+        assert (np.abs(Uq - g[pname + "_qp_u"][:n]) / scale).max() < 2e-3, (pname, (np.abs(Uq - g[pname + "_qp_u"][:n]) / scale).max())
+
+
+def test_cascade_matches_reference(cuda_required):
+    """config 4 cascade: umpcUpdate -> (h0, M0 accdes) -> wlConUpdate -> actualT0 feedback."""
+    from robobee3d_b200.batch import BatchUMPC
+    c = util.load_constants()
+    g = np.load(os.path.join(GOLDEN, "wl_seq.npz"))
+    nt = 1000
+    b = BatchUMPC(32, hlInterval=1.0, wlMode=1, wl_popts=c["popts_waypoint"])
+    p, R, dq = _ic(32)
+    b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
+    b.set_log(1, nt)
+    b.rollout(nt)
+    y, u = b.get_log(nt)
+    assert np.abs(y[::10, :3] - g["cascade_y"][:, :3]).max() <= TOL_TRAJ_P
+    assert np.abs(y[::10, 3:6] - g["cascade_y"][:, 3:6]).max() <= TOL_TRAJ_S
+    assert b.metrics()["nsolve"][0] == int(g["cascade_metrics"][2])
+    b.close()
+
+
+def test_monte_carlo_rollout_properties(cuda_required):
+    """config 3 shape at reduced horizon: 65,536 perturbed flights stay finite, the rotation stays
+    orthonormal, metrics reduce on-device to the same sums as on the host, and a shard of the batch
+    reproduces the same envs bit for bit."""
+    from robobee3d_b200.batch import BatchUMPC
+    B, nt = 65536, 50
+    p, R, dq = util.config3_ics(B, seed=0)
+    b = BatchUMPC(B)
+    b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
+    b.rollout(nt)
+    pf, Rf, dqf, uq = b.state()
+    assert np.isfinite(pf).all() and np.isfinite(Rf).all() and np.isfinite(dqf).all()
+    RtR = np.einsum("bij,bik->bjk", Rf, Rf)
+    assert np.abs(RtR - np.eye(3)).max() < 1e-3
+    m = b.metrics()
+    s = b.reduce_metrics()
+    assert s[2] == B * nt and s[3] == B * nt and s[4] == 0
+    assert abs(s[0] / (m["err"].astype(np.float64) * nt).sum() - 1) < 1e-5
+    lo, hi = 1000, 1512
+    b2 = BatchUMPC(hi - lo)
+    b2.set_state(p[lo:hi], R[lo:hi], dq[lo:hi], task=0, tp=(0.0, 0.0, 0.1, 0.0))
+    b2.rollout(nt)
+    p2, R2, dq2, _ = b2.state()
+    assert np.array_equal(p2, pf[lo:hi]) and np.array_equal(dq2, dqf[lo:hi])
+    b.close(); b2.close()
