@@ -1,0 +1,288 @@
+#!/usr/bin/env python
+"""bench.py -- closed-loop UprightMPC2 Monte Carlo on B200 (BASELINE.json configs[2]).
+
+Workload (per GPU): 65,536 independent flights (config-3 perturbed ICs, hover task), MPC every plant step
+(hlInterval=None, controlTest's default), so one env-step = one umpcUpdate-equivalent QP solve (Ruiz x10,
+factor, 50 fixed-rho ADMM iterations, float32 -- the reference C path) + torque clip + rigid-body step.
+A "step" = one lockstep env-step of all envs of the rank = one launch of umpc_rollout_kernel.
+
+  value : env-steps/s (= QP solves/s), state resident in HBM, CUDA events on the launching stream.
+  e2e   : the same env-step through the C-ABI with HOST (pinned) buffers, umpcBatchEnvStep: H2D of
+          (p,R,dq,pdes,dpdes,sdes), kernel, D2H of (uquad,accdes,p,R,dq) inside the timed region.
+  --impl reference : the reference's own C controller (oracle/_ref, compiled from /root/reference sources)
+          driven by the same loop on all host cores, one process per core.
+
+Launch: python bench.py [--gpus N --steps K --warmup W]; for N>1 via torchrun (one rank per GPU).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+NENV_PER_GPU = 65536
+METRIC = "closed-loop UprightMPC2 env-steps/s (MPC every step: = QP solves/s)"
+UNIT = "env-steps/s"
+
+
+def workload_config(n_gpus, nenv):
+    return {"workload": "BASELINE configs[2]: %d-env closed-loop Monte Carlo per GPU (quadrotorNLDyn plant + UprightMPC2 "
+                        "N=3, faithful C path: 10 Ruiz passes + refactor + 50 fixed-rho float32 ADMM iterations per "
+                        "env-step), perturbed controlTest ICs, hover task, hlInterval=None, dtsim=0.2 ms" % nenv,
+            "envs_per_gpu": nenv, "envs_total": nenv * n_gpus, "mpc_every_step": True, "max_iter": 50,
+            "sharding": "contiguous env ranges per rank, no data-path collective; one all-reduce of 8 doubles at the end",
+            "l2_policy": "per-step working set %.0f MB/GPU (SoA state of all envs) streams through L2 each step; "
+                         "inputs are not re-used between steps except by the same env" % (nenv * 2172 / 1e6)}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.stop = False
+        self.idx = gpu_index
+        self.t = None
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def start(self):
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def finish(self):
+        self.stop = True
+        if self.t:
+            self.t.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for j, n in enumerate(names) if any(r[3 + j].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
+
+
+def make_ics(nenv, seed):
+    import util
+    p, R, dq = util.config3_ics(nenv, seed=seed)
+    return p, R, dq
+
+
+def fast_ics(nenv, seed):
+    """config-3 ICs vectorised (65k rotations through the python loop of tests/util.py would take a minute)."""
+    from oracle.binding import control_test_ic
+    rng = np.random.default_rng(seed)
+    p0, R0, dq0 = control_test_ic()
+    p = p0[None] + rng.normal(0, 5.0, (nenv, 3))
+    dq = np.tile(dq0, (nenv, 1))
+    dq[:, :3] += rng.normal(0, 0.05, (nenv, 3))
+    w = rng.normal(0, 0.1, (nenv, 3))
+    th = np.linalg.norm(w, axis=1)
+    K = np.zeros((nenv, 3, 3))
+    K[:, 0, 1], K[:, 0, 2], K[:, 1, 0], K[:, 1, 2], K[:, 2, 0], K[:, 2, 1] = -w[:, 2], w[:, 1], w[:, 2], -w[:, 0], -w[:, 1], w[:, 0]
+    a = (np.sin(th) / th)[:, None, None]
+    b = ((1 - np.cos(th)) / th ** 2)[:, None, None]
+    Ex = np.eye(3)[None] + a * K + b * (K @ K)
+    R = R0[None] @ Ex
+    return p, R, dq
+
+
+def run_reference(args):
+    """CPU arm: the reference's C controller on all host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import binding as OB
+    if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle_f32.so")):
+        OB.build(ref=os.path.isdir("/root/reference"))
+    cores = os.cpu_count() or 1
+    nenv = min(NENV_PER_GPU, cores * 256)  # bounded sample of the workload per step
+    p, R, dq = fast_ics(nenv, seed=0)
+    ics = np.concatenate([p, R.transpose(0, 2, 1).reshape(-1, 9), dq], axis=1)
+    # warm-up + timed: each "step" advances the sampled envs one closed-loop step on all cores
+    OB.cpu_env_steps(ics[: cores * 8], max(1, args.warmup), cores)
+    done, tmax, wall, kind = OB.cpu_env_steps(ics, args.steps, cores)
+    value = done / tmax
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.gpus, NENV_PER_GPU),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": "%d of %d envs x %d steps, one process per core (%s)" % (
+                                 nenv, NENV_PER_GPU, args.steps,
+                                 "reference C sources compiled -O3, oracle/_ref" if kind == "reference" else "oracle port")},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--envs", type=int, default=NENV_PER_GPU, help="envs per GPU (default: the BASELINE config)")
+    ap.add_argument("--tpb", type=int, default=0, help="threads per block override (tuning)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from robobee3d_b200 import build as _build
+    from robobee3d_b200.batch import BatchUMPC, gather_metrics, shard_range
+    from robobee3d_b200 import flops as F
+    if rank == 0:
+        _build.build()
+    if world > 1:
+        dist.barrier()
+    nenv = args.envs
+    # global env ids [rank*nenv, (rank+1)*nenv): seed keyed by the global range -> shard-invariant ICs
+    p, R, dq = fast_ics(nenv * world, seed=0)
+    lo, hi = shard_range(nenv * world, rank, world)
+    p, R, dq = p[lo:hi], R[lo:hi], dq[lo:hi]
+    b = BatchUMPC(nenv, device=local)
+    if args.tpb:
+        b.set_launch(args.tpb)
+    b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg ------------------------------------------------------------------
+    for _ in range(args.warmup):
+        b.rollout(1, sync=False)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    # CUDA events recorded on the stream the kernels are launched on (the library's own stream)
+    t0 = time.perf_counter()
+    b.timer_start()
+    for _ in range(args.steps):
+        b.rollout(1, sync=False)
+    dev_s = b.timer_stop_ms() * 1e-3
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.finish() if rank == 0 else None
+    t = torch.tensor([dev_s, wall], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_s, wall = float(t[0]), float(t[1])
+    sums = gather_metrics(b.reduce_metrics())
+
+    # ---- e2e leg: host buffers through the C-ABI -------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        pin = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).pin_memory()
+        hp, hR, hdq = pin(p), pin(R.transpose(0, 2, 1).reshape(nenv, 9)), pin(dq)
+        hpd, hdp, hsd = pin(np.zeros((nenv, 3))), pin(np.zeros((nenv, 3))), pin(np.tile([0, 0, 1.0], (nenv, 1)))
+        huq, hacc = pin(np.zeros((nenv, 3))), pin(np.zeros((nenv, 6)))
+        b2 = BatchUMPC(nenv, device=local)
+        if args.tpb:
+            b2.set_launch(args.tpb)
+        for _ in range(args.warmup):
+            b2.env_step_raw(huq, hacc, hp, hR, hdq, hpd, hdp, hsd)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            b2.env_step_raw(huq, hacc, hp, hR, hdq, hpd, hdp, hsd)
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        assert torch.isfinite(hp).all()
+        e2e = {"value": nenv * world * args.steps / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 27 * 4 * nenv,
+               "d2h_bytes_per_step": 27 * 4 * nenv, "ms_per_step": 1e3 * float(te[0]) / args.steps,
+               "call": "umpcBatchEnvStep (pinned host buffers; umpcUpdate + clip + quadrotorNLDyn per env)"}
+        b2.close()
+
+    if rank == 0:
+        fl = F.our_flops(50)
+        per_launch_flops = (fl["total"] + F.DYN_STEP_FLOPS) * nenv
+        launch_s = dev_s / args.steps
+        peak_tf = b.lib.umpcMeasureFp32Peak(local, 4096)
+        achieved_tf = per_launch_flops / launch_s * 1e-12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
+                    "traffic": None,
+                    "kernel": "umpc_rollout_kernel",
+                    "note": "FP32 CUDA-core pipe bound (arithmetic intensity %.0f flop/B vs ridge ~11): peak = FFMA "
+                            "microbenchmark run in this process (MEASURED_PEAKS.json has no FP32 figure); achieved = "
+                            "executed-algorithm flops %d/solve (FMA=2; reference formulation would be %d) x envs / "
+                            "CUDA-event launch time" % (fl["total"] / F.BYTES_PER_SOLVE, fl["total"],
+                                                        F.reference_algorithm_flops(50)),
+                    "hbm": {"achieved": F.BYTES_PER_SOLVE * nenv / launch_s * 1e-9, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": F.BYTES_PER_SOLVE * nenv / launch_s * 1e-9 / hbm_peak,
+                            "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"},
+                    "ref_algorithm_equiv_tflops": F.reference_algorithm_flops(50) * nenv / launch_s * 1e-12}
+        line = {"metric": METRIC, "value": nenv * world * args.steps / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(world, nenv),
+                "qp_solves_per_s": nenv * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall / args.steps,
+                "gpu_launches": args.steps, "clocks": clocks, "roofline": roofline,
+                "tracking": {"mean_err_mm2": sums[0] / max(sums[3], 1), "mean_eff": sums[1] / max(sums[3], 1),
+                             "env_steps_total": sums[3], "non_finite_envs": sums[4]}}
+        if e2e:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu:
+            from oracle import binding as OB
+            cores = os.cpu_count() or 1
+            ns = min(nenv, cores * 128)
+            pc, Rc, dqc = p[:ns], R[:ns], dq[:ns]
+            ics = np.concatenate([pc, Rc.transpose(0, 2, 1).reshape(-1, 9), dqc], axis=1)
+            steps_cpu = 20
+            done, tmax, _, kind = OB.cpu_env_steps(ics, steps_cpu, cores)
+            line["cpu_baseline"] = {"value": done / tmax, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "sample": "%d of the %d envs x %d steps, one process per host core" % (ns, nenv, steps_cpu)}
+        print(json.dumps(line))
+    b.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

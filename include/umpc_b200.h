@@ -143,6 +143,11 @@ int umpcBatchReset(UmpcBatch *b);
  * actualT0[B] or NULL (= -1: keep internal T0) -> uquad[B][3], accdes[B][6]. */
 int umpcBatchUpdate(UmpcBatch *b, float *uquad, float *accdes, const float *p0, const float *R0, const float *dq0,
                     const float *pdes, const float *dpdes, const float *sdes, const float *actualT0);
+/* One closed-loop env-step per environment with HOST buffers: umpcUpdate, torque clip, rigid-body step
+ * (the batched twin of uprightmpc2.py:139-151).  Outputs may alias the inputs. */
+int umpcBatchEnvStep(UmpcBatch *b, float *uquad, float *accdes, float *p_next, float *R_next, float *dq_next,
+                     const float *p0, const float *R0, const float *dq0, const float *pdes, const float *dpdes,
+                     const float *sdes, const float *actualT0);
 /* same with DEVICE pointers in the same [B][k] layout, asynchronous on the batch's stream */
 int umpcBatchUpdateDev(UmpcBatch *b, float *uquad, float *accdes, const float *p0, const float *R0, const float *dq0,
                        const float *pdes, const float *dpdes, const float *sdes, const float *actualT0);
@@ -174,6 +179,9 @@ int umpcBatchSync(UmpcBatch *b);
 void *umpcBatchDevPtr(UmpcBatch *b, const char *name);
 /* CUDA-event time (ms) of the last kernel sequence launched by the Update or Rollout calls */
 float umpcBatchLastKernelMs(UmpcBatch *b);
+/* CUDA events on the batch's stream around any sequence of calls: Start records, StopMs records + waits */
+int umpcBatchTimerStart(UmpcBatch *b);
+float umpcBatchTimerStopMs(UmpcBatch *b);
 /* launch configuration knobs (threads per block) for tuning/benchmarks */
 int umpcBatchSetLaunch(UmpcBatch *b, int threads_per_block);
 /* FP32 FMA-pipe peak of the device, measured with a register-resident FFMA loop (TFLOP/s) */

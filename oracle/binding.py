@@ -283,3 +283,47 @@ def rollout(lib, par, ctrl, ic, cfg, task=TASK_HELIX, tp=(0.0, 0.0, 0.1, 0.0), w
     lib.orc_rollout(par, ctrl, wl, int(wlmode), _p(icv), _p(cfg), int(task), _p(_d(tp, 4)),
                     _p(y) if log else nul, _p(u) if log else nul, _p(pd) if log else nul, _p(fin), _p(met))
     return dict(y=y, u=u, pdes=pd, final=fin, err=met[0], eff=met[1], nsolve=int(met[2]), u4sum=met[3])
+
+
+# ---- timed CPU baseline (bench.py cpu_baseline / --impl reference) ---------------------------------
+def _cpu_worker(args):
+    kind, nenv, nsteps, ics, seed = args
+    import time
+    if kind == "reference":
+        lib = C.CDLL(os.path.join(REF_DIR, "libref_umpc_f32_fast.so"))
+    else:
+        lib = C.CDLL(os.path.join(HERE, "liboracle_f32.so"))
+    lib.orc_batch_steps.restype = C.c_long
+    lib.orc_batch_steps.argtypes = [C.c_int, C.c_int, DP, DP, DP, C.c_int, dbl, dbl]
+    a = _d([UMPC_DEFAULTS[k] for k in ARG_ORDER])
+    Ib = _d(UMPC_DEFAULTS["Ib"])
+    ics = np.ascontiguousarray(ics, dtype=np.float64)
+    t0 = time.perf_counter()
+    n = lib.orc_batch_steps(int(nenv), int(nsteps), _p(ics), _p(a), _p(Ib), int(UMPC_DEFAULTS["maxIter"]), 0.2, 100.0)
+    return n, time.perf_counter() - t0, ics
+
+
+def cpu_baseline_kind():
+    return "reference" if os.path.exists(os.path.join(REF_DIR, "libref_umpc_f32_fast.so")) else "port"
+
+
+def cpu_env_steps(ics18, nsteps, procs):
+    """Advance the envs in ics18 (n x 18: p, R col-major, dq) nsteps closed-loop steps (hover, MPC every
+    step) on `procs` host processes (one per core: the reference's OSQP workspace is a process global,
+    template/uprightmpc2/workspace.c:2620, so threads cannot share it).  Returns (env_steps, seconds, kind)
+    with seconds = wall time of the slowest worker."""
+    import multiprocessing as mp
+    import time
+    kind = cpu_baseline_kind()
+    ics18 = np.asarray(ics18, dtype=np.float64).reshape(-1, 18)
+    chunks = [c for c in np.array_split(ics18, procs) if len(c)]
+    jobs = [(kind, len(c), nsteps, c, i) for i, c in enumerate(chunks)]
+    t0 = time.perf_counter()
+    if len(jobs) == 1:
+        res = [_cpu_worker(jobs[0])]
+    else:
+        with mp.get_context("fork").Pool(len(jobs)) as pool:
+            res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    done = sum(r[0] for r in res)
+    return done, max(r[1] for r in res), wall, kind

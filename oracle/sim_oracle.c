@@ -203,3 +203,80 @@ void orc_rollout(void *par, void *ctrl, void *wl, int wlmode, const double *ic, 
   }
   metrics[0] = err / nt; metrics[1] = eff / nt; metrics[2] = nsolve; metrics[3] = u4sum;
 }
+
+/* ---- batched CPU driver for bench.py's cpu_baseline / --impl reference legs -----------------------
+ * nenv environments advanced nsteps plant steps each, hover task, MPC every step (hlInterval=None),
+ * one core.  ref build: the reference's umpcUpdate with its process-global OSQP workspace, so each
+ * env's solver state is swapped in/out with ref_ctx_load/save (oracle/ref_glue.c) around the call.
+ * oracle build: one umpc_state_t per env.  ics: nenv x 18 (p, R col-major, dq), updated in place.
+ * Returns the number of env-steps done. */
+#ifdef SIM_USE_REF
+int ref_ctx_floats(void);
+void ref_ctx_save(float *buf);
+void ref_ctx_load(const float *buf);
+#include <stdlib.h>
+long orc_batch_steps(int nenv, int nsteps, double *ics, const double *args11, const double *Ib, int maxIter,
+                     double dtsim, double taulim) {
+  int nf = ref_ctx_floats(), e, k, i;
+  float *ctx = (float *)malloc((size_t)nf * nenv * sizeof(float));
+  UprightMPC_t *ups = (UprightMPC_t *)malloc(sizeof(UprightMPC_t) * nenv);
+  float fIb[3] = {(float)Ib[0], (float)Ib[1], (float)Ib[2]};
+  long done = 0;
+  for (e = 0; e < nenv; ++e) {
+    umpcInit(&ups[e], (float)args11[0], (float)args11[1], (float)args11[2], (float)args11[3], (float)args11[4],
+             (float)args11[5], (float)args11[6], (float)args11[7], (float)args11[8], (float)args11[9],
+             (float)args11[10], fIb, maxIter);
+    ref_ctx_save(ctx + (size_t)e * nf); /* all envs start from the generated workspace + warm start 0 */
+  }
+  for (k = 0; k < nsteps; ++k)
+    for (e = 0; e < nenv; ++e) {
+      double *s = ics + (size_t)e * 18;
+      float fu[3], fa[6], fp[3], fR[9], fdq[6], fpd[3] = {0, 0, 0}, fdp[3] = {0, 0, 0}, fs[3] = {0, 0, 1};
+      real p[3], R[9], dq[6], uq[3], rIb[3];
+      for (i = 0; i < 3; ++i) { fp[i] = (float)s[i]; p[i] = s[i]; rIb[i] = Ib[i]; }
+      for (i = 0; i < 9; ++i) { fR[i] = (float)s[3 + i]; R[i] = s[3 + i]; }
+      for (i = 0; i < 6; ++i) { fdq[i] = (float)s[12 + i]; dq[i] = s[12 + i]; }
+      ref_ctx_load(ctx + (size_t)e * nf);
+      umpcUpdate(&ups[e], fu, fa, fp, fR, fdq, fpd, fdp, fs, -1.0f);
+      ref_ctx_save(ctx + (size_t)e * nf);
+      for (i = 0; i < 3; ++i) uq[i] = fu[i];
+      for (i = 1; i < 3; ++i) uq[i] = uq[i] < -taulim ? -taulim : (uq[i] > taulim ? taulim : uq[i]);
+      dyn_step(p, R, dq, uq, dtsim, rIb, args11[1]);
+      for (i = 0; i < 3; ++i) s[i] = p[i];
+      for (i = 0; i < 9; ++i) s[3 + i] = R[i];
+      for (i = 0; i < 6; ++i) s[12 + i] = dq[i];
+      ++done;
+    }
+  free(ctx); free(ups);
+  return done;
+}
+#else
+#include <stdlib.h>
+void orc_umpc_init(umpc_par_t *par, umpc_state_t *st, const double *a11, const double *Ib, int maxIter);
+long orc_batch_steps(int nenv, int nsteps, double *ics, const double *args11, const double *Ib, int maxIter,
+                     double dtsim, double taulim) {
+  umpc_par_t par;
+  umpc_state_t *sts = (umpc_state_t *)malloc(sizeof(umpc_state_t) * nenv);
+  int e, k, i;
+  long done = 0;
+  double pd[3] = {0, 0, 0}, sd[3] = {0, 0, 1};
+  for (e = 0; e < nenv; ++e) orc_umpc_init(&par, &sts[e], args11, Ib, maxIter);
+  for (k = 0; k < nsteps; ++k)
+    for (e = 0; e < nenv; ++e) {
+      double *s = ics + (size_t)e * 18, uqd[3], acc[6];
+      real p[3], R[9], dq[6], uq[3], rIb[3];
+      orc_umpc_update(&par, &sts[e], uqd, acc, s, s + 3, s + 12, pd, pd, sd, -1.0);
+      for (i = 0; i < 3; ++i) { p[i] = (real)s[i]; rIb[i] = (real)Ib[i]; uq[i] = (real)uqd[i]; }
+      for (i = 0; i < 9; ++i) R[i] = (real)s[3 + i];
+      for (i = 0; i < 6; ++i) dq[i] = (real)s[12 + i];
+      for (i = 1; i < 3; ++i) uq[i] = uq[i] < (real)-taulim ? (real)-taulim : (uq[i] > (real)taulim ? (real)taulim : uq[i]);
+      dyn_step(p, R, dq, uq, (real)dtsim, rIb, (real)args11[1]);
+      for (i = 0; i < 3; ++i) s[i] = p[i];
+      for (i = 0; i < 9; ++i) s[3 + i] = R[i];
+      for (i = 0; i < 6; ++i) s[12 + i] = dq[i];
+      ++done;
+    }
+  free(sts);
+  return done;
+}
+#endif

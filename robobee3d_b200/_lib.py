@@ -54,9 +54,9 @@ EXPORTS = [
     "umpcInit", "umpcUpdate", "umpcS", "umpcGetInfo", "umpcGetSolution", "umpcFree",
     "wlConInit", "wlConUpdate", "wlconS", "wlControllerUpdate", "wlControllerUpdateW", "wlControllerReset",
     "umpcBatchDefaults", "umpcLastError", "umpcBatchCreate", "umpcBatchDestroy", "umpcBatchSize", "umpcBatchReset",
-    "umpcBatchUpdate", "umpcBatchUpdateDev", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
+    "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
     "umpcBatchGetState", "umpcBatchRollout", "umpcBatchGetMetrics", "umpcBatchReduceMetrics", "umpcBatchSetLog",
-    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchLastKernelMs", "umpcBatchSetLaunch",
+    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch",
     "umpcMeasureFp32Peak",
 ]
 
@@ -81,6 +81,7 @@ def load():
     vp = C.c_void_p
     L.umpcBatchUpdate.argtypes = [vp] + [vp] * 9
     L.umpcBatchUpdateDev.argtypes = [vp] + [vp] * 9
+    L.umpcBatchEnvStep.argtypes = [vp] + [vp] * 12
     L.umpcBatchGetSolve.argtypes = [vp] + [vp] * 8
     L.umpcBatchGetQPData.argtypes = [vp, vp]
     L.umpcBatchSetState.argtypes = [vp] + [vp] * 5
@@ -95,6 +96,9 @@ def load():
     L.umpcBatchDevPtr.restype = C.c_void_p
     L.umpcBatchLastKernelMs.argtypes = [vp]
     L.umpcBatchLastKernelMs.restype = C.c_float
+    L.umpcBatchTimerStart.argtypes = [vp]
+    L.umpcBatchTimerStopMs.argtypes = [vp]
+    L.umpcBatchTimerStopMs.restype = C.c_float
     L.umpcBatchSetLaunch.argtypes = [vp, C.c_int]
     L.umpcMeasureFp32Peak.argtypes = [C.c_int, C.c_int]
     L.umpcMeasureFp32Peak.restype = C.c_double

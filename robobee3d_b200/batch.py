@@ -106,6 +106,13 @@ class BatchUMPC:
                                             ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchUpdate")
         return uquad, accdes
 
+    def env_step_raw(self, uquad, accdes, p, Rc, dq, pdes, dpdes, sdes, actualT0=None):
+        """One closed-loop env-step with HOST buffers in the C-ABI layout (numpy or pinned torch tensors):
+        controller update, torque clip, rigid-body step; p, Rc, dq are overwritten with the next state."""
+        ptr = lambda a: None if a is None else C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        _lib.check(self.lib.umpcBatchEnvStep(self.h, ptr(uquad), ptr(accdes), ptr(p), ptr(Rc), ptr(dq), ptr(p), ptr(Rc), ptr(dq),
+                                             ptr(pdes), ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchEnvStep")
+
     def update_dev(self, uquad, accdes, p0, R0c, dq0, pdes, dpdes, sdes, actualT0=None):
         """torch CUDA tensors (float32, contiguous, [B,k]); asynchronous on the batch's stream."""
         ptr = lambda a: None if a is None else C.c_void_p(a.data_ptr())
@@ -155,6 +162,12 @@ class BatchUMPC:
 
     def sync(self):
         _lib.check(self.lib.umpcBatchSync(self.h), "umpcBatchSync")
+
+    def timer_start(self):
+        _lib.check(self.lib.umpcBatchTimerStart(self.h), "umpcBatchTimerStart")
+
+    def timer_stop_ms(self):
+        return float(self.lib.umpcBatchTimerStopMs(self.h))
 
     def last_kernel_ms(self):
         return float(self.lib.umpcBatchLastKernelMs(self.h))

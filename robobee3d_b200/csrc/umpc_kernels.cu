@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(160, 1)
 umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
                    float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
                    const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
-                   const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata) {
+                   const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata,
+                   float* __restrict__ p_next, float* __restrict__ R_next, float* __restrict__ dq_next) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= s.B) return;
   float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
@@ -134,6 +135,18 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
   for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; s.uq[(size_t)i * s.B + e] = uq[i]; }
 #pragma unroll
   for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; s.acc[(size_t)i * s.B + e] = acc[i]; }
+  if (p_next) {
+    // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
+    uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
+    uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
+    sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) p_next[(size_t)e * 3 + i] = p[i];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R_next[(size_t)e * 9 + i] = R[i];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dq_next[(size_t)e * 6 + i] = dq[i];
+  }
 }
 
 // ---- kernel 2: fused closed loop (uprightmpc2.py:87-159) -------------------------------------
@@ -353,7 +366,7 @@ extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
 struct UmpcBatch {
   int B = 0, device = 0, tpb = 128;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
   bool timed = false;
   UmpcBatchParams bp;
   KernelParams kp;
@@ -363,6 +376,7 @@ struct UmpcBatch {
   size_t slab_floats = 0;
   // staging ([B][k] layout of the C-ABI)
   float *d_in = nullptr, *d_out = nullptr;  // in: 28 floats/env, out: 9 floats/env
+  float* d_next = nullptr;                  // next plant state of umpcBatchEnvStep: 18 floats/env
   // rollout schedule (host-evaluated in double like numpy, uprightmpc2.py:118,136,145)
   long long step = 0;
   double thl = 0.0;
@@ -502,7 +516,7 @@ extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   if (!b) return;
   cudaSetDevice(b->device);
   cudaStreamSynchronize(b->stream);
-  cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums);
+  cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums); cudaFree(b->d_next);
   cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
   cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
   cudaStreamDestroy(b->stream);
@@ -515,6 +529,22 @@ extern "C" int umpcBatchSync(UmpcBatch* b) {
   CK(cudaStreamSynchronize(b->stream));
   return UMPC_OK;
 }
+// CUDA events on the batch's own stream bracketing any sequence of calls (bench.py's timed region)
+extern "C" int umpcBatchTimerStart(UmpcBatch* b) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  if (!b->tev0) { CK(cudaEventCreate(&b->tev0)); CK(cudaEventCreate(&b->tev1)); }
+  CK(cudaEventRecord(b->tev0, b->stream));
+  return UMPC_OK;
+}
+extern "C" float umpcBatchTimerStopMs(UmpcBatch* b) {
+  if (!b || !b->tev0) return -1.0f;
+  if (cudaEventRecord(b->tev1, b->stream) != cudaSuccess) return -1.0f;
+  if (cudaEventSynchronize(b->tev1) != cudaSuccess) return -1.0f;
+  float ms = -1.0f;
+  cudaEventElapsedTime(&ms, b->tev0, b->tev1);
+  return ms;
+}
 extern "C" float umpcBatchLastKernelMs(UmpcBatch* b) {
   if (!b || !b->timed) return -1.0f;
   float ms = -1.0f;
@@ -524,11 +554,12 @@ extern "C" float umpcBatchLastKernelMs(UmpcBatch* b) {
 }
 
 static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0, const float* dq0,
-                         const float* pdes, const float* dpdes, const float* sdes, const float* aT0) {
+                         const float* pdes, const float* dpdes, const float* sdes, const float* aT0,
+                         float* pn = nullptr, float* Rn = nullptr, float* dqn = nullptr) {
   const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
   umpc_update_kernel<<<grid, tpb, smem_bytes(tpb), b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes,
-                                                                 aT0, b->have_qpdata ? 1 : 0);
+                                                                 aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);
   CK(cudaGetLastError());
   CK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;
@@ -563,6 +594,41 @@ extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const 
   if (rc) return rc;
   CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaMemcpyAsync(accdes, dacc, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+// umpcUpdate + torque clip + quadrotorNLDyn for B environments with HOST buffers: the batched twin of
+//   uquad, accdes = mdl.update(p, Rb, dq, pdes, dpdes, sdes); p, Rb, dq = quadrotorNLDyn(p, Rb, dq, uquad, dtsim)
+// (uprightmpc2.py:139-151).  p_next/R_next/dq_next may alias p0/R0/dq0.
+extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float* p_next, float* R_next, float* dq_next,
+                                const float* p0, const float* R0, const float* dq0, const float* pdes, const float* dpdes,
+                                const float* sdes, const float* actualT0) {
+  if (!b || !uquad || !accdes || !p_next || !R_next || !dq_next || !p0 || !R0 || !dq0 || !pdes || !dpdes || !sdes) {
+    g_err = "umpcBatchEnvStep: NULL argument";
+    return UMPC_ERR_ARG;
+  }
+  CK(cudaSetDevice(b->device));
+  const size_t B = b->B;
+  if (!b->d_next) CK(cudaMalloc(&b->d_next, (size_t)18 * B * sizeof(float)));
+  float* d = b->d_in;
+  float *dp = d, *dR = dp + 3 * B, *ddq = dR + 9 * B, *dpd = ddq + 6 * B, *ddp = dpd + 3 * B, *dsd = ddp + 3 * B, *daT = dsd + 3 * B;
+  CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dpd, pdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
+  if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
+  float *duq = b->d_out, *dacc = duq + 3 * B;
+  float *dpn = b->d_next, *dRn = dpn + 3 * B, *ddqn = dRn + 9 * B;
+  int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr, dpn, dRn, ddqn);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaMemcpyAsync(accdes, dacc, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaMemcpyAsync(p_next, dpn, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaMemcpyAsync(R_next, dRn, 9 * B * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaMemcpyAsync(dq_next, ddqn, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   return UMPC_OK;
 }
