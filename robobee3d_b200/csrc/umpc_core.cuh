@@ -66,6 +66,16 @@ struct UmpcAVals {
   float abs_dt, abs_dtT0, abs_ds0, abs_ds1, abs_ds2, abs_db0, abs_db1, abs_db2, abs_db3, abs_db4, abs_db5;
 };
 
+// reciprocal / reciprocal square root: MUFU approximations (1-2 ulp) on the device instead of the
+// IEEE division + sqrt slow paths; the host build (tests/hostcheck) keeps the exact forms.
+#if defined(__CUDA_ARCH__)
+#define UMPC_RCP(x) __fdividef(1.0f, (x))
+#define UMPC_RSQRT(x) rsqrtf(x)
+#else
+#define UMPC_RCP(x) (1.0f / (x))
+#define UMPC_RSQRT(x) (1.0f / sqrtf(x))
+#endif
+
 #include "umpc_gen.cuh"
 
 UMPC_HD float umpc_limit_scaling(float v) {
@@ -168,6 +178,9 @@ struct UmpcInfo {
 //   L(n) n<167, Di(k) k<45 : factor of K      aW(i) i<36 : alpha * W_i of the equality rows
 //   Sg(j) j<45 : sigma / D_j^2                Lo(i) i<36 : l0 (== u0) of the equality rows
 //   Vf(i) i<36 : first-iteration fix-up (see below)
+// Reads are L(n)/Di(k)/aW(i)/Sg(j)/Lo(i)/Vf(i), writes setL(n,v) ... ; begin_iteration(it) is called at
+// the top of every ADMM pass (the CUDA store ties its loads to `it` so that the compiler cannot treat
+// the loop-invariant scratch as 300 registers' worth of hoisted values and spill them).
 // Per-env persistent state (IO; global memory, SoA): OSQP's scaled iterates xs/zs/ys (the
 // warm start, never rescaled), the last D, E (E of the thrust rows decides their
 // constraint type on the next call: bounds are scaled with the OLD E before the
@@ -202,7 +215,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
 #pragma unroll
-    for (int i = 0; i < UMPC_NEQ; ++i) st.Lo(i) = qp.lo[i];
+    for (int i = 0; i < UMPC_NEQ; ++i) st.setLo(i, qp.lo[i]);
   }
   // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
   float W3[3], Wi3[3];
@@ -231,10 +244,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       for (int j = 0; j < UMPC_NX; ++j) {
         const float pc = c * umpc_px(par, j) * D[j] * D[j];
         const float nj = fmaxf(pc, cn[j] * D[j]);
-        D[j] *= 1.0f / sqrtf(umpc_limit_scaling(nj));
+        D[j] *= UMPC_RSQRT(umpc_limit_scaling(nj));
       }
 #pragma unroll
-      for (int i = 0; i < UMPC_NC; ++i) E[i] *= 1.0f / sqrtf(umpc_limit_scaling(rn[i] * E[i]));
+      for (int i = 0; i < UMPC_NC; ++i) E[i] *= UMPC_RSQRT(umpc_limit_scaling(rn[i] * E[i]));
       // cost normalisation (scaling.c:100-131)
       float psum = 0.0f, nq = 0.0f;
 #pragma unroll
@@ -249,15 +262,15 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       float ct = psum * (1.0f / UMPC_NX);
       ct = fmaxf(ct, umpc_limit_scaling(nq));
       ct = umpc_limit_scaling(ct);
-      c *= 1.0f / ct;
+      c *= UMPC_RCP(ct);
     }
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
     {
       float G[UMPC_NX], W[UMPC_NC];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float sg = par.sigma / (D[j] * D[j]);
-        st.Sg(j) = sg;
+        const float sg = par.sigma * UMPC_RCP(D[j] * D[j]);
+        st.setSg(j, sg);
         G[j] = c * umpc_px(par, j) + sg;
         io.st_D(j, D[j]);
       }
@@ -271,18 +284,18 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       // ---- warm start -> hatted coordinates (x D, z / E, y E) ----------------------------
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) {
-        const float zh = io.ld_zs(i) / E[i], yh = io.ld_ys(i) * E[i];
+        const float zh = io.ld_zs(i) * UMPC_RCP(E[i]), yh = io.ld_ys(i) * E[i];
         const float lo = umpc_lo_eq(par, i, st.Lo(i));
         v[i] = W[i] * zh - yh;
-        st.Vf(i) = (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh;
-        st.aW(i) = alpha * W[i];
+        st.setVf(i, (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh);
+        st.setaW(i, alpha * W[i]);
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        z3[k] = io.ld_zs(UMPC_NEQ + k) / E[UMPC_NEQ + k];
+        z3[k] = io.ld_zs(UMPC_NEQ + k) * UMPC_RCP(E[UMPC_NEQ + k]);
         y3[k] = io.ld_ys(UMPC_NEQ + k) * E[UMPC_NEQ + k];
         W3[k] = W[UMPC_NEQ + k];
-        Wi3[k] = 1.0f / W3[k];
+        Wi3[k] = UMPC_RCP(W3[k]);
       }
     }
 #pragma unroll
@@ -294,6 +307,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   for (int i = 0; i < 6; ++i) { cyd[i] = c * yd[i]; cdyd[i] = c * dyd[i]; }
   const int niter = par.max_iter < 1 ? 1 : par.max_iter;
   for (int it = 0; it < niter; ++it) {
+    st.begin_iteration(it);  // scratch reads of this pass must not be hoisted out of the loop
     float r[UMPC_NX];
     {
       float vv[UMPC_NC];
@@ -367,7 +381,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
       }
     }
-    const float cinv = 1.0f / c;
+    const float cinv = UMPC_RCP(c);
     dua *= cinv;
     info.iter = niter; info.pri_res = pri; info.dua_res = dua;
     const float ep = par.eps_abs + par.eps_rel * fmaxf(nz, nAx);
@@ -385,7 +399,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     for (int j = 0; j < UMPC_NX; ++j) {
       const float sx = bad ? nanv : xs[j];
       io.st_solx(j, sx);
-      io.st_xs(j, bad ? 0.0f : xs[j] / io.ld_D(j));
+      io.st_xs(j, bad ? 0.0f : xs[j] * UMPC_RCP(io.ld_D(j)));
       if (j >= 18 && j < 24) solx_dy1[j - 18] = sx;
       if (j >= 36 && j < 39) solx_u[j - 36] = sx;
     }
@@ -394,7 +408,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       const float e = io.ld_E(i);
       io.st_soly(i, bad ? nanv : ys[i] * cinv);
       io.st_zs(i, bad ? 0.0f : zs[i] * e);
-      io.st_ys(i, bad ? 0.0f : ys[i] / e);
+      io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));
     }
   }
   // ---- extraction (uprightmpc2.c:252-269) ---------------------------------------------------

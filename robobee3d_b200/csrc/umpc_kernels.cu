@@ -30,23 +30,52 @@
 #define SM_OFF_LO (SM_OFF_SG + UMPC_NX)
 #define SM_FLOATS_PER_THREAD (SM_OFF_LO + 18)
 
+template <int TPB>
 struct SmemStore {
-  float* base;  // &smem[threadIdx.x]
-  int nt;       // blockDim.x
-  float* vf;    // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
+  static constexpr uint32_t nt4 = TPB * 4u;  // byte stride between entries: compile-time -> immediate offsets
+  uint32_t sbase;  // shared-window byte address of &smem[threadIdx.x]
+  int tok;         // current ADMM pass: an input of every load so that loads stay inside the loop
+  float* vf;       // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
   int B;
-  __device__ __forceinline__ float& L(int n) { return base[(SM_OFF_L + n) * nt]; }
-  __device__ __forceinline__ float L(int n) const { return base[(SM_OFF_L + n) * nt]; }
-  __device__ __forceinline__ float& Di(int k) { return base[(SM_OFF_DI + k) * nt]; }
-  __device__ __forceinline__ float Di(int k) const { return base[(SM_OFF_DI + k) * nt]; }
-  __device__ __forceinline__ float& aW(int i) { return base[(SM_OFF_AW + i) * nt]; }
-  __device__ __forceinline__ float& Sg(int j) { return base[(SM_OFF_SG + j) * nt]; }
-  // only rows 0..5 and 18..29 have run-time bounds (umpc_lo_eq); the others get a dummy slot
-  __device__ __forceinline__ float& Lo(int i) {
-    return (i < 6) ? base[(SM_OFF_LO + i) * nt] : (i >= 18 && i < 30) ? base[(SM_OFF_LO + i - 12) * nt] : dummy;
+  __device__ __forceinline__ void init(float* smem_thread, float* vf_, int B_) {
+    sbase = (uint32_t)__cvta_generic_to_shared(smem_thread);
+    tok = 0; vf = vf_; B = B_;
   }
-  __device__ __forceinline__ float& Vf(int i) { return vf[(size_t)i * B]; }
-  float dummy;
+  __device__ __forceinline__ void begin_iteration(int it) { tok = it; }
+  // non-volatile asm: free to be scheduled anywhere in the pass, but not CSE'd across passes (tok differs)
+  __device__ __forceinline__ float ld(int e, int t) const {
+    float v;
+    asm("ld.shared.f32 %0, [%1]; // %2" : "=f"(v) : "r"(sbase + (uint32_t)e * nt4), "r"(t));
+    return v;
+  }
+  __device__ __forceinline__ void stf(int e, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)e * nt4), "f"(v) : "memory");
+  }
+  __device__ __forceinline__ float L(int n) const { return ld(SM_OFF_L + n, tok); }
+  // second read of the same entries in the backward substitution: a different token, so that the
+  // compiler re-loads instead of keeping 167 forward values alive (and spilling them)
+  __device__ __forceinline__ float Lb(int n) const {
+    float v;  // volatile: ptxas would otherwise merge it with the forward read of the same address
+    asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"(sbase + (uint32_t)(SM_OFF_L + n) * nt4));
+    return v;
+  }
+  __device__ __forceinline__ float Di(int k) const { return ld(SM_OFF_DI + k, tok); }
+  __device__ __forceinline__ float aW(int i) const { return ld(SM_OFF_AW + i, tok); }
+  __device__ __forceinline__ float Sg(int j) const { return ld(SM_OFF_SG + j, tok); }
+  // only rows 0..5 and 18..29 have run-time bounds (umpc_lo_eq); the others are compile-time constants
+  __device__ __forceinline__ float Lo(int i) const {
+    return (i < 6) ? ld(SM_OFF_LO + i, tok) : (i >= 18 && i < 30) ? ld(SM_OFF_LO + i - 12, tok) : 0.0f;
+  }
+  __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
+  __device__ __forceinline__ void setL(int n, float v) { stf(SM_OFF_L + n, v); }
+  __device__ __forceinline__ void setDi(int k, float v) { stf(SM_OFF_DI + k, v); }
+  __device__ __forceinline__ void setaW(int i, float v) { stf(SM_OFF_AW + i, v); }
+  __device__ __forceinline__ void setSg(int j, float v) { stf(SM_OFF_SG + j, v); }
+  __device__ __forceinline__ void setLo(int i, float v) {
+    if (i < 6) stf(SM_OFF_LO + i, v);
+    else if (i >= 18 && i < 30) stf(SM_OFF_LO + i - 12, v);
+  }
+  __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
 
 // ---- global SoA state -------------------------------------------------------------------------
@@ -96,7 +125,8 @@ __device__ __forceinline__ void store_info(const DevState& s, int e, const UmpcI
 }
 
 // ---- kernel 1: one umpcUpdate per environment, inputs in [B][k] (the C-ABI's layout) ---------
-__global__ void __launch_bounds__(160, 1)
+template <int TPB>
+__global__ void __launch_bounds__(TPB, 1)
 umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
                    float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
                    const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
@@ -123,8 +153,8 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
     umpc_qpdata(kp.mpc, qp, out);
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
   }
-  SmemStore st;
-  st.base = g_smem + threadIdx.x; st.nt = blockDim.x; st.vf = s.soly + e; st.B = s.B;
+  SmemStore<TPB> st;
+  st.init(g_smem + threadIdx.x, s.soly + e, s.B);
   GlobIO io(s, e);
   float uq[3], acc[6];
   UmpcInfo info;
@@ -203,7 +233,8 @@ __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp,
   s.actualT0[e] = w0[2] / sim.mb;
 }
 
-__global__ void __launch_bounds__(160, 1)
+template <int TPB>
+__global__ void __launch_bounds__(TPB, 1)
 umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
                     const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
                     const float* __restrict__ tvals, LogBuf lg) {
@@ -222,8 +253,8 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
   const int task = s.task[e];
   float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
   float pert_done = s.metrics[4 * B + e];
-  SmemStore st;
-  st.base = g_smem + threadIdx.x; st.nt = blockDim.x; st.vf = s.soly + e; st.B = s.B;
+  SmemStore<TPB> st;
+  st.init(g_smem + threadIdx.x, s.soly + e, s.B);
   GlobIO io(s, e);
   for (int k = 0; k < nsteps; ++k) {
     const float t = tvals[k];
@@ -503,9 +534,11 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   CK(cudaMalloc(&b->d_in, (size_t)28 * nenv * sizeof(float)));
   CK(cudaMalloc(&b->d_out, (size_t)10 * nenv * sizeof(float)));
   CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
-  CK(cudaFuncSetAttribute(umpc_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(160)));
-  CK(cudaFuncSetAttribute(umpc_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(160)));
-  b->tpb = nenv < 128 ? 32 : 128;
+#define UMPC_SET_SMEM(T)                                                                                              \
+  CK(cudaFuncSetAttribute(umpc_update_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(T)));      \
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(T)));
+  UMPC_SET_SMEM(32) UMPC_SET_SMEM(64) UMPC_SET_SMEM(96) UMPC_SET_SMEM(128) UMPC_SET_SMEM(160)
+  b->tpb = 32;  // 5 independent 1-warp CTAs per SM (smem-limited): best measured, smooth tail
   int rc = reset_state(b);
   if (rc) return rc;
   *out = b;
@@ -558,8 +591,15 @@ static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float*
                          float* pn = nullptr, float* Rn = nullptr, float* dqn = nullptr) {
   const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
-  umpc_update_kernel<<<grid, tpb, smem_bytes(tpb), b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes,
-                                                                 aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);
+#define UMPC_LAUNCH_UPDATE(T)                                                                                        \
+  case T:                                                                                                           \
+    umpc_update_kernel<T><<<grid, T, smem_bytes(T), b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, \
+                                                                 sdes, aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);      \
+    break;
+  switch (tpb) {
+    UMPC_LAUNCH_UPDATE(32) UMPC_LAUNCH_UPDATE(64) UMPC_LAUNCH_UPDATE(96) UMPC_LAUNCH_UPDATE(128) UMPC_LAUNCH_UPDATE(160)
+    default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
+  }
   CK(cudaGetLastError());
   CK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;
@@ -739,8 +779,15 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
   CK(cudaStreamSynchronize(b->stream));
   const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
-  umpc_rollout_kernel<<<grid, tpb, smem_bytes(tpb), b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t,
-                                                                  b->lg);
+#define UMPC_LAUNCH_ROLLOUT(T)                                                                                   \
+  case T:                                                                                                       \
+    umpc_rollout_kernel<T><<<grid, T, smem_bytes(T), b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, \
+                                                                  b->d_t, b->lg);                                \
+    break;
+  switch (tpb) {
+    UMPC_LAUNCH_ROLLOUT(32) UMPC_LAUNCH_ROLLOUT(64) UMPC_LAUNCH_ROLLOUT(96) UMPC_LAUNCH_ROLLOUT(128) UMPC_LAUNCH_ROLLOUT(160)
+    default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
+  }
   CK(cudaGetLastError());
   CK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;

@@ -7,14 +7,20 @@
 
 struct HostStore {
   float l[UMPC_GEN_NNZL], di[UMPC_NX], aw[UMPC_NEQ], sg[UMPC_NX], lo[UMPC_NEQ], vf[UMPC_NEQ];
-  float& L(int n) { return l[n]; }
   float L(int n) const { return l[n]; }
-  float& Di(int k) { return di[k]; }
+  float Lb(int n) const { return l[n]; }
   float Di(int k) const { return di[k]; }
-  float& aW(int i) { return aw[i]; }
-  float& Sg(int j) { return sg[j]; }
-  float& Lo(int i) { return lo[i]; }
-  float& Vf(int i) { return vf[i]; }
+  float aW(int i) const { return aw[i]; }
+  float Sg(int j) const { return sg[j]; }
+  float Lo(int i) const { return lo[i]; }
+  float Vf(int i) const { return vf[i]; }
+  void setL(int n, float v) { l[n] = v; }
+  void setDi(int k, float v) { di[k] = v; }
+  void setaW(int i, float v) { aw[i] = v; }
+  void setSg(int j, float v) { sg[j] = v; }
+  void setLo(int i, float v) { lo[i] = v; }
+  void setVf(int i, float v) { vf[i] = v; }
+  void begin_iteration(int) {}
 };
 
 struct HostIO {

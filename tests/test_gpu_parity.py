@@ -48,14 +48,15 @@ def test_batch_update_matches_reference_golden(cuda_required, gold):
         l, u, q, Px, Ax = b.qpdata()
         # call 0 has identical inputs -> float32 rounding only; later calls build on T0 += x[36] of the
         # previous (tolerance-level) solution, so T0-dependent entries inherit that tolerance
-        tol_data = TOL_QPDATA if c == 0 else 1e-4
+        tol_data = TOL_QPDATA if c == 0 else 1e-3
         for name, got in (("l", l), ("u", u), ("q", q), ("Px", Px), ("Ax", Ax)):
             _close_rel(got, gold[name][:, c], tol_data, "call %d QP data %s" % (c, name))
         s = b.solve_info(full=True)
         _close_rel(s["x"], gold["x"][:, c], TOL_X_REL, "call %d x" % c)
         _close_rel(s["y"], gold["y"][:, c], TOL_Y_REL, "call %d y" % c)
-        _close_rel(s["D"], gold["D"][:, c], 1e-4, "call %d D" % c)
-        _close_rel(s["E"], gold["E"][:, c], 1e-4, "call %d E" % c)
+        tol_sc = 1e-4 if c == 0 else 2e-3  # D, E depend on T0 (dt*T0 entries) and on c through q
+        _close_rel(s["D"], gold["D"][:, c], tol_sc, "call %d D" % c)
+        _close_rel(s["E"], gold["E"][:, c], tol_sc, "call %d E" % c)
         assert (np.abs(uq - gold["uquad"][:, c]).max(axis=1) <= TOL_X_REL * np.maximum(1.0, np.abs(gold["x"][:, c]).max(axis=1))).all()
         # accdes = (x[18:24] - dq0)/dt: same absolute tolerance as x, divided by dt
         assert np.abs(acc - gold["accdes"][:, c]).max() <= TOL_X_REL * np.abs(gold["x"][:, c]).max() / 5.0
@@ -127,7 +128,7 @@ def test_dropin_single_controller_matches_golden(cuda_required, gold):
             assert np.abs(uq - gold["uquad"][e, c]).max() <= TOL_X_REL * max(1.0, np.abs(gold["x"][e, c]).max())
             l, u, q = up.vectors()
             Px, Ax, idx = up.matrices()
-            tol_data = TOL_QPDATA if c == 0 else 1e-4
+            tol_data = TOL_QPDATA if c == 0 else 1e-3
             _close_rel(l, gold["l"][e, c], tol_data, "l"); _close_rel(u, gold["u"][e, c], tol_data, "u")
             _close_rel(q, gold["q"][e, c], tol_data, "q"); _close_rel(Ax, gold["Ax"][e, c], tol_data, "Ax")
             assert np.array_equal(idx, gold["Ax_idx"])
