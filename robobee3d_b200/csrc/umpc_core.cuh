@@ -205,8 +205,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
                          const float sdes[3], float actualT0, float& T0, UmpcInfo& info) {
   const float dt = par.dt;
   if (actualT0 >= 0.0f) T0 = actualT0;
+  io.prefetch_warm_start();  // xs/zs/ys are needed only after Ruiz + factor: start pulling them into L2 now
   UmpcAVals a;
   float yd[6], dyd[6], lo_thr, hi_thr;
+  float qp_lo[18];  // run-time equality bounds: rows 0..5 and 18..29
   {
     UmpcQP qp;
     umpc_build(par, qp, p0, R0, dq0, pdes, dpdes, sdes, T0);
@@ -216,6 +218,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
 #pragma unroll
     for (int i = 0; i < UMPC_NEQ; ++i) st.setLo(i, qp.lo[i]);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) qp_lo[i] = qp.lo[i];
+#pragma unroll
+    for (int i = 18; i < 30; ++i) qp_lo[i - 12] = qp.lo[i];
   }
   // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
   float W3[3], Wi3[3];
@@ -282,24 +288,35 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       }
       umpc_gen_factor(G, W, a, st);
       // ---- warm start -> hatted coordinates (x D, z / E, y E) ----------------------------
+      // All global loads are issued before any global store (the compiler cannot move a load across
+      // a store that might alias, and a load -> store -> load chain exposes the full memory latency
+      // once per element).
+      float zs0[UMPC_NC], ys0[UMPC_NC];
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) { zs0[i] = io.ld_zs(i); ys0[i] = io.ld_ys(i); }
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) xs[j] = io.ld_xs(j);
+      float vfix[UMPC_NEQ];
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) {
-        const float zh = io.ld_zs(i) * UMPC_RCP(E[i]), yh = io.ld_ys(i) * E[i];
-        const float lo = umpc_lo_eq(par, i, st.Lo(i));
+        const float zh = zs0[i] * UMPC_RCP(E[i]), yh = ys0[i] * E[i];
+        const float lo = umpc_lo_eq(par, i, qp_lo[i < 6 ? i : (i >= 18 && i < 30 ? i - 12 : 0)]);
         v[i] = W[i] * zh - yh;
-        st.setVf(i, (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh);
+        vfix[i] = (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh;
         st.setaW(i, alpha * W[i]);
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        z3[k] = io.ld_zs(UMPC_NEQ + k) * UMPC_RCP(E[UMPC_NEQ + k]);
-        y3[k] = io.ld_ys(UMPC_NEQ + k) * E[UMPC_NEQ + k];
+        z3[k] = zs0[UMPC_NEQ + k] * UMPC_RCP(E[UMPC_NEQ + k]);
+        y3[k] = ys0[UMPC_NEQ + k] * E[UMPC_NEQ + k];
         W3[k] = W[UMPC_NEQ + k];
         Wi3[k] = UMPC_RCP(W3[k]);
       }
-    }
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) xs[j] = io.ld_xs(j) * D[j];
+      for (int j = 0; j < UMPC_NX; ++j) xs[j] *= D[j];
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) st.setVf(i, vfix[i]);
+    }
   }
   // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
   float cyd[6], cdyd[6];  // c * ydes, c * dydes  ->  -c q0_j = Px_j * (c yd)
@@ -395,17 +412,22 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     // ---- store_solution (auxil.c:527-562); warm start back to OSQP's scaled coordinates ---
     const bool bad = status == UMPC_ST_NON_CVX;
     const float nanv = nanf("");
+    float Dl[UMPC_NX], El[UMPC_NC];  // loads first, stores after (see the warm-start note)
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) Dl[j] = io.ld_D(j);
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) El[i] = io.ld_E(i);
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) {
       const float sx = bad ? nanv : xs[j];
       io.st_solx(j, sx);
-      io.st_xs(j, bad ? 0.0f : xs[j] * UMPC_RCP(io.ld_D(j)));
+      io.st_xs(j, bad ? 0.0f : xs[j] * UMPC_RCP(Dl[j]));
       if (j >= 18 && j < 24) solx_dy1[j - 18] = sx;
       if (j >= 36 && j < 39) solx_u[j - 36] = sx;
     }
 #pragma unroll
     for (int i = 0; i < UMPC_NC; ++i) {
-      const float e = io.ld_E(i);
+      const float e = El[i];
       io.st_soly(i, bad ? nanv : ys[i] * cinv);
       io.st_zs(i, bad ? 0.0f : zs[i] * e);
       io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));

@@ -96,6 +96,15 @@ struct GlobIO {
   const DevState& s;
   int e;
   __device__ __forceinline__ GlobIO(const DevState& s_, int e_) : s(s_), e(e_) {}
+  __device__ __forceinline__ void prefetch_warm_start() const {
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) asm volatile("prefetch.global.L2 [%0];" ::"l"(s.xs + (size_t)j * s.B + e));
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(s.zs + (size_t)i * s.B + e));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(s.ys + (size_t)i * s.B + e));
+    }
+  }
   __device__ __forceinline__ float ld_xs(int j) const { return s.xs[(size_t)j * s.B + e]; }
   __device__ __forceinline__ float ld_zs(int i) const { return s.zs[(size_t)i * s.B + e]; }
   __device__ __forceinline__ float ld_ys(int i) const { return s.ys[(size_t)i * s.B + e]; }

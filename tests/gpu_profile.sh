@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu: launch list + full capture of the rollout kernel (after the same command ran clean)
 mkdir -p gpurun_out
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e"
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e --tpb ${TPB:-32}"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 $CMD > gpurun_out/plain2.log 2>&1 &&

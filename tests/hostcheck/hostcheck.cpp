@@ -25,6 +25,7 @@ struct HostStore {
 
 struct HostIO {
   float xs[UMPC_NX], zs[UMPC_NC], ys[UMPC_NC], D[UMPC_NX], E[UMPC_NC], solx[UMPC_NX], soly[UMPC_NC];
+  void prefetch_warm_start() const {}
   float ld_xs(int j) const { return xs[j]; }
   float ld_zs(int i) const { return zs[i]; }
   float ld_ys(int i) const { return ys[i]; }
