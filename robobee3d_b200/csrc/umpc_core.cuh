@@ -176,7 +176,9 @@ struct UmpcInfo {
 // Per-QP scratch the iterations re-read every pass (ST).  The kernels back it with
 // shared memory laid out [entry][thread]; the host check backs it with arrays.
 //   L(n) n<167, Di(k) k<45 : factor of K      aW(i) i<36 : alpha * W_i of the equality rows
-//   Sg(j) j<45 : sigma / D_j^2                Lo(i) i<36 : l0 (== u0) of the equality rows
+//   Sg2(q) q<23 : sigma / D_j^2 in pairs       Lo(i) i<36 : l0 (== u0) of the equality rows
+//   (the store may keep the Sg pairs in reduced precision: the term is ~1e-6 of the diagonal; and may
+//    declare kAWInRegs / kLoInRegs to keep alpha*W / the bounds in registers instead of the scratch)
 //   Vf(i) i<36 : first-iteration fix-up (see below)
 // Reads are L(n)/Di(k)/aW(i)/Sg(j)/Lo(i)/Vf(i), writes setL(n,v) ... ; begin_iteration(it) is called at
 // the top of every ADMM pass (the CUDA store ties its loads to `it` so that the compiler cannot treat
@@ -217,7 +219,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
 #pragma unroll
-    for (int i = 0; i < UMPC_NEQ; ++i) st.setLo(i, qp.lo[i]);
+    for (int i = 0; i < UMPC_NEQ; ++i) if (!ST::kLoInRegs) st.setLo(i, qp.lo[i]);
 #pragma unroll
     for (int i = 0; i < 6; ++i) qp_lo[i] = qp.lo[i];
 #pragma unroll
@@ -237,6 +239,9 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
   float c = 1.0f;
   float xs[UMPC_NX], v[UMPC_NEQ], z3[3], y3[3];
+  float aWr[ST::kAWInRegs ? UMPC_NEQ : 1];  // alpha*W of the equality rows when the store keeps them in registers
+#define UMPC_AW(i) (ST::kAWInRegs ? aWr[ST::kAWInRegs ? (i) : 0] : st.aW(i))
+#define UMPC_LO(i) umpc_lo_eq(par, (i), ST::kLoInRegs ? qp_lo[(i) < 6 ? (i) : ((i) >= 18 && (i) < 30 ? (i) - 12 : 0)] : st.Lo(i))
   {
     float D[UMPC_NX], E[UMPC_NC];
 #pragma unroll
@@ -272,11 +277,12 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
     {
-      float G[UMPC_NX], W[UMPC_NC];
+      float G[UMPC_NX], W[UMPC_NC], sgv[UMPC_NX + 1];
+      sgv[UMPC_NX] = 0.0f;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
         const float sg = par.sigma * UMPC_RCP(D[j] * D[j]);
-        st.setSg(j, sg);
+        sgv[j] = sg;
         G[j] = c * umpc_px(par, j) + sg;
         io.st_D(j, D[j]);
       }
@@ -286,6 +292,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         W[i] = rho_i * E[i] * E[i];
         io.st_E(i, E[i]);
       }
+#pragma unroll
+      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setSg2(q, sgv[2 * q], sgv[2 * q + 1]);
       umpc_gen_factor(G, W, a, st);
       // ---- warm start -> hatted coordinates (x D, z / E, y E) ----------------------------
       // All global loads are issued before any global store (the compiler cannot move a load across
@@ -303,7 +311,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         const float lo = umpc_lo_eq(par, i, qp_lo[i < 6 ? i : (i >= 18 && i < 30 ? i - 12 : 0)]);
         v[i] = W[i] * zh - yh;
         vfix[i] = (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh;
-        st.setaW(i, alpha * W[i]);
+        if (ST::kAWInRegs) aWr[i] = alpha * W[i]; else st.setaW(i, alpha * W[i]);
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
@@ -333,10 +341,18 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int k = 0; k < 3; ++k) vv[UMPC_NEQ + k] = W3[k] * z3[k] - y3[k];
 #pragma unroll
-      for (int j = 0; j < UMPC_NX; ++j) {
-        float rj = st.Sg(j) * xs[j];
-        if (j < 36) rj += umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]);
-        r[j] = rj;
+      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
+        float s0, s1;
+        st.Sg2(q, s0, s1);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int j = 2 * q + h;
+          if (j < UMPC_NX) {
+            float rj = (h ? s1 : s0) * xs[j];
+            if (j < 36) rj += umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]);
+            r[j] = rj;
+          }
+        }
       }
       umpc_gen_ATv_add(r, vv, a);
     }
@@ -349,7 +365,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       float zt[UMPC_NC];
       umpc_gen_Ax(zt, r, a);
 #pragma unroll
-      for (int i = 0; i < UMPC_NEQ; ++i) v[i] -= st.aW(i) * (zt[i] - umpc_lo_eq(par, i, st.Lo(i)));
+      for (int i = 0; i < UMPC_NEQ; ++i) v[i] -= UMPC_AW(i) * (zt[i] - UMPC_LO(i));
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const float t = alpha * zt[UMPC_NEQ + k] + oma * z3[k];
@@ -368,8 +384,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     const float ialpha = 1.0f / alpha;
 #pragma unroll
     for (int i = 0; i < UMPC_NEQ; ++i) {
-      zs[i] = umpc_lo_eq(par, i, st.Lo(i));
-      ys[i] = st.aW(i) * (zs[i] * ialpha) - v[i];
+      zs[i] = UMPC_LO(i);
+      ys[i] = UMPC_AW(i) * (zs[i] * ialpha) - v[i];
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) { zs[UMPC_NEQ + k] = z3[k]; ys[UMPC_NEQ + k] = y3[k]; }

@@ -12,6 +12,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <string>
 #include <vector>
 #include <map>
@@ -25,10 +26,8 @@
 // ---- shared-memory store: [entry][thread] ---------------------------------------------------
 #define SM_OFF_L 0
 #define SM_OFF_DI (SM_OFF_L + UMPC_GEN_NNZL)
-#define SM_OFF_AW (SM_OFF_DI + UMPC_NX)
-#define SM_OFF_SG (SM_OFF_AW + UMPC_NEQ)
-#define SM_OFF_LO (SM_OFF_SG + UMPC_NX)
-#define SM_FLOATS_PER_THREAD (SM_OFF_LO + 18)
+#define SM_OFF_SG (SM_OFF_DI + UMPC_NX)             // 23 words: sigma/D^2 as bf16 pairs
+#define SM_FLOATS_PER_THREAD (SM_OFF_SG + 23)       // 235 floats = 940 B per QP -> 7 one-warp CTAs per SM
 
 template <int TPB>
 struct SmemStore {
@@ -60,21 +59,27 @@ struct SmemStore {
     return v;
   }
   __device__ __forceinline__ float Di(int k) const { return ld(SM_OFF_DI + k, tok); }
-  __device__ __forceinline__ float aW(int i) const { return ld(SM_OFF_AW + i, tok); }
-  __device__ __forceinline__ float Sg(int j) const { return ld(SM_OFF_SG + j, tok); }
-  // only rows 0..5 and 18..29 have run-time bounds (umpc_lo_eq); the others are compile-time constants
-  __device__ __forceinline__ float Lo(int i) const {
-    return (i < 6) ? ld(SM_OFF_LO + i, tok) : (i >= 18 && i < 30) ? ld(SM_OFF_LO + i - 12, tok) : 0.0f;
+  // alpha*W (36) and the 18 run-time bounds stay in registers: the scratch then fits 7 CTAs per SM
+  static constexpr bool kAWInRegs = true, kLoInRegs = true;
+  __device__ __forceinline__ float aW(int) const { return 0.0f; }
+  __device__ __forceinline__ float Lo(int) const { return 0.0f; }
+  __device__ __forceinline__ void setaW(int, float) {}
+  __device__ __forceinline__ void setLo(int, float) {}
+  // sigma/D_j^2 enters the right-hand side as a ~1e-6-relative term: bf16 (8 significant bits, full
+  // float range) is ample, and halves its footprint
+  __device__ __forceinline__ void Sg2(int q, float& a, float& b) const {
+    uint32_t w;
+    asm("ld.shared.b32 %0, [%1]; // %2" : "=r"(w) : "r"(sbase + (uint32_t)(SM_OFF_SG + q) * nt4), "r"(tok));
+    a = __uint_as_float(w << 16);
+    b = __uint_as_float(w & 0xffff0000u);
+  }
+  __device__ __forceinline__ void setSg2(int q, float a, float b) {
+    const uint32_t w = (__float_as_uint(a) >> 16) | (__float_as_uint(b) & 0xffff0000u);
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(sbase + (uint32_t)(SM_OFF_SG + q) * nt4), "r"(w) : "memory");
   }
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
   __device__ __forceinline__ void setL(int n, float v) { stf(SM_OFF_L + n, v); }
   __device__ __forceinline__ void setDi(int k, float v) { stf(SM_OFF_DI + k, v); }
-  __device__ __forceinline__ void setaW(int i, float v) { stf(SM_OFF_AW + i, v); }
-  __device__ __forceinline__ void setSg(int j, float v) { stf(SM_OFF_SG + j, v); }
-  __device__ __forceinline__ void setLo(int i, float v) {
-    if (i < 6) stf(SM_OFF_LO + i, v);
-    else if (i >= 18 && i < 30) stf(SM_OFF_LO + i - 12, v);
-  }
   __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
 
@@ -135,7 +140,7 @@ __device__ __forceinline__ void store_info(const DevState& s, int e, const UmpcI
 
 // ---- kernel 1: one umpcUpdate per environment, inputs in [B][k] (the C-ABI's layout) ---------
 template <int TPB>
-__global__ void __launch_bounds__(TPB, 1)
+__global__ void __launch_bounds__(TPB, 224 / TPB)
 umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
                    float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
                    const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
@@ -243,7 +248,7 @@ __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp,
 }
 
 template <int TPB>
-__global__ void __launch_bounds__(TPB, 1)
+__global__ void __launch_bounds__(TPB, 224 / TPB)
 umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
                     const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
                     const float* __restrict__ tvals, LogBuf lg) {
@@ -478,7 +483,12 @@ static void fill_kernel_params(UmpcBatch* b) {
   w.max_iter = 40; w.check_termination = p.wlqpCheckTermination; w.scaling_iters = 10;
 }
 
-static size_t smem_bytes(int tpb) { return (size_t)SM_FLOATS_PER_THREAD * tpb * sizeof(float); }
+static size_t smem_bytes(int tpb) {
+  // UMPC_SMEM_PAD_FLOATS (debug/tuning only): extra floats per thread, to study occupancy sensitivity
+  static int pad = -1;
+  if (pad < 0) { const char* e = getenv("UMPC_SMEM_PAD_FLOATS"); pad = e ? atoi(e) : 0; }
+  return (size_t)(SM_FLOATS_PER_THREAD + pad) * tpb * sizeof(float);
+}
 
 extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
   if (!b || tpb < 32 || tpb > 160 || (tpb % 32)) { g_err = "threads_per_block must be 32..160, multiple of 32"; return UMPC_ERR_ARG; }
@@ -544,8 +554,8 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   CK(cudaMalloc(&b->d_out, (size_t)10 * nenv * sizeof(float)));
   CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
 #define UMPC_SET_SMEM(T)                                                                                              \
-  CK(cudaFuncSetAttribute(umpc_update_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(T)));      \
-  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(T)));
+  CK(cudaFuncSetAttribute(umpc_update_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));      \
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
   UMPC_SET_SMEM(32) UMPC_SET_SMEM(64) UMPC_SET_SMEM(96) UMPC_SET_SMEM(128) UMPC_SET_SMEM(160)
   b->tpb = 32;  // 5 independent 1-warp CTAs per SM (smem-limited): best measured, smooth tail
   int rc = reset_state(b);
