@@ -127,6 +127,9 @@ typedef struct {
   int wlMode;
   float wl_u0[4], wl_umin[4], wl_umax[4], wl_dumax[4], wl_Qw[6], wl_controlRate, wl_popts[90];
   int wlqpCheckTermination; /* 25 = C (wlqp.c), 0 = C++ (wlqp.cpp:63-66) */
+  /* 1: the task's initialPos has integer dtype, as in controlTest (uprightmpc2.py:94-104 builds p with
+   * np.array([0, 0, 0]); flight_tasks' in-place `posdes[i] += x` then truncates pdes toward zero). 0: float. */
+  int intInitialPos;
 } UmpcBatchParams;
 
 void umpcBatchDefaults(UmpcBatchParams *par);

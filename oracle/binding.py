@@ -259,9 +259,10 @@ class RefWLQP:
 
 
 def rollout_cfg(tend=500.0, dtsim=0.2, hlInterval=None, taulim=100.0, tpert=None,
-                Ib=(3333.0, 3333.0, 1000.0), g=9.81e-3, mb=100.0):
+                Ib=(3333.0, 3333.0, 1000.0), g=9.81e-3, mb=100.0, intInitialPos=False):
+    """intInitialPos: controlTest's integer-dtype initialPos (uprightmpc2.py:94-104) truncates pdes toward zero."""
     return _d([tend, dtsim, -1.0 if hlInterval is None else hlInterval, taulim,
-               -1.0 if tpert is None else tpert, Ib[0], Ib[1], Ib[2], g, mb])
+               -1.0 if tpert is None else tpert, Ib[0], Ib[1], Ib[2], g, mb, 1.0 if intInitialPos else 0.0])
 
 
 def control_test_ic():

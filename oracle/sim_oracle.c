@@ -42,29 +42,39 @@ static double clipd(double v, double lo, double hi) { return v < lo ? lo : (v > 
 
 /* tp: helix (trajAmp, trajFreq, dz, useY) | straightAcc (tduration, vdes) |
  *     flip (tstart, tend) | perch (tend, trotstart, trotend, vdes) */
-void orc_task(int task, double t, const double *p_init, const double *tp, double *pdes, double *dpdes, double *sdes) {
+/* int_pos: controlTest builds its initial position with np.array([0, 0, 0]) (uprightmpc2.py:94-104), an int64
+ * array; flight_tasks.py copies it (np.copy keeps the dtype) and `posdes[i] += x` stores the float sum back
+ * into the int array, i.e. truncates toward zero.  dpdes / sdes are float arrays and unaffected. */
+static double trunc_if(double v, int int_pos) { return int_pos ? trunc(v) : v; }
+
+void orc_task_q(int task, double t, const double *p_init, const double *tp, int int_pos, double *pdes, double *dpdes,
+                double *sdes) {
   int i;
   for (i = 0; i < 3; ++i) { pdes[i] = p_init[i]; dpdes[i] = 0; }
   sdes[0] = 0; sdes[1] = 0; sdes[2] = 1;
   if (task == TASK_HELIX) {
     double amp = tp[0], omg = 2 * PI_D * tp[1] * 1e-3;
-    pdes[0] += amp * sin(omg * t); dpdes[0] = amp * omg * cos(omg * t);
-    if (tp[3] != 0) { pdes[1] += amp * (1 - cos(omg * t)); dpdes[1] = amp * omg * sin(omg * t); }
-    if (amp > 1e-3) { pdes[2] += tp[2] * t; dpdes[2] = tp[2]; }
+    pdes[0] = trunc_if(pdes[0] + amp * sin(omg * t), int_pos); dpdes[0] = amp * omg * cos(omg * t);
+    if (tp[3] != 0) { pdes[1] = trunc_if(pdes[1] + amp * (1 - cos(omg * t)), int_pos); dpdes[1] = amp * omg * sin(omg * t); }
+    if (amp > 1e-3) { pdes[2] = trunc_if(pdes[2] + tp[2] * t, int_pos); dpdes[2] = tp[2]; }
   } else if (task == TASK_STRAIGHT) {
     dpdes[0] = t < tp[0] ? tp[1] : 0;
-    pdes[0] += tp[1] * clipd(t, 0, tp[0]);
+    pdes[0] = trunc_if(pdes[0] + tp[1] * clipd(t, 0, tp[0]), int_pos);
   } else if (task == TASK_FLIP) {
     double ph = clipd((t - tp[0]) / tp[1], 0, 1);
     sdes[0] = -sin(ph * 2 * PI_D); sdes[1] = 0; sdes[2] = cos(ph * 2 * PI_D);
   } else if (task == TASK_PERCH) {
-    pdes[0] += tp[3] * clipd(t, 0, tp[0]);
+    pdes[0] = trunc_if(pdes[0] + tp[3] * clipd(t, 0, tp[0]), int_pos);
     dpdes[0] = t < tp[0] ? tp[3] : 0;
     if (t < tp[0]) {
       double ph = clipd((t - tp[2]) / tp[1], 0, 1);
       sdes[0] = -sin(ph * PI_D); sdes[1] = 0; sdes[2] = cos(ph * PI_D);
     } else { sdes[0] = -1; sdes[1] = 0; sdes[2] = 0; }
   }
+}
+
+void orc_task(int task, double t, const double *p_init, const double *tp, double *pdes, double *dpdes, double *sdes) {
+  orc_task_q(task, t, p_init, tp, 0, pdes, dpdes, sdes);
 }
 
 /* one explicit-Euler step; R column-major; expm(skew(w) dt) by Rodrigues */
@@ -127,7 +137,7 @@ int orc_schedule(double dtsim, double hlInterval, int nt, unsigned char *fire) {
  *   oracle build : umpc_par_t*, umpc_state_t*, wl_t*   (wlmode 0 none, 1 WLCon, 2 WLQP)
  *   ref build    : UprightMPC_t* (par ignored), WLCon_t* (wlmode 0/1)
  * ic = p[3], R[9 col-major], dq[6].  cfg = tend, dtsim, hlInterval(<0 None), taulim,
- * tpert(<0 None), Ib[3], g, mb.  Outputs: log_y (nt x 12: p, R[:,2], dq), log_u (nt x 3),
+ * tpert(<0 None), Ib[3], g, mb, int_pos (integer-dtype initialPos quirk of controlTest).  Outputs: log_y (nt x 12: p, R[:,2], dq), log_u (nt x 3),
  * log_pdes (nt x 3) may be NULL; metrics = err, eff (logMetric), n_solves, sum|u4| (wl) .
  */
 void orc_rollout(void *par, void *ctrl, void *wl, int wlmode, const double *ic, const double *cfg,
@@ -135,6 +145,7 @@ void orc_rollout(void *par, void *ctrl, void *wl, int wlmode, const double *ic, 
                  double *final_state, double *metrics) {
   double tend = cfg[0], dtsim = cfg[1], hl = cfg[2], taulim = cfg[3], tpert = cfg[4];
   double Ibd[3] = {cfg[5], cfg[6], cfg[7]}, g = cfg[8], mb = cfg[9];
+  int int_pos = cfg[10] != 0;
   int nt = orc_rollout_nt(tend, dtsim), ti, i, nsolve = 0;
   real p[3], R[9], dq[6], Ib[3], uq[3] = {0, 0, 0};
   double p_init[3], thl = 0, err = 0, eff = 0, actualT0 = -1.0, u4sum = 0;
@@ -143,7 +154,7 @@ void orc_rollout(void *par, void *ctrl, void *wl, int wlmode, const double *ic, 
   for (i = 0; i < 6; ++i) dq[i] = (real)ic[12 + i];
   for (ti = 0; ti < nt; ++ti) {
     double t = ti * dtsim, pdes[3], dpdes[3], sdes[3];
-    orc_task(task, t, p_init, tp, pdes, dpdes, sdes);
+    orc_task_q(task, t, p_init, tp, int_pos, pdes, dpdes, sdes);
     if (task == TASK_HELIX && tpert >= 0 && t > tpert) { dq[1] += 2; tpert = -1; }
     if (hl < 0 || t - thl > hl) {
       double uqd[3], acc[6], pd[3], Rd[9], dqd[6];

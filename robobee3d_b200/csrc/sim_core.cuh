@@ -28,6 +28,7 @@ struct SimParams {
   float g;           // 9.81e-3 mm/ms^2
   float mb;          // body mass for the WL glue (ca6dynamics.py:5-10)
   int wl_mode;       // 0: none, 1: WLCon projected gradient, 2: true WLQP
+  int int_pos;       // 1: initialPos has integer dtype as in controlTest (see sim_task)
 };
 
 UMPC_HD float sim_clip(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
@@ -35,39 +36,46 @@ UMPC_HD float sim_clip(float v, float lo, float hi) { return v < lo ? lo : (v > 
 // (pdes, dpdes, sdes) of the task at time t (ms).  tp[4]:
 //   helix (trajAmp, trajFreq, dz, useY) | straightAcc (tduration, vdes) |
 //   flip (tstart, tend) | perch (tend, trotstart, trotend, vdes)   -- flight_tasks.py argument order
-UMPC_HD void sim_task(int task, float t, const float p_init[3], const float tp[4], float pdes[3], float dpdes[3],
-                      float sdes[3]) {
-  const float PI_F = 3.14159265358979323846f;
+// Evaluated in double like numpy does (it runs once per MPC update, next to ~9e4 float instructions).
+// int_pos reproduces controlTest's integer-dtype initialPos (uprightmpc2.py:94-104: p = np.array([0, 0, 0]) is an
+// int64 array, flight_tasks copies it and `posdes[i] += x` then stores the float sum back into the int array,
+// i.e. truncates it toward zero); dpdes and sdes are float arrays in the reference and are not affected.
+UMPC_HD double sim_trunc_if(double v, int int_pos) { return int_pos ? trunc(v) : v; }
+
+UMPC_HD void sim_task(int task, double t, const float p_init[3], const float tp[4], int int_pos, float pdes[3],
+                      float dpdes[3], float sdes[3]) {
+  const double PI_D = 3.14159265358979323846;
+  double pd[3], dpd[3] = {0.0, 0.0, 0.0}, sd[3] = {0.0, 0.0, 1.0};
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { pdes[i] = p_init[i]; dpdes[i] = 0.0f; }
-  sdes[0] = 0.0f; sdes[1] = 0.0f; sdes[2] = 1.0f;
+  for (int i = 0; i < 3; ++i) pd[i] = (double)p_init[i];
   if (task == SIM_TASK_HELIX) {
-    const float amp = tp[0], omg = 2.0f * PI_F * tp[1] * 1e-3f;
-    float sn, cs;
-#if defined(__CUDA_ARCH__)
-    sincosf(omg * t, &sn, &cs);
-#else
-    sn = sinf(omg * t); cs = cosf(omg * t);
-#endif
-    pdes[0] += amp * sn; dpdes[0] = amp * omg * cs;
-    if (tp[3] != 0.0f) { pdes[1] += amp * (1.0f - cs); dpdes[1] = amp * omg * sn; }
-    if (amp > 1e-3f) { pdes[2] += tp[2] * t; dpdes[2] = tp[2]; }
+    const double amp = (double)tp[0], omg = 2.0 * PI_D * (double)tp[1] * 1e-3;
+    const double sn = sin(omg * t), cs = cos(omg * t);
+    pd[0] = sim_trunc_if(pd[0] + amp * sn, int_pos); dpd[0] = amp * omg * cs;
+    if (tp[3] != 0.0f) { pd[1] = sim_trunc_if(pd[1] + amp * (1.0 - cs), int_pos); dpd[1] = amp * omg * sn; }
+    if (amp > 1e-3) { pd[2] = sim_trunc_if(pd[2] + (double)tp[2] * t, int_pos); dpd[2] = (double)tp[2]; }
   } else if (task == SIM_TASK_STRAIGHT) {
-    dpdes[0] = t < tp[0] ? tp[1] : 0.0f;
-    pdes[0] += tp[1] * sim_clip(t, 0.0f, tp[0]);
+    const double td = (double)tp[0], vd = (double)tp[1];
+    dpd[0] = t < td ? vd : 0.0;
+    pd[0] = sim_trunc_if(pd[0] + vd * (t < 0.0 ? 0.0 : (t > td ? td : t)), int_pos);
   } else if (task == SIM_TASK_FLIP) {
-    const float ph = sim_clip((t - tp[0]) / tp[1], 0.0f, 1.0f) * 2.0f * PI_F;
-    sdes[0] = -sinf(ph); sdes[1] = 0.0f; sdes[2] = cosf(ph);
+    double ph = (t - (double)tp[0]) / (double)tp[1];
+    ph = ph < 0.0 ? 0.0 : (ph > 1.0 ? 1.0 : ph);
+    sd[0] = -sin(ph * 2.0 * PI_D); sd[1] = 0.0; sd[2] = cos(ph * 2.0 * PI_D);
   } else if (task == SIM_TASK_PERCH) {
-    pdes[0] += tp[3] * sim_clip(t, 0.0f, tp[0]);
-    dpdes[0] = t < tp[0] ? tp[3] : 0.0f;
-    if (t < tp[0]) {
-      const float ph = sim_clip((t - tp[2]) / tp[1], 0.0f, 1.0f) * PI_F;
-      sdes[0] = -sinf(ph); sdes[1] = 0.0f; sdes[2] = cosf(ph);
+    const double te = (double)tp[0], vd = (double)tp[3];
+    pd[0] = sim_trunc_if(pd[0] + vd * (t < 0.0 ? 0.0 : (t > te ? te : t)), int_pos);
+    dpd[0] = t < te ? vd : 0.0;
+    if (t < te) {
+      double ph = (t - (double)tp[2]) / (double)tp[1];
+      ph = ph < 0.0 ? 0.0 : (ph > 1.0 ? 1.0 : ph);
+      sd[0] = -sin(ph * PI_D); sd[1] = 0.0; sd[2] = cos(ph * PI_D);
     } else {
-      sdes[0] = -1.0f; sdes[1] = 0.0f; sdes[2] = 0.0f;
+      sd[0] = -1.0; sd[1] = 0.0; sd[2] = 0.0;
     }
   }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { pdes[i] = (float)pd[i]; dpdes[i] = (float)dpd[i]; sdes[i] = (float)sd[i]; }
 }
 
 // One explicit-Euler step of the rigid body (genqp.py:24-41).  R column-major,

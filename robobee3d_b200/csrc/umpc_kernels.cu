@@ -251,7 +251,7 @@ template <int TPB>
 __global__ void __launch_bounds__(TPB, 224 / TPB)
 umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
                     const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
-                    const float* __restrict__ tvals, LogBuf lg) {
+                    const double* __restrict__ tvals, LogBuf lg) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= s.B) return;
   const size_t B = s.B;
@@ -271,13 +271,14 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
   st.init(g_smem + threadIdx.x, s.soly + e, s.B);
   GlobIO io(s, e);
   for (int k = 0; k < nsteps; ++k) {
-    const float t = tvals[k];
-    float pdes[3], dpdes[3], sdes[3];
-    sim_task(task, t, pinit, tp, pdes, dpdes, sdes);
-    if (task == SIM_TASK_HELIX && kp.sim.tpert >= 0.0f && t > kp.sim.tpert && pert_done == 0.0f) {
+    const double t = tvals[k];
+    if (task == SIM_TASK_HELIX && kp.sim.tpert >= 0.0f && t > (double)kp.sim.tpert && pert_done == 0.0f) {
       dq[1] += 2.0f; pert_done = 1.0f;
     }
     if (fire[k]) {
+      // the task's reference is consumed by the controller only: evaluate it when the MPC fires
+      float pdes[3], dpdes[3], sdes[3];
+      sim_task(task, t, pinit, tp, kp.sim.int_pos, pdes, dpdes, sdes);
       float acc[6], T0 = s.T0[e];
       const float aT0 = kp.sim.wl_mode ? s.actualT0[e] : -1.0f;
       UmpcInfo info;
@@ -426,7 +427,7 @@ struct UmpcBatch {
   long long step = 0;
   double thl = 0.0;
   uint8_t* d_fire = nullptr;
-  float* d_t = nullptr;
+  double* d_t = nullptr;
   int sched_cap = 0;
   double* d_sums = nullptr;
   LogBuf lg{-1, 0, nullptr, nullptr};
@@ -469,7 +470,7 @@ static void fill_kernel_params(UmpcBatch* b) {
   SimParams& sm = b->kp.sim;
   sm.dtsim = (float)p.dtsim; sm.hl_interval = (float)p.hlInterval; sm.taulim = p.taulim; sm.tpert = p.tpert;
   for (int i = 0; i < 3; ++i) sm.Ib[i] = p.Ib[i];
-  sm.g = p.g; sm.mb = p.mb; sm.wl_mode = p.wlMode;
+  sm.g = p.g; sm.mb = p.mb; sm.wl_mode = p.wlMode; sm.int_pos = p.intInitialPos;
   WlParams& w = b->wlp;
   memset(&w, 0, sizeof(w));
   memcpy(w.popts, p.wl_popts, sizeof(w.popts));
@@ -778,23 +779,23 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
     cudaFree(b->d_fire); cudaFree(b->d_t);
     b->sched_cap = nsteps < 4096 ? 4096 : nsteps;
     CK(cudaMalloc(&b->d_fire, b->sched_cap));
-    CK(cudaMalloc(&b->d_t, (size_t)b->sched_cap * sizeof(float)));
+    CK(cudaMalloc(&b->d_t, (size_t)b->sched_cap * sizeof(double)));
   } else {
     CK(cudaStreamSynchronize(b->stream));  // host staging vectors below are reused per call
   }
   // firing schedule in double, like numpy: t = ti*dtsim ; fire when hlInterval is None or t - thlPrev > hlInterval
   std::vector<uint8_t> fire(nsteps);
-  std::vector<float> tv(nsteps);
+  std::vector<double> tv(nsteps);
   const double dts = b->bp.dtsim, hl = b->bp.hlInterval;
   for (int k = 0; k < nsteps; ++k) {
     const double t = (double)(b->step + k) * dts;
     const bool f = hl < 0.0 || (t - b->thl > hl);
     if (f) b->thl = t;
     fire[k] = f ? 1 : 0;
-    tv[k] = (float)t;
+    tv[k] = t;
   }
   CK(cudaMemcpyAsync(b->d_fire, fire.data(), nsteps, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->d_t, tv.data(), (size_t)nsteps * sizeof(float), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->d_t, tv.data(), (size_t)nsteps * sizeof(double), cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));

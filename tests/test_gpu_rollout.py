@@ -147,3 +147,41 @@ def test_monte_carlo_rollout_properties(cuda_required):
     p2, R2, dq2, _ = b2.state()
     assert np.array_equal(p2, pf[lo:hi]) and np.array_equal(dq2, dqf[lo:hi])
     b.close(); b2.close()
+
+
+# ---- against the reference's OWN PYTHON LOOP (tests/golden/make_golden_pyloop.py) -----------------
+from test_oracle_vs_pyloop import RUNS as PY_RUNS  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(PY_RUNS))
+def test_rollout_matches_reference_python_loop(cuda_required, name):
+    """controlTest run by the reference's Python sources (flight_tasks, quadrotorNLDyn with scipy expm in float64,
+    the reference C controller) vs the fused CUDA rollout (float32 plant), incl. the integer-initialPos quirk."""
+    from robobee3d_b200.batch import BatchUMPC
+    g = np.load(os.path.join(GOLDEN, "pyloop_c1.npz"))
+    r = PY_RUNS[name]
+    nt = int(g[name + "_nt"])
+    B = 32
+    b = BatchUMPC(B, hlInterval=r["hl"], tpert=r.get("tpert"), intInitialPos=1)
+    if "ic" in r:
+        p, R, dq = (np.tile(np.asarray(a, float), (B,) + (1,) * np.ndim(a)) for a in r["ic"])
+    else:
+        p, R, dq = _ic(B)
+    b.set_state(p, R, dq, task=r["task"], tp=r["tp"])
+    b.set_log(5, nt)
+    b.rollout(nt)
+    y, u = b.get_log(nt)
+    y = y[::10]
+    gy = g[name + "_y"]
+    tol_p = max(TOL_TRAJ_P, 2e-3 * np.abs(gy[:, :3]).max())
+    if name in ("c_helixpert", "c_speed"):  # ill-conditioned flights, see test_oracle_vs_pyloop.py
+        k = 50 if name == "c_helixpert" else 8
+        assert np.abs(y[:k, :3] - gy[:k, :3]).max() <= tol_p
+        assert np.abs(y[:, :3] - gy[:, :3]).max() <= (10.0 if name == "c_helixpert" else 120.0)
+    else:
+        assert np.abs(y[:, :3] - gy[:, :3]).max() <= tol_p
+        assert np.abs(y[:, 3:6] - gy[:, 3:6]).max() <= 2 * TOL_TRAJ_S
+        gm = g[name + "_metrics"]
+        m = b.metrics()
+        assert abs(m["err"][5] / gm[0] - 1) < 2e-2 and abs(m["eff"][5] / gm[1] - 1) < 5e-2
+    b.close()

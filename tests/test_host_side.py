@@ -1,0 +1,126 @@
+"""CPU tests of the host side (no GPU, no compute calls into the CUDA library):
+  * the C-ABI library loads and exports every symbol include/umpc_b200.h declares;
+  * the product fails loudly (no CPU fallback) when no CUDA device is present;
+  * the generated device header is what the generator emits today;
+  * the device algorithm headers (robobee3d_b200/csrc/*.cuh are __host__ __device__), compiled for the host by
+    tests/hostcheck, reproduce the reference golden vectors -- a development aid that validates the kernel's
+    FORMULATION (reduced 45x45 system, un-scaled coordinates) before GPU time is spent.  The real parity
+    tests are the -m gpu ones, through the C-ABI on the device.
+"""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import util
+from util import GOLDEN, ROOT, TOL_X_REL, TOL_Y_REL, TOL_QPDATA
+
+HEADER = os.path.join(ROOT, "include", "umpc_b200.h")
+
+
+def _declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    names = re.findall(r"^\s*(?:const\s+)?(?:void|int|float|double|char)\s*\*?\s*(\w+)\s*\(", src, flags=re.M)
+    return sorted(set(names))
+
+
+def test_header_symbols_are_exported():
+    from robobee3d_b200 import _lib
+    decl = _declared_symbols()
+    assert len(decl) >= 35, decl
+    L = _lib.load()
+    missing = [s for s in decl if not hasattr(L, s)]
+    assert not missing, "libumpc_b200.so lacks %s" % missing
+    assert sorted(set(_lib.EXPORTS)) == decl, "robobee3d_b200/_lib.py EXPORTS out of sync with include/umpc_b200.h"
+    # struct layouts of the drop-in API (uprightmpc2.h:27-43, funapprox.h:18-43): sizes as the reference compiles them
+    assert C.sizeof(_lib.UprightMPC_t) == 4 * (3 + 27 + 6 + 18 + 39 + 39 + 45 + 45 + 48 + 48 + 2 + 6 + 1)
+    assert C.sizeof(_lib.FunApprox_t) == 4 * (1 + 1 + 4 + 16) and C.sizeof(_lib.WLCon_t) == 4 * (16 + 36) + 6 * 88
+
+
+def test_only_cuda_runtime_dependencies():
+    """the product library links the CUDA runtime and libc/libstdc++ only -- not torch, not the oracle"""
+    from robobee3d_b200 import _lib
+    out = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "torch" not in out
+    nm = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "orc_" not in nm and "osqp_" not in nm
+
+
+@pytest.mark.skipif(util.has_cuda(), reason="checks the no-GPU behaviour")
+def test_no_cpu_fallback_without_device():
+    from robobee3d_b200 import _lib, uprightmpc2py
+    from robobee3d_b200.batch import BatchUMPC
+    with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
+        BatchUMPC(4)
+    d = util.load_constants()["umpc_defaults"]
+    with pytest.raises(RuntimeError):
+        uprightmpc2py.UprightMPC2C(d["dt"], d["g"], d["TtoWmax"], d["ws"], d["wds"], d["wpr"], d["wpf"], d["wvr"], d["wvf"],
+                                   d["wthrust"], d["wmom"], d["Ib"], d["maxIter"])
+    # raw C-ABI: error code + message, outputs poisoned with NaN
+    L = _lib.load()
+    up = _lib.UprightMPC_t()
+    uq, acc = (C.c_float * 3)(), (C.c_float * 6)()
+    z3, R = (C.c_float * 3)(), (C.c_float * 9)(1, 0, 0, 0, 1, 0, 0, 0, 1)
+    z6 = (C.c_float * 6)()
+    rc = L.umpcUpdate(C.byref(up), uq, acc, z3, R, z6, z3, z3, z3, C.c_float(-1.0))
+    assert rc == 100 and np.isnan(uq[0]) and np.isnan(acc[0])
+
+
+def test_product_package_never_imports_oracle():
+    pkg = os.path.join(ROOT, "robobee3d_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+                assert "liboracle" not in src and "libref_" not in src and "binding" not in src, f
+
+
+def test_generated_header_is_current():
+    out = subprocess.run([sys.executable, "-m", "robobee3d_b200.codegen.gen_umpc"], capture_output=True, text=True, cwd=ROOT,
+                         check=True).stdout
+    cur = open(os.path.join(ROOT, "robobee3d_b200", "csrc", "umpc_gen.cuh")).read()
+    assert out == cur, "robobee3d_b200/csrc/umpc_gen.cuh is stale: re-run python -m robobee3d_b200.codegen.gen_umpc"
+
+
+def test_symbolic_structure():
+    """A has the reference's 111 non-zeros of which 48 change per update (uprightmpc2.h:25, workspace.c:154-427);
+    the reduced K's factor has the nnz the kernel's shared-memory layout assumes."""
+    from robobee3d_b200.codegen.gen_umpc import build
+    nx, nc, ent, rows, kent, perm, cols = build(3)
+    assert (nx, nc, len(ent)) == (45, 39, 111)
+    assert sum(1 for (_, _, k) in ent if k[0] != "c") == 48
+    assert sorted(perm) == list(range(45))
+    hdr = open(os.path.join(ROOT, "robobee3d_b200", "csrc", "umpc_gen.cuh")).read()
+    nnzl = int(re.search(r"#define UMPC_GEN_NNZL (\d+)", hdr).group(1))
+    assert nnzl == sum(len(c) for c in cols)
+
+
+def test_device_formulation_on_host_matches_reference_golden():
+    sys.path.insert(0, os.path.join(ROOT, "tests", "hostcheck"))
+    import hc
+    gold = np.load(os.path.join(GOLDEN, "umpc_seq.npz"))
+    d = util.load_constants()["umpc_defaults"]
+    B, ncall = gold["p"].shape[:2]
+    worst = 0.0
+    for e in range(B):
+        h = hc.HostUMPC(d)
+        for c in range(ncall):
+            uq, acc = h.update(gold["p"][e, c], gold["R"][e, c], gold["dq"][e, c], gold["pdes"][e, c], gold["dpdes"][e, c],
+                               gold["sdes"][e, c], float(gold["aT0"][e, c]))
+            o = h.get()
+            ex, ey = util.relerr(o["x"], gold["x"][e, c]), util.relerr(o["y"], gold["y"][e, c])
+            worst = max(worst, ex)
+            assert ex <= TOL_X_REL and ey <= TOL_Y_REL, (e, c, ex, ey)
+            assert util.relerr(o["D"], gold["D"][e, c]) <= (1e-4 if c == 0 else 2e-3)
+            assert util.relerr(o["E"], gold["E"][e, c]) <= (1e-4 if c == 0 else 2e-3)
+            # warm start kept in OSQP's scaled coordinates like the reference's workspace.x/z/y
+            assert util.relerr(o["xs"], gold["xs"][e, c]) <= 2 * TOL_X_REL
+            assert int(o["info"][0]) == 50
+            assert np.abs(uq - gold["uquad"][e, c]).max() <= TOL_X_REL * max(1.0, np.abs(gold["x"][e, c]).max())
+    print("hostcheck worst rel err vs reference C: %.2e" % worst)

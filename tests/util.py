@@ -67,3 +67,11 @@ def load_constants():
 def relerr(a, b):
     a, b = np.asarray(a, float), np.asarray(b, float)
     return np.abs(a - b).max() / max(1.0, np.abs(b).max())
+
+
+def has_cuda():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
