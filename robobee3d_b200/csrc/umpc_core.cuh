@@ -173,32 +173,47 @@ struct UmpcInfo {
   float pri_res, dua_res;
 };
 
-// Per-QP scratch the iterations re-read every pass (ST).  The kernels back it with
-// shared memory laid out [entry][thread]; the host check backs it with arrays.
-//   L(n) n<167, Di(k) k<45 : factor of K      aW(i) i<36 : alpha * W_i of the equality rows
-//   Sg2(q) q<23 : sigma / D_j^2 in pairs       Lo(i) i<36 : l0 (== u0) of the equality rows
-//   (the store may keep the Sg pairs in reduced precision: the term is ~1e-6 of the diagonal; and may
-//    declare kAWInRegs / kLoInRegs to keep alpha*W / the bounds in registers instead of the scratch)
-//   Vf(i) i<36 : first-iteration fix-up (see below)
-// Reads are L(n)/Di(k)/aW(i)/Sg(j)/Lo(i)/Vf(i), writes setL(n,v) ... ; begin_iteration(it) is called at
-// the top of every ADMM pass (the CUDA store ties its loads to `it` so that the compiler cannot treat
-// the loop-invariant scratch as 300 registers' worth of hoisted values and spill them).
-// Per-env persistent state (IO; global memory, SoA): OSQP's scaled iterates xs/zs/ys (the
-// warm start, never rescaled), the last D, E (E of the thrust rows decides their
-// constraint type on the next call: bounds are scaled with the OLD E before the
-// re-equilibration, osqp.c:784-832 + auxil.c:103-146), and the solution.
+// Per-QP scratch the iterations re-read every pass (ST).  The kernels back it with shared memory (and a few
+// registers), the host check backs it with arrays.
+//   L(n) / Lb(n) n<167 : factor of K (forward / backward read)     Di(k) k<45 : 1/d of the LDL'
+//   Sg2(q) q<23 : sigma / D_j^2 in pairs (the store may keep them in reduced precision: the term is ~1e-6 of
+//                 the diagonal, and it enters the iteration only through products with (xh - xt) and xh)
+//   Vf(j) j<45 : first-iteration fix-up of w (see below), global scratch
+// begin_iteration(it) is called at the top of every ADMM pass (the CUDA store ties its loads to `it` so that the
+// compiler cannot treat the loop-invariant scratch as 300 registers' worth of hoisted values and spill them).
+// Per-env persistent state (IO; global memory, SoA): OSQP's scaled iterates xs/zs/ys (the warm start, never
+// rescaled), the last D, E (E of the thrust rows decides their constraint type on the next call: bounds are
+// scaled with the OLD E before the re-equilibration, osqp.c:784-832 + auxil.c:103-146), and the solution.
 //
-// Equality rows (l == u).  After the first projection z_i == l_i exactly (proj.c:4-14), so
-// for those 36 rows only the combination the right-hand side needs is carried:
-//     v_i = W_i zh_i - yh_i ,   v_i+ = v_i - alpha W_i (zt_i - l_i)          (iterations >= 2)
-// and yh_i = W_i l_i - v_i is recovered at the end.  In the first iteration zh_i is the
-// stale warm start, which only changes the constant: v_i <- Vf_i before the same update,
-// Vf_i = (2 - alpha) W_i l_i - yh0_i - (1 - alpha) W_i zh0_i.
+// The iteration actually executed ("A-free" form).  For the 36 equality rows (l == u) z_i == l_i exactly after
+// the first projection (proj.c:4-14), so only v = W zh - yh matters there, and v enters the right-hand side
+// only through g = A_eq' v.  With K_eq = A_eq' W A_eq and b = A_eq' W l the v-update v+ = v - alpha W (A_eq xt - l)
+// becomes g+ = g - alpha (K_eq xt - b), and K_eq xt is available WITHOUT multiplying by A: K xt = r (the system
+// just solved) and K = G + K_eq + A_3' W_3 A_3 with G diagonal and A_3 the three unit thrust rows, so
+//     K_eq xt = r - G xt - A_3' W_3 A_3 xt .
+// Shifting the primal iterates by the open-loop roll-out xp (A_eq xp = l, zero inputs; umpc_gen_xp) removes b
+// and folds every constant of the right-hand side into the initial value of  w = g + c P0 (ydes - xp) - b :
+//     r   = S xh' + w  (+ W_3 z_3 - y_3 on the three thrust columns)            S = sigma D^-2, xh' = xh - xp
+//     xt' = K^-1 r                                                               (umpc_gen_solve)
+//     w  <- (1 - alpha) w + alpha c P0 xt' - alpha S (xh' - xt')  (+ alpha (W_3 xt' - (W_3 z_3 - y_3)) thrust cols)
+//     xh' <- xh' - alpha (xh' - xt') ;  thrust rows: the generic z/y update with clipping
+// i.e. per iteration one sparse LDL' solve and ~7 flops per variable: no product with A, no per-row state.
+// This is algebraically the iteration of auxil.c:164-228 (same iterates x, and z, y on the thrust rows; the
+// equality-row duals are recovered at the end from g by substitution, umpc_gen_v_from_g).  The stale warm
+// start z of the FIRST iteration (z_prev != l, and OSQP uses it in xz_tilde and in the relaxation) only changes
+// a constant: w is replaced by a second start vector Vf right after the first right-hand side is formed,
+//     w0 = kappa + A_eq'(W zh0 - yh0),   wf = kappa + A_eq'((2 - alpha) W l - yh0 - (1 - alpha) W zh0),
+//     kappa = c P0 (ydes - xp) - A_eq' W l ,   w1 = wf - alpha w0 + (rest of the update).
 UMPC_HD float umpc_lo_eq(const UmpcParams& par, int i, float stored) {
   // rows 6..17 are 0 and rows 30..35 are -dt*c0 (uprightmpc2.c:139-152): no load needed
   if (i >= 6 && i < 18) return 0.0f;
   if (i >= 30) return i == 32 ? par.dt * par.g : 0.0f;
   return stored;
+}
+
+// c * P0_j * ref_j : the constant part of -c q0 (q0 = -P0 .* [ydes x3, dydes x3, 0 x9], uprightmpc2.c:182-207)
+UMPC_HD float umpc_ref(const float (&yd)[6], const float (&dyd)[6], int j) {
+  return j < 18 ? yd[j % 6] : (j < 36 ? dyd[j % 6] : 0.0f);
 }
 
 template <class ST, class IO>
@@ -219,12 +234,11 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; }
 #pragma unroll
-    for (int i = 0; i < UMPC_NEQ; ++i) if (!ST::kLoInRegs) st.setLo(i, qp.lo[i]);
-#pragma unroll
     for (int i = 0; i < 6; ++i) qp_lo[i] = qp.lo[i];
 #pragma unroll
     for (int i = 18; i < 30; ++i) qp_lo[i - 12] = qp.lo[i];
   }
+#define UMPC_LO(i) umpc_lo_eq(par, (i), qp_lo[(i) < 6 ? (i) : ((i) >= 18 && (i) < 30 ? (i) - 12 : 0)])
   // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
   float W3[3], Wi3[3];
 #pragma unroll
@@ -238,10 +252,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
   float c = 1.0f;
-  float xs[UMPC_NX], v[UMPC_NEQ], z3[3], y3[3];
-  float aWr[ST::kAWInRegs ? UMPC_NEQ : 1];  // alpha*W of the equality rows when the store keeps them in registers
-#define UMPC_AW(i) (ST::kAWInRegs ? aWr[ST::kAWInRegs ? (i) : 0] : st.aW(i))
-#define UMPC_LO(i) umpc_lo_eq(par, (i), ST::kLoInRegs ? qp_lo[(i) < 6 ? (i) : ((i) >= 18 && (i) < 30 ? (i) - 12 : 0)] : st.Lo(i))
+  float xs[UMPC_NX], w[UMPC_NEQ], kpu[UMPC_NX - UMPC_NEQ], z3[3], y3[3];
   {
     float D[UMPC_NX], E[UMPC_NC];
 #pragma unroll
@@ -265,10 +276,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       for (int j = 0; j < UMPC_NX; ++j) {
         const float px = umpc_px(par, j);
         psum += c * px * D[j] * D[j];
-        if (j < 36) {
-          const float ydj = j < 18 ? yd[j % 6] : dyd[j % 6];
-          nq = fmaxf(nq, fabsf(c * D[j] * px * ydj));
-        }
+        if (j < 36) nq = fmaxf(nq, fabsf(c * D[j] * px * umpc_ref(yd, dyd, j)));
       }
       float ct = psum * (1.0f / UMPC_NX);
       ct = fmaxf(ct, umpc_limit_scaling(nq));
@@ -295,7 +303,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setSg2(q, sgv[2 * q], sgv[2 * q + 1]);
       umpc_gen_factor(G, W, a, st);
-      // ---- warm start -> hatted coordinates (x D, z / E, y E) ----------------------------
+      // ---- warm start -> hatted, shifted coordinates; the two start vectors of w ---------
       // All global loads are issued before any global store (the compiler cannot move a load across
       // a store that might alias, and a load -> store -> load chain exposes the full memory latency
       // once per element).
@@ -304,91 +312,131 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       for (int i = 0; i < UMPC_NC; ++i) { zs0[i] = io.ld_zs(i); ys0[i] = io.ld_ys(i); }
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) xs[j] = io.ld_xs(j);
-      float vfix[UMPC_NEQ];
+      float lo[UMPC_NEQ], xp[UMPC_NX];
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) lo[i] = UMPC_LO(i);
+      umpc_gen_xp(xp, lo, a);
+      float v0[UMPC_NC], vf[UMPC_NC];  // minus W l: the -b of kappa rides along
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) {
         const float zh = zs0[i] * UMPC_RCP(E[i]), yh = ys0[i] * E[i];
-        const float lo = umpc_lo_eq(par, i, qp_lo[i < 6 ? i : (i >= 18 && i < 30 ? i - 12 : 0)]);
-        v[i] = W[i] * zh - yh;
-        vfix[i] = (2.0f - alpha) * W[i] * lo - yh - oma * W[i] * zh;
-        if (ST::kAWInRegs) aWr[i] = alpha * W[i]; else st.setaW(i, alpha * W[i]);
+        v0[i] = W[i] * (zh - lo[i]) - yh;
+        vf[i] = oma * W[i] * (lo[i] - zh) - yh;   // (2 - alpha) W l - yh - (1 - alpha) W zh - W l
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
+        v0[UMPC_NEQ + k] = 0.0f; vf[UMPC_NEQ + k] = 0.0f;
         z3[k] = zs0[UMPC_NEQ + k] * UMPC_RCP(E[UMPC_NEQ + k]);
         y3[k] = ys0[UMPC_NEQ + k] * E[UMPC_NEQ + k];
         W3[k] = W[UMPC_NEQ + k];
         Wi3[k] = UMPC_RCP(W3[k]);
       }
+      float w0[UMPC_NX], wf[UMPC_NX], kapo[UMPC_NEQ];
 #pragma unroll
-      for (int j = 0; j < UMPC_NX; ++j) xs[j] *= D[j];
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const float kap = c * umpc_px(par, j) * (umpc_ref(yd, dyd, j) - xp[j]);  // 0 on the input columns
+        w0[j] = kap; wf[j] = kap;
+        if (j < UMPC_NEQ) kapo[j] = kap;
+        xs[j] = xs[j] * D[j] - xp[j];
+      }
+      umpc_gen_ATv_add(w0, v0, a);
+      umpc_gen_ATv_add(wf, vf, a);
+      // constant of the input-column part: w_u = kappa_u + B_u' vhat, vhat = M^-T (w_o - kappa_o), kappa_u = 0
+      umpc_gen_gu_from_go(kpu, kapo, a);
 #pragma unroll
-      for (int i = 0; i < UMPC_NEQ; ++i) st.setVf(i, vfix[i]);
+      for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) kpu[i] = -kpu[i];
+      // The first pass forms r with w0 but must continue from wf:  w1 = wf - alpha w0 + t  (t = the rest of the
+      // update).  Written as the regular update (1 - alpha) X + t of a substitute X = (wf - alpha w0) / (1 - alpha),
+      // so that the loop body has no first-iteration special case beyond swapping w (alpha != 1: OSQP's 1.6).
+      const float ioma = 1.0f / oma;
+#pragma unroll
+      for (int j = 0; j < UMPC_NEQ; ++j) { w[j] = w0[j]; st.setVf(j, (wf[j] - alpha * w0[j]) * ioma); }
     }
   }
   // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
-  float cyd[6], cdyd[6];  // c * ydes, c * dydes  ->  -c q0_j = Px_j * (c yd)
-#pragma unroll
-  for (int i = 0; i < 6; ++i) { cyd[i] = c * yd[i]; cdyd[i] = c * dyd[i]; }
+  const float ac = alpha * c;
   const int niter = par.max_iter < 1 ? 1 : par.max_iter;
   for (int it = 0; it < niter; ++it) {
     st.begin_iteration(it);  // scratch reads of this pass must not be hoisted out of the loop
     float r[UMPC_NX];
-    {
-      float vv[UMPC_NC];
+    float m3[3];
 #pragma unroll
-      for (int i = 0; i < UMPC_NEQ; ++i) vv[i] = v[i];
+    for (int k = 0; k < 3; ++k) m3[k] = W3[k] * z3[k] - y3[k];
+    // input-column part of w, re-derived from the own-column part every pass: g stays exactly in range(A_eq')
+    float wu[UMPC_NX - UMPC_NEQ];
+    umpc_gen_gu_from_go(wu, w, a);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) vv[UMPC_NEQ + k] = W3[k] * z3[k] - y3[k];
+    for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) wu[i] += kpu[i];
 #pragma unroll
-      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
-        float s0, s1;
-        st.Sg2(q, s0, s1);
+    for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
+      float s0, s1;
+      st.Sg2(q, s0, s1);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int j = 2 * q + h;
-          if (j < UMPC_NX) {
-            float rj = (h ? s1 : s0) * xs[j];
-            if (j < 36) rj += umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]);
-            r[j] = rj;
-          }
-        }
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * q + h;
+        if (j < UMPC_NX) r[j] = (h ? s1 : s0) * xs[j] + (j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] : wu[j >= UMPC_NEQ ? j - UMPC_NEQ : 0]);
       }
-      umpc_gen_ATv_add(r, vv, a);
     }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) r[36 + 3 * k] += m3[k];
     if (it == 0) {
 #pragma unroll
-      for (int i = 0; i < UMPC_NEQ; ++i) v[i] = st.Vf(i);
+      for (int j = 0; j < UMPC_NEQ; ++j) w[j] = st.Vf(j);
     }
     umpc_gen_solve(r, st);
-    {
-      float zt[UMPC_NC];
-      umpc_gen_Ax(zt, r, a);
 #pragma unroll
-      for (int i = 0; i < UMPC_NEQ; ++i) v[i] -= UMPC_AW(i) * (zt[i] - UMPC_LO(i));
+    for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
+      float s0, s1;
+      st.Sg2b(q, s0, s1);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        const float t = alpha * zt[UMPC_NEQ + k] + oma * z3[k];
-        const float zn = fminf(fmaxf(t + Wi3[k] * y3[k], lo_thr), hi_thr);
-        y3[k] += W3[k] * (t - zn);
-        z3[k] = zn;
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * q + h;
+        if (j < UMPC_NX) {
+          const float d = xs[j] - r[j];
+          if (j < UMPC_NEQ) {
+            const float t = (ac * umpc_px(par, j)) * r[j] - alpha * ((h ? s1 : s0) * d);
+            w[j < UMPC_NEQ ? j : 0] = oma * w[j < UMPC_NEQ ? j : 0] + t;
+          }
+          xs[j] -= alpha * d;
+        }
       }
     }
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) xs[j] = alpha * r[j] + oma * xs[j];
+    for (int k = 0; k < 3; ++k) {
+      const float t = alpha * r[36 + 3 * k] + oma * z3[k];
+      const float zn = fminf(fmaxf(t + Wi3[k] * y3[k], lo_thr), hi_thr);
+      y3[k] += W3[k] * (t - zn);
+      z3[k] = zn;
+    }
   }
-  // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
+  // ---- back to un-shifted coordinates; equality-row duals from g = w - kappa ----------------
   float solx_u[3], solx_dy1[6];
   {
     float zs[UMPC_NC], ys[UMPC_NC];
-    const float ialpha = 1.0f / alpha;
+    float Dl[UMPC_NX], El[UMPC_NC];  // global loads first, stores after (see the warm-start note)
 #pragma unroll
-    for (int i = 0; i < UMPC_NEQ; ++i) {
-      zs[i] = UMPC_LO(i);
-      ys[i] = UMPC_AW(i) * (zs[i] * ialpha) - v[i];
+    for (int j = 0; j < UMPC_NX; ++j) Dl[j] = io.ld_D(j);
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) El[i] = io.ld_E(i);
+    {
+      float lo[UMPC_NEQ], xp[UMPC_NX], v[UMPC_NEQ];
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) lo[i] = UMPC_LO(i);
+      umpc_gen_xp(xp, lo, a);
+      float g[UMPC_NX];
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) {
+        // own columns of g - b = A_eq'(v - W l); the input columns are not read by the substitution
+        g[j] = j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] - c * umpc_px(par, j) * (umpc_ref(yd, dyd, j) - xp[j]) : 0.0f;
+        xs[j] += xp[j];
+      }
+      umpc_gen_v_from_g(v, g, a);  // v - W l
+#pragma unroll
+      for (int i = 0; i < UMPC_NEQ; ++i) { zs[i] = lo[i]; ys[i] = -v[i]; }  // yh = W l - v
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) { zs[UMPC_NEQ + k] = z3[k]; ys[UMPC_NEQ + k] = y3[k]; }
+    // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
     float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
     {
       float Ax[UMPC_NC];
@@ -409,7 +457,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
         const float px = c * umpc_px(par, j) * xs[j];
-        const float qj = j < 36 ? -umpc_px(par, j) * (j < 18 ? cyd[j % 6] : cdyd[j % 6]) : 0.0f;
+        const float qj = -c * umpc_px(par, j) * umpc_ref(yd, dyd, j);
         dua = fmaxf(dua, fabsf(px + qj + Aty[j]));
         nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
       }
@@ -428,11 +476,6 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     // ---- store_solution (auxil.c:527-562); warm start back to OSQP's scaled coordinates ---
     const bool bad = status == UMPC_ST_NON_CVX;
     const float nanv = nanf("");
-    float Dl[UMPC_NX], El[UMPC_NC];  // loads first, stores after (see the warm-start note)
-#pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) Dl[j] = io.ld_D(j);
-#pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) El[i] = io.ld_E(i);
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) {
       const float sx = bad ? nanv : xs[j];
@@ -459,4 +502,5 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0[i]) / dt;
   }
+#undef UMPC_LO
 }

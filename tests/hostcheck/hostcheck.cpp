@@ -6,20 +6,16 @@
 #include "../../robobee3d_b200/csrc/umpc_core.cuh"
 
 struct HostStore {
-  float l[UMPC_GEN_NNZL], di[UMPC_NX], aw[UMPC_NEQ], sg[UMPC_NX + 1], lo[UMPC_NEQ], vf[UMPC_NEQ];
+  float l[UMPC_GEN_NNZL], di[UMPC_NX], sg[UMPC_NX + 1], vf[UMPC_NX];
   float L(int n) const { return l[n]; }
   float Lb(int n) const { return l[n]; }
   float Di(int k) const { return di[k]; }
-  float aW(int i) const { return aw[i]; }
-  static constexpr bool kAWInRegs = false, kLoInRegs = false;
   void Sg2(int q, float& a, float& b) const { a = sg[2 * q]; b = sg[2 * q + 1]; }
-  float Lo(int i) const { return lo[i]; }
+  void Sg2b(int q, float& a, float& b) const { Sg2(q, a, b); }
   float Vf(int i) const { return vf[i]; }
   void setL(int n, float v) { l[n] = v; }
   void setDi(int k, float v) { di[k] = v; }
-  void setaW(int i, float v) { aw[i] = v; }
   void setSg2(int q, float a, float b) { sg[2 * q] = a; sg[2 * q + 1] = b; }
-  void setLo(int i, float v) { lo[i] = v; }
   void setVf(int i, float v) { vf[i] = v; }
   void begin_iteration(int) {}
 };
