@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libumpc_b200.so")
+# UMPC_B200_LIB: alternative build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("UMPC_B200_LIB") or os.path.join(HERE, "libumpc_b200.so")
 
 FP = C.POINTER(C.c_float)
 IP = C.POINTER(C.c_int)

@@ -19,20 +19,22 @@ def stale():
     return any(os.path.getmtime(d) > t for d in DEPS)
 
 
-def build(force=False, verbose=False):
-    if not force and not stale():
+def build(force=False, verbose=False, defines=(), out=None):
+    """defines/out: tuning variants (e.g. defines=("UMPC_LREG_GROUPS=8",), out="/path/libumpc_b200_v.so")"""
+    if out is None and not force and not stale():
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", OUT, SRC]
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
-    with open(os.path.join(HERE, "csrc", "ptxas_v.log"), "w") as f:
-        f.write(log)
+    if out is None:
+        with open(os.path.join(HERE, "csrc", "ptxas_v.log"), "w") as f:
+            f.write(log)
     if verbose or r.returncode:
         sys.stderr.write(log)
     if r.returncode:
         raise RuntimeError("nvcc failed for libumpc_b200.so")
-    return OUT
+    return out or OUT
 
 
 if __name__ == "__main__":

@@ -83,6 +83,21 @@ UMPC_HD float umpc_limit_scaling(float v) {
   return v > 1e4f ? 1e4f : v; // MAX_SCALING
 }
 
+// sigma / D_j^2 pairs are kept as two bf16 halves of one scratch word (8 significant bits, full float range):
+// the term is ~1e-6 of the diagonal of K, and it multiplies xh and (xh - xt) only
+UMPC_HD float umpc_pack2(float a, float b) {
+  union { float f; unsigned u; } ua, ub, r;
+  ua.f = a; ub.f = b;
+  r.u = (ua.u >> 16) | (ub.u & 0xffff0000u);
+  return r.f;
+}
+UMPC_HD void umpc_unpack2(float w, float& a, float& b) {
+  union { float f; unsigned u; } uw, ua, ub;
+  uw.f = w;
+  ua.u = uw.u << 16; ub.u = uw.u & 0xffff0000u;
+  a = ua.f; b = ub.f;
+}
+
 // diagonal of P0 (updateObjective, uprightmpc2.c:182-207)
 UMPC_HD float umpc_px(const UmpcParams& par, int j) {
   if (j < 12) return par.Qyr[j % 6];
@@ -223,6 +238,16 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   const float dt = par.dt;
   if (actualT0 >= 0.0f) T0 = actualT0;
   io.prefetch_warm_start();  // xs/zs/ys are needed only after Ruiz + factor: start pulling them into L2 now
+  // The 28 inputs are needed again only after the ADMM loop (bounds for the un-shift, R0/dq0 for accdes): park
+  // them in the IO's scratch and re-read them there, so that they do not occupy registers during the loop
+  // (the loop's own state is ~170 registers; what is left buys instruction-level parallelism).
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { io.stash(i, p0[i]); io.stash(18 + i, pdes[i]); io.stash(21 + i, dpdes[i]); io.stash(24 + i, sdes[i]); }
+#pragma unroll
+  for (int i = 0; i < 9; ++i) io.stash(3 + i, R0[i]);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) io.stash(12 + i, dq0[i]);
+  io.stash(27, T0);
   UmpcAVals a;
   float yd[6], dyd[6], lo_thr, hi_thr;
   float qp_lo[18];  // run-time equality bounds: rows 0..5 and 18..29
@@ -301,7 +326,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         io.st_E(i, E[i]);
       }
 #pragma unroll
-      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setSg2(q, sgv[2 * q], sgv[2 * q + 1]);
+      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setW(UMPC_GEN_OFF_SG + q, umpc_pack2(sgv[2 * q], sgv[2 * q + 1]));
       umpc_gen_factor(G, W, a, st);
       // ---- warm start -> hatted, shifted coordinates; the two start vectors of w ---------
       // All global loads are issued before any global store (the compiler cannot move a load across
@@ -368,13 +393,18 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) wu[i] += kpu[i];
 #pragma unroll
-    for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
-      float s0, s1;
-      st.Sg2(q, s0, s1);
+    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / 4; ++gq) {
+      const UmpcF4 sg = st.ldf(UMPC_GEN_OFF_SG / 4 + gq);
+      const float wd[4] = {sg.x, sg.y, sg.z, sg.w};
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int j = 2 * q + h;
-        if (j < UMPC_NX) r[j] = (h ? s1 : s0) * xs[j] + (j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] : wu[j >= UMPC_NEQ ? j - UMPC_NEQ : 0]);
+      for (int u = 0; u < 4; ++u) {
+        float s2[2];
+        umpc_unpack2(wd[u], s2[0], s2[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int j = 2 * (4 * gq + u) + h;
+          if (j < UMPC_NX) r[j] = s2[h] * xs[j] + (j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] : wu[j >= UMPC_NEQ && j < UMPC_NX ? j - UMPC_NEQ : 0]);
+        }
       }
     }
 #pragma unroll
@@ -385,19 +415,24 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
     umpc_gen_solve(r, st);
 #pragma unroll
-    for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) {
-      float s0, s1;
-      st.Sg2b(q, s0, s1);
+    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / 4; ++gq) {
+      const UmpcF4 sg = st.ldb(UMPC_GEN_OFF_SG / 4 + gq);
+      const float wd[4] = {sg.x, sg.y, sg.z, sg.w};
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int j = 2 * q + h;
-        if (j < UMPC_NX) {
-          const float d = xs[j] - r[j];
-          if (j < UMPC_NEQ) {
-            const float t = (ac * umpc_px(par, j)) * r[j] - alpha * ((h ? s1 : s0) * d);
-            w[j < UMPC_NEQ ? j : 0] = oma * w[j < UMPC_NEQ ? j : 0] + t;
+      for (int u = 0; u < 4; ++u) {
+        float s2[2];
+        umpc_unpack2(wd[u], s2[0], s2[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int j = 2 * (4 * gq + u) + h;
+          if (j < UMPC_NX) {
+            const float d = xs[j] - r[j];
+            if (j < UMPC_NEQ) {
+              const float t = (ac * umpc_px(par, j)) * r[j] - alpha * (s2[h] * d);
+              w[j < UMPC_NEQ ? j : 0] = oma * w[j < UMPC_NEQ ? j : 0] + t;
+            }
+            xs[j] -= alpha * d;
           }
-          xs[j] -= alpha * d;
         }
       }
     }
@@ -411,8 +446,27 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   }
   // ---- back to un-shifted coordinates; equality-row duals from g = w - kappa ----------------
   float solx_u[3], solx_dy1[6];
+  float R0b[9], dq0b[6];
   {
     float zs[UMPC_NC], ys[UMPC_NC];
+    float qp_lo[18], yd[6], dyd[6];
+    UmpcAVals a;
+    {
+      float p0b[3], pdb[3], dpdb[3], sdb[3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { p0b[i] = io.unstash(i); pdb[i] = io.unstash(18 + i); dpdb[i] = io.unstash(21 + i); sdb[i] = io.unstash(24 + i); }
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R0b[i] = io.unstash(3 + i);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) dq0b[i] = io.unstash(12 + i);
+      UmpcQP qp;
+      umpc_build(par, qp, p0b, R0b, dq0b, pdb, dpdb, sdb, io.unstash(27));
+      a = qp.a;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) { yd[i] = qp.yd[i]; dyd[i] = qp.dyd[i]; qp_lo[i] = qp.lo[i]; }
+#pragma unroll
+      for (int i = 18; i < 30; ++i) qp_lo[i - 12] = qp.lo[i];
+    }
     float Dl[UMPC_NX], El[UMPC_NC];  // global loads first, stores after (see the warm-start note)
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) Dl[j] = io.ld_D(j);
@@ -496,11 +550,11 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   T0 += solx_u[0];
   uquad[0] = T0; uquad[1] = solx_u[1]; uquad[2] = solx_u[2];
   {
-    const float t0 = R0[0] * solx_dy1[3] + R0[1] * solx_dy1[4] + R0[2] * solx_dy1[5];
-    const float t1 = R0[3] * solx_dy1[3] + R0[4] * solx_dy1[4] + R0[5] * solx_dy1[5];
+    const float t0 = R0b[0] * solx_dy1[3] + R0b[1] * solx_dy1[4] + R0b[2] * solx_dy1[5];
+    const float t1 = R0b[3] * solx_dy1[3] + R0b[4] * solx_dy1[4] + R0b[5] * solx_dy1[5];
     const float dq1[6] = {solx_dy1[0], solx_dy1[1], solx_dy1[2], -t1, t0, 0.0f};
 #pragma unroll
-    for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0[i]) / dt;
+    for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt;
   }
 #undef UMPC_LO
 }

@@ -23,65 +23,59 @@
 #include "wl_core.cuh"
 #include "../../include/umpc_b200.h"
 
-// ---- shared-memory store: [entry][thread] ---------------------------------------------------
-#define SM_OFF_L 0
-#define SM_OFF_DI (SM_OFF_L + UMPC_GEN_NNZL)
-#define SM_OFF_SG (SM_OFF_DI + UMPC_NX)             // 23 words: sigma/D^2 as bf16 pairs
-#define SM_FLOATS_PER_THREAD (SM_OFF_SG + 23)       // 235 floats = 940 B per QP -> 7 one-warp CTAs per SM
+// ---- shared-memory store: [group of 4 words][thread][4] ---------------------------------------------
+// One 128-bit LDS per four scratch words: a quarter warp reads 128 contiguous bytes (conflict free), and the
+// ADMM pass issues ~100 shared loads instead of ~400.  UMPC_LREG_GROUPS leading groups (the L entries of the
+// columns eliminated first: read at the start of the forward and at the end of the backward substitution) stay
+// in registers for the whole solve.
+#ifndef UMPC_LREG_GROUPS
+#define UMPC_LREG_GROUPS 0
+#endif
+#define SM_GROUPS (UMPC_GEN_NWORDS / 4 - UMPC_LREG_GROUPS)
+#define SM_FLOATS_PER_THREAD (SM_GROUPS * 4)
 
 template <int TPB>
 struct SmemStore {
-  static constexpr uint32_t nt4 = TPB * 4u;  // byte stride between entries: compile-time -> immediate offsets
-  uint32_t sbase;  // shared-window byte address of &smem[threadIdx.x]
+  static constexpr uint32_t gstride = TPB * 16u;  // byte stride between groups: compile-time -> immediate offsets
+  uint32_t sbase;  // shared-window byte address of this thread's first group
   int tok;         // current ADMM pass: an input of every load so that loads stay inside the loop
   float* vf;       // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
   int B;
-  __device__ __forceinline__ void init(float* smem_thread, float* vf_, int B_) {
-    sbase = (uint32_t)__cvta_generic_to_shared(smem_thread);
+  UmpcF4 lr[UMPC_LREG_GROUPS > 0 ? UMPC_LREG_GROUPS : 1];
+  __device__ __forceinline__ void init(float* smem_block, int lane, float* vf_, int B_) {
+    sbase = (uint32_t)__cvta_generic_to_shared(smem_block) + (uint32_t)lane * 16u;
     tok = 0; vf = vf_; B = B_;
   }
   __device__ __forceinline__ void begin_iteration(int it) { tok = it; }
   // non-volatile asm: free to be scheduled anywhere in the pass, but not CSE'd across passes (tok differs)
-  __device__ __forceinline__ float ld(int e, int t) const {
-    float v;
-    asm("ld.shared.f32 %0, [%1]; // %2" : "=f"(v) : "r"(sbase + (uint32_t)e * nt4), "r"(t));
+  __device__ __forceinline__ UmpcF4 ldf(int q) const {
+    if (q < UMPC_LREG_GROUPS) return lr[q < UMPC_LREG_GROUPS ? q : 0];
+    UmpcF4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4]; // %5"
+        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+        : "r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride), "r"(tok));
     return v;
   }
-  __device__ __forceinline__ void stf(int e, float v) {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)e * nt4), "f"(v) : "memory");
-  }
-  __device__ __forceinline__ float L(int n) const { return ld(SM_OFF_L + n, tok); }
-  // second read of the same entries in the backward substitution: a different token, so that the
-  // compiler re-loads instead of keeping 167 forward values alive (and spilling them)
-  __device__ __forceinline__ float Lb(int n) const {
-    float v;  // volatile: ptxas would otherwise merge it with the forward read of the same address
-    asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"(sbase + (uint32_t)(SM_OFF_L + n) * nt4));
+  // second read of a group in the same pass (backward substitution): volatile, so that the compiler re-loads
+  // instead of keeping ~200 forward values alive (and spilling them)
+  __device__ __forceinline__ UmpcF4 ldb(int q) const {
+    if (q < UMPC_LREG_GROUPS) return lr[q < UMPC_LREG_GROUPS ? q : 0];
+    UmpcF4 v;
+    asm volatile("ld.volatile.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride));
     return v;
   }
-  __device__ __forceinline__ float Di(int k) const { return ld(SM_OFF_DI + k, tok); }
-  // sigma/D_j^2 enters the right-hand side as a ~1e-6-relative term: bf16 (8 significant bits, full
-  // float range) is ample, and halves its footprint
-  __device__ __forceinline__ void Sg2(int q, float& a, float& b) const {
-    uint32_t w;
-    asm("ld.shared.b32 %0, [%1]; // %2" : "=r"(w) : "r"(sbase + (uint32_t)(SM_OFF_SG + q) * nt4), "r"(tok));
-    a = __uint_as_float(w << 16);
-    b = __uint_as_float(w & 0xffff0000u);
-  }
-  // second read of the pair in the same pass (after the solve): volatile so that it is re-loaded instead of
-  // 23 registers staying live across the solve
-  __device__ __forceinline__ void Sg2b(int q, float& a, float& b) const {
-    uint32_t w;
-    asm volatile("ld.volatile.shared.b32 %0, [%1];" : "=r"(w) : "r"(sbase + (uint32_t)(SM_OFF_SG + q) * nt4));
-    a = __uint_as_float(w << 16);
-    b = __uint_as_float(w & 0xffff0000u);
-  }
-  __device__ __forceinline__ void setSg2(int q, float a, float b) {
-    const uint32_t w = (__float_as_uint(a) >> 16) | (__float_as_uint(b) & 0xffff0000u);
-    asm volatile("st.shared.b32 [%0], %1;" ::"r"(sbase + (uint32_t)(SM_OFF_SG + q) * nt4), "r"(w) : "memory");
+  __device__ __forceinline__ void setW(int e, float v) {
+    const int q = e >> 2, c = e & 3;
+    if (q < UMPC_LREG_GROUPS) {
+      UmpcF4& g = lr[q < UMPC_LREG_GROUPS ? q : 0];
+      if (c == 0) g.x = v; else if (c == 1) g.y = v; else if (c == 2) g.z = v; else g.w = v;
+    } else {
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride + (uint32_t)c * 4u), "f"(v) : "memory");
+    }
   }
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
-  __device__ __forceinline__ void setL(int n, float v) { stf(SM_OFF_L + n, v); }
-  __device__ __forceinline__ void setDi(int k, float v) { stf(SM_OFF_DI + k, v); }
   __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
 
@@ -112,6 +106,10 @@ struct GlobIO {
       asm volatile("prefetch.global.L2 [%0];" ::"l"(s.ys + (size_t)i * s.B + e));
     }
   }
+  // inputs parked over the ADMM loop (solx is dead until the solution is stored); volatile read-back so that the
+  // compiler cannot keep the values in registers instead
+  __device__ __forceinline__ void stash(int k, float v) { s.solx[(size_t)k * s.B + e] = v; }
+  __device__ __forceinline__ float unstash(int k) const { return *(volatile const float*)(s.solx + (size_t)k * s.B + e); }
   __device__ __forceinline__ float ld_xs(int j) const { return s.xs[(size_t)j * s.B + e]; }
   __device__ __forceinline__ float ld_zs(int i) const { return s.zs[(size_t)i * s.B + e]; }
   __device__ __forceinline__ float ld_ys(int i) const { return s.ys[(size_t)i * s.B + e]; }
@@ -170,7 +168,7 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
   }
   SmemStore<TPB> st;
-  st.init(g_smem + threadIdx.x, s.soly + e, s.B);
+  st.init(g_smem, threadIdx.x, s.soly + e, s.B);
   GlobIO io(s, e);
   float uq[3], acc[6];
   UmpcInfo info;
@@ -183,6 +181,13 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
   for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; s.acc[(size_t)i * s.B + e] = acc[i]; }
   if (p_next) {
     // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
+    // (inputs re-read: they were not kept in registers over the solve)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) p[i] = *(volatile const float*)(p0 + (size_t)e * 3 + i);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = *(volatile const float*)(R0 + (size_t)e * 9 + i);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dq[i] = *(volatile const float*)(dq0 + (size_t)e * 6 + i);
     uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
     uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
     sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
@@ -257,20 +262,18 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= s.B) return;
   const size_t B = s.B;
-  float p[3], R[9], dq[6], uq[3], pinit[3], tp[4];
+  float p[3], R[9], dq[6], uq[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { p[i] = s.p[i * B + e]; uq[i] = s.uq[i * B + e]; pinit[i] = s.pinit[i * B + e]; }
+  for (int i = 0; i < 3; ++i) { p[i] = s.p[i * B + e]; uq[i] = s.uq[i * B + e]; }
 #pragma unroll
   for (int i = 0; i < 9; ++i) R[i] = s.R[i * B + e];
 #pragma unroll
   for (int i = 0; i < 6; ++i) dq[i] = s.dq[i * B + e];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) tp[i] = s.tp[i * B + e];
   const int task = s.task[e];
   float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
   float pert_done = s.metrics[4 * B + e];
   SmemStore<TPB> st;
-  st.init(g_smem + threadIdx.x, s.soly + e, s.B);
+  st.init(g_smem, threadIdx.x, s.soly + e, s.B);
   GlobIO io(s, e);
   for (int k = 0; k < nsteps; ++k) {
     const double t = tvals[k];
@@ -280,15 +283,39 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
     if (fire[k]) {
       // the task's reference is consumed by the controller only: evaluate it when the MPC fires
       float pdes[3], dpdes[3], sdes[3];
-      sim_task(task, t, pinit, tp, kp.sim.int_pos, pdes, dpdes, sdes);
+      {
+        float pinit[3], tp[4];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) pinit[i] = s.pinit[i * B + e];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tp[i] = s.tp[i * B + e];
+        sim_task(task, t, pinit, tp, kp.sim.int_pos, pdes, dpdes, sdes);
+      }
       float acc[6], T0 = s.T0[e];
       const float aT0 = kp.sim.wl_mode ? s.actualT0[e] : -1.0f;
       UmpcInfo info;
+      // plant state and metric sums through memory across the solve: they are not touched by it, and the
+      // ADMM loop needs every register
+#pragma unroll
+      for (int i = 0; i < 3; ++i) s.p[i * B + e] = p[i];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
+      s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
       umpc_update(kp.mpc, st, io, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0, T0, info);
       s.T0[e] = T0;
       store_info(s, e, info);
 #pragma unroll
       for (int i = 0; i < 6; ++i) s.acc[i * B + e] = acc[i];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) p[i] = *(volatile float*)(s.p + i * B + e);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = *(volatile float*)(s.R + i * B + e);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) dq[i] = *(volatile float*)(s.dq + i * B + e);
+      err = *(volatile float*)(s.metrics + 0 * B + e); eff = *(volatile float*)(s.metrics + 1 * B + e);
+      nsolve = *(volatile float*)(s.metrics + 2 * B + e); nstep = *(volatile float*)(s.metrics + 3 * B + e);
       if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, s, e, R, acc);
       nsolve += 1.0f;
     }

@@ -6,23 +6,21 @@
 #include "../../robobee3d_b200/csrc/umpc_core.cuh"
 
 struct HostStore {
-  float l[UMPC_GEN_NNZL], di[UMPC_NX], sg[UMPC_NX + 1], vf[UMPC_NX];
-  float L(int n) const { return l[n]; }
-  float Lb(int n) const { return l[n]; }
-  float Di(int k) const { return di[k]; }
-  void Sg2(int q, float& a, float& b) const { a = sg[2 * q]; b = sg[2 * q + 1]; }
-  void Sg2b(int q, float& a, float& b) const { Sg2(q, a, b); }
+  float wds[UMPC_GEN_NWORDS], vf[UMPC_NX];
+  UmpcF4 ldf(int q) const { return UmpcF4{wds[4 * q], wds[4 * q + 1], wds[4 * q + 2], wds[4 * q + 3]}; }
+  UmpcF4 ldb(int q) const { return ldf(q); }
+  void setW(int e, float v) { wds[e] = v; }
   float Vf(int i) const { return vf[i]; }
-  void setL(int n, float v) { l[n] = v; }
-  void setDi(int k, float v) { di[k] = v; }
-  void setSg2(int q, float a, float b) { sg[2 * q] = a; sg[2 * q + 1] = b; }
   void setVf(int i, float v) { vf[i] = v; }
   void begin_iteration(int) {}
 };
 
 struct HostIO {
   float xs[UMPC_NX], zs[UMPC_NC], ys[UMPC_NC], D[UMPC_NX], E[UMPC_NC], solx[UMPC_NX], soly[UMPC_NC];
+  float scratch[28];
   void prefetch_warm_start() const {}
+  void stash(int k, float v) { scratch[k] = v; }
+  float unstash(int k) const { return scratch[k]; }
   float ld_xs(int j) const { return xs[j]; }
   float ld_zs(int i) const { return zs[i]; }
   float ld_ys(int i) const { return ys[i]; }
