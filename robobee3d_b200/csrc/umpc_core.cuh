@@ -328,6 +328,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setW(UMPC_GEN_OFF_SG + q, umpc_pack2(sgv[2 * q], sgv[2 * q + 1]));
       umpc_gen_factor(G, W, a, st);
+      st.end_writes();  // the factor is read back by the solve (asynchronous stores of a TMEM-backed scratch)
       // ---- warm start -> hatted, shifted coordinates; the two start vectors of w ---------
       // All global loads are issued before any global store (the compiler cannot move a load across
       // a store that might alias, and a load -> store -> load chain exposes the full memory latency
@@ -393,16 +394,17 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) wu[i] += kpu[i];
 #pragma unroll
-    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / 4; ++gq) {
-      const UmpcF4 sg = st.ldf(UMPC_GEN_OFF_SG / 4 + gq);
-      const float wd[4] = {sg.x, sg.y, sg.z, sg.w};
+    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
+      float wd[UMPC_GEN_CHUNK];
+      st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
+      st.wait(wd);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
         float s2[2];
-        umpc_unpack2(wd[u], s2[0], s2[1]);
+        if (2 * (UMPC_GEN_CHUNK * gq + u) < UMPC_NX) umpc_unpack2(wd[u], s2[0], s2[1]);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int j = 2 * (4 * gq + u) + h;
+          const int j = 2 * (UMPC_GEN_CHUNK * gq + u) + h;
           if (j < UMPC_NX) r[j] = s2[h] * xs[j] + (j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] : wu[j >= UMPC_NEQ && j < UMPC_NX ? j - UMPC_NEQ : 0]);
         }
       }
@@ -415,16 +417,17 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
     umpc_gen_solve(r, st);
 #pragma unroll
-    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / 4; ++gq) {
-      const UmpcF4 sg = st.ldb(UMPC_GEN_OFF_SG / 4 + gq);
-      const float wd[4] = {sg.x, sg.y, sg.z, sg.w};
+    for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
+      float wd[UMPC_GEN_CHUNK];
+      st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
+      st.wait(wd);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
         float s2[2];
-        umpc_unpack2(wd[u], s2[0], s2[1]);
+        if (2 * (UMPC_GEN_CHUNK * gq + u) < UMPC_NX) umpc_unpack2(wd[u], s2[0], s2[1]);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int j = 2 * (4 * gq + u) + h;
+          const int j = 2 * (UMPC_GEN_CHUNK * gq + u) + h;
           if (j < UMPC_NX) {
             const float d = xs[j] - r[j];
             if (j < UMPC_NEQ) {

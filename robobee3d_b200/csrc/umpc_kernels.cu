@@ -23,65 +23,103 @@
 #include "wl_core.cuh"
 #include "../../include/umpc_b200.h"
 
-// ---- shared-memory store: [group of 4 words][thread][4] ---------------------------------------------
-// One 128-bit LDS per four scratch words: a quarter warp reads 128 contiguous bytes (conflict free), and the
-// ADMM pass issues ~100 shared loads instead of ~400.  UMPC_LREG_GROUPS leading groups (the L entries of the
-// columns eliminated first: read at the start of the forward and at the end of the backward substitution) stay
-// in registers for the whole solve.
-#ifndef UMPC_LREG_GROUPS
-#define UMPC_LREG_GROUPS 0
-#endif
-#define SM_GROUPS (UMPC_GEN_NWORDS / 4 - UMPC_LREG_GROUPS)
-#define SM_FLOATS_PER_THREAD (SM_GROUPS * 4)
+// ---- per-QP scratch stores ---------------------------------------------------------------------------
+// The scratch of a QP is UMPC_GEN_NWORDS 32-bit words (factor in stream order + sigma/D^2 pairs), requested
+// UMPC_GEN_CHUNK = 16 words at a time by the generated solve: issue(c, buf) ... wait(buf).
+//
+// (1) SmemStore: shared memory laid out [group of 4 words][thread][4]: a chunk is four 128-bit LDS, a quarter
+//     warp reads 128 contiguous bytes (conflict free).  One-warp CTAs, 7 per SM (31 KB each).
+// (2) TmemStore: Blackwell tensor memory (256 KB per SM, 128 lanes x 512 columns x 32 bit) used as PER-THREAD
+//     PRIVATE storage: tcgen05.ld/st.32x32b give thread i of a warp lane (32*(warp%4) + i) and N consecutive
+//     columns -- exactly "word e of my own QP" for every lane, with a warp-uniform address.  256 words per
+//     thread x 8 warps = the whole TMEM; one tcgen05.ld.x16 per chunk, completion by tcgen05.wait::ld.  It
+//     takes the factor traffic off the shared-memory pipe entirely (measured >= 188 B/clk/SM, tests/microbench).
+#define SM_WORDS_USED (UMPC_GEN_OFF_SG + 24)   // 23 pair words, rounded to a 128-bit group
+#define SM_FLOATS_PER_THREAD SM_WORDS_USED
 
 template <int TPB>
 struct SmemStore {
+  static constexpr bool kTmem = false;
   static constexpr uint32_t gstride = TPB * 16u;  // byte stride between groups: compile-time -> immediate offsets
   uint32_t sbase;  // shared-window byte address of this thread's first group
-  int tok;         // current ADMM pass: an input of every load so that loads stay inside the loop
   float* vf;       // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
   int B;
-  UmpcF4 lr[UMPC_LREG_GROUPS > 0 ? UMPC_LREG_GROUPS : 1];
-  __device__ __forceinline__ void init(float* smem_block, int lane, float* vf_, int B_) {
-    sbase = (uint32_t)__cvta_generic_to_shared(smem_block) + (uint32_t)lane * 16u;
-    tok = 0; vf = vf_; B = B_;
-  }
-  __device__ __forceinline__ void begin_iteration(int it) { tok = it; }
-  // non-volatile asm: free to be scheduled anywhere in the pass, but not CSE'd across passes (tok differs)
-  __device__ __forceinline__ UmpcF4 ldf(int q) const {
-    if (q < UMPC_LREG_GROUPS) return lr[q < UMPC_LREG_GROUPS ? q : 0];
-    UmpcF4 v;
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4]; // %5"
-        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-        : "r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride), "r"(tok));
-    return v;
-  }
-  // second read of a group in the same pass (backward substitution): volatile, so that the compiler re-loads
-  // instead of keeping ~200 forward values alive (and spilling them)
-  __device__ __forceinline__ UmpcF4 ldb(int q) const {
-    if (q < UMPC_LREG_GROUPS) return lr[q < UMPC_LREG_GROUPS ? q : 0];
-    UmpcF4 v;
-    asm volatile("ld.volatile.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride));
-    return v;
-  }
-  __device__ __forceinline__ void setW(int e, float v) {
-    const int q = e >> 2, c = e & 3;
-    if (q < UMPC_LREG_GROUPS) {
-      UmpcF4& g = lr[q < UMPC_LREG_GROUPS ? q : 0];
-      if (c == 0) g.x = v; else if (c == 1) g.y = v; else if (c == 2) g.z = v; else g.w = v;
-    } else {
-      asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(q - UMPC_LREG_GROUPS) * gstride + (uint32_t)c * 4u), "f"(v) : "memory");
+  __device__ __forceinline__ void init(uint32_t sbase_, float* vf_, int B_) { sbase = sbase_; vf = vf_; B = B_; }
+  __device__ __forceinline__ void begin_iteration(int) {}
+  // volatile: keeps the generated request order (the software pipeline) and re-loads every pass
+  __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
+#pragma unroll
+    for (int g = 0; g < UMPC_GEN_CHUNK / 4; ++g) {
+      if ((c * (UMPC_GEN_CHUNK / 4) + g) * 4 < SM_WORDS_USED)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[4 * g]), "=f"(v[4 * g + 1]), "=f"(v[4 * g + 2]), "=f"(v[4 * g + 3])
+                     : "r"(sbase + (uint32_t)(c * (UMPC_GEN_CHUNK / 4) + g) * gstride));
     }
   }
+  __device__ __forceinline__ void wait(float (&)[UMPC_GEN_CHUNK]) const {}
+  __device__ __forceinline__ void setW(int e, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(e >> 2) * gstride + (uint32_t)(e & 3) * 4u), "f"(v) : "memory");
+  }
+  __device__ __forceinline__ void end_writes() {}
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
   __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
 
+struct TmemStore {
+  static constexpr bool kTmem = true;
+  uint32_t tbase;  // TMEM address of this warp's word 0: lane block 32*(warp%4), column block 256*(warp/4)
+  float* vf;
+  int B;
+  __device__ __forceinline__ void init(uint32_t tbase_, float* vf_, int B_) { tbase = tbase_; vf = vf_; B = B_; }
+  __device__ __forceinline__ void begin_iteration(int) {}
+  __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]),
+          "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+        : "r"(tbase + (uint32_t)c * UMPC_GEN_CHUNK));
+  }
+  // the loaded registers are in/out operands so that no use of them can be scheduled above the wait
+  __device__ __forceinline__ void wait(float (&v)[UMPC_GEN_CHUNK]) const {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
+                   "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15])
+                 :: "memory");
+  }
+  __device__ __forceinline__ void setW(int e, float v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tbase + (uint32_t)e), "f"(v) : "memory");
+  }
+  __device__ __forceinline__ void end_writes() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
+  __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
+};
+
+// TMEM allocation for a CTA of TPB threads: (TPB / 128) * 256 columns, all 128 lanes.  Warp 0 allocates and frees.
+template <int TPB>
+__device__ __forceinline__ uint32_t tmem_acquire(uint32_t* slot) {
+  constexpr int ncols = (TPB / 128) * UMPC_GEN_NWORDS;
+  if ((threadIdx.x >> 5) == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(slot)), "n"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const int warp = threadIdx.x >> 5;
+  return *slot + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * UMPC_GEN_NWORDS);
+}
+template <int TPB>
+__device__ __forceinline__ void tmem_release(const uint32_t* slot) {
+  constexpr int ncols = (TPB / 128) * UMPC_GEN_NWORDS;
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*slot), "n"(ncols) : "memory");
+}
+
 // ---- global SoA state -------------------------------------------------------------------------
 struct DevState {
-  int B;
+  int B;      // row stride = number of env slots, padded to a multiple of 32 (whole warps only)
+  int nreal;  // environments the caller asked for
   // plant
   float *p, *R, *dq, *uq, *acc;
   // controller
@@ -124,6 +162,10 @@ struct GlobIO {
   __device__ __forceinline__ void st_soly(int i, float v) { s.soly[(size_t)i * s.B + e] = v; }
 };
 
+#ifndef UMPC_DEFAULT_TPB
+#define UMPC_DEFAULT_TPB 32
+#endif
+
 struct KernelParams {
   UmpcParams mpc;
   SimParams sim;
@@ -139,15 +181,19 @@ __device__ __forceinline__ void store_info(const DevState& s, int e, const UmpcI
 }
 
 // ---- kernel 1: one umpcUpdate per environment, inputs in [B][k] (the C-ABI's layout) ---------
-template <int TPB>
-__global__ void __launch_bounds__(TPB, 224 / TPB)
+template <int TPB, class ST>
+__global__ void __launch_bounds__(TPB, ST::kTmem ? 1 : 224 / TPB)
 umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
                    float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
                    const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
                    const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata,
                    float* __restrict__ p_next, float* __restrict__ R_next, float* __restrict__ dq_next) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= s.B) return;
+  __shared__ uint32_t tmem_slot;
+  uint32_t scratch_base;
+  if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
+  else scratch_base = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
+  if (e < s.B) {  // B is a multiple of 32: whole warps
   float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -167,8 +213,8 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
     umpc_qpdata(kp.mpc, qp, out);
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
   }
-  SmemStore<TPB> st;
-  st.init(g_smem, threadIdx.x, s.soly + e, s.B);
+  ST st;
+  st.init(scratch_base, s.soly + e, s.B);
   GlobIO io(s, e);
   float uq[3], acc[6];
   UmpcInfo info;
@@ -198,6 +244,8 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
 #pragma unroll
     for (int i = 0; i < 6; ++i) dq_next[(size_t)e * 6 + i] = dq[i];
   }
+  }
+  if (ST::kTmem) tmem_release<TPB>(&tmem_slot);
 }
 
 // ---- kernel 2: fused closed loop (uprightmpc2.py:87-159) -------------------------------------
@@ -254,13 +302,17 @@ __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp,
   s.actualT0[e] = w0[2] / sim.mb;
 }
 
-template <int TPB>
-__global__ void __launch_bounds__(TPB, 224 / TPB)
+template <int TPB, class ST>
+__global__ void __launch_bounds__(TPB, ST::kTmem ? 1 : 224 / TPB)
 umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
                     const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
                     const double* __restrict__ tvals, LogBuf lg) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= s.B) return;
+  __shared__ uint32_t tmem_slot;
+  uint32_t scratch_base;
+  if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);
+  else scratch_base = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
+  if (e < s.B) {
   const size_t B = s.B;
   float p[3], R[9], dq[6], uq[3];
 #pragma unroll
@@ -272,8 +324,8 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
   const int task = s.task[e];
   float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
   float pert_done = s.metrics[4 * B + e];
-  SmemStore<TPB> st;
-  st.init(g_smem, threadIdx.x, s.soly + e, s.B);
+  ST st;
+  st.init(scratch_base, s.soly + e, s.B);
   GlobIO io(s, e);
   for (int k = 0; k < nsteps; ++k) {
     const double t = tvals[k];
@@ -342,6 +394,8 @@ umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_consta
   for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
   s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
   s.metrics[4 * B + e] = pert_done;
+  }
+  if (ST::kTmem) tmem_release<TPB>(&tmem_slot);
 }
 
 // ---- kernel 3: WL stage alone (drop-in wlConUpdate / wlControllerUpdate, batch of B) ---------
@@ -349,7 +403,7 @@ __global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __g
                                  float* __restrict__ u1, float* __restrict__ w0o, const float* __restrict__ h0,
                                  const float* __restrict__ pdotdes, float* __restrict__ info2) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= s.B) return;
+  if (e >= s.nreal) return;
   float h[6], pd[6], u0[4], w0[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) { h[i] = h0[(size_t)e * 6 + i]; pd[i] = pdotdes[(size_t)e * 6 + i]; }
@@ -374,7 +428,7 @@ __global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __g
 // ---- kernel 4: metric reduction (what ranks all-reduce at the end of a run) -------------------
 __global__ void reduce_metrics_kernel(const __grid_constant__ DevState s, double* __restrict__ out8) {
   double a[6] = {0, 0, 0, 0, 0, 0};
-  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < s.B; e += gridDim.x * blockDim.x) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < s.nreal; e += gridDim.x * blockDim.x) {
     const size_t B = s.B;
     const float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e];
     const float ns = s.metrics[3 * B + e];
@@ -439,7 +493,7 @@ static int set_err(const char* what, cudaError_t e) {
 extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
 
 struct UmpcBatch {
-  int B = 0, device = 0, tpb = 128;
+  int B = 0, Bp = 0, device = 0, tpb = 128;  // B: caller's env count, Bp: padded to whole warps (device stride)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
   bool timed = false;
@@ -521,7 +575,8 @@ static size_t smem_bytes(int tpb) {
 }
 
 extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
-  if (!b || tpb < 32 || tpb > 160 || (tpb % 32)) { g_err = "threads_per_block must be 32..160, multiple of 32"; return UMPC_ERR_ARG; }
+  // 32, 64: shared-memory scratch (one/two-warp CTAs); 128, 256: tensor-memory scratch (TMEM needs 4-warp multiples)
+  if (!b || (tpb != 32 && tpb != 64 && tpb != 128 && tpb != 256)) { g_err = "threads_per_block must be 32, 64 (shared-memory scratch) or 128, 256 (TMEM scratch)"; return UMPC_ERR_ARG; }
   b->tpb = tpb;
   return UMPC_OK;
 }
@@ -529,15 +584,15 @@ extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
 static int reset_state(UmpcBatch* b) {
   CK(cudaMemsetAsync(b->slab, 0, b->slab_floats * sizeof(float), b->stream));
   // D = E = 1 ; WL u0 ; wlqp D = E = c = 1 ; actualT0 = -1
-  std::vector<float> ones((size_t)b->B * 45, 1.0f);
-  CK(cudaMemcpyAsync(b->s.D, ones.data(), (size_t)45 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->s.E, ones.data(), (size_t)39 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->s.wlqp + (size_t)12 * b->B, ones.data(), (size_t)9 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
-  std::vector<float> tmp((size_t)b->B * 4);
-  for (int i = 0; i < 4; ++i) for (int e = 0; e < b->B; ++e) tmp[(size_t)i * b->B + e] = b->bp.wl_u0[i];
-  CK(cudaMemcpyAsync(b->s.wl_u0, tmp.data(), (size_t)4 * b->B * 4, cudaMemcpyHostToDevice, b->stream));
-  for (int e = 0; e < b->B; ++e) tmp[e] = -1.0f;
-  CK(cudaMemcpyAsync(b->s.actualT0, tmp.data(), (size_t)b->B * 4, cudaMemcpyHostToDevice, b->stream));
+  std::vector<float> ones((size_t)b->Bp * 45, 1.0f);
+  CK(cudaMemcpyAsync(b->s.D, ones.data(), (size_t)45 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->s.E, ones.data(), (size_t)39 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->s.wlqp + (size_t)12 * b->Bp, ones.data(), (size_t)9 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
+  std::vector<float> tmp((size_t)b->Bp * 4);
+  for (int i = 0; i < 4; ++i) for (int e = 0; e < b->Bp; ++e) tmp[(size_t)i * b->Bp + e] = b->bp.wl_u0[i];
+  CK(cudaMemcpyAsync(b->s.wl_u0, tmp.data(), (size_t)4 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
+  for (int e = 0; e < b->Bp; ++e) tmp[e] = -1.0f;
+  CK(cudaMemcpyAsync(b->s.actualT0, tmp.data(), (size_t)b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   b->step = 0; b->thl = 0.0;
   return UMPC_OK;
@@ -560,7 +615,7 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   }
   CK(cudaSetDevice(device));
   UmpcBatch* b = new UmpcBatch();
-  b->B = nenv; b->device = device; b->bp = *par;
+  b->B = nenv; b->Bp = (nenv + 31) & ~31; b->device = device; b->bp = *par;
   fill_kernel_params(b);
   CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&b->ev0));
@@ -568,26 +623,32 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   // one slab, SoA rows of B floats
   const int rows = 3 + 9 + 6 + 3 + 6 /*plant*/ + 1 + 45 + 39 + 39 + 45 + 39 + 45 + 39 + 4 /*ctrl*/ + 1 /*task*/ + 4 + 3 + 1 + 5 +
                    4 + 25;
-  b->slab_floats = (size_t)rows * nenv;
+  const int np = b->Bp;
+  b->slab_floats = (size_t)rows * np;
   CK(cudaMalloc(&b->slab, b->slab_floats * sizeof(float)));
   float* q = b->slab;
-  auto take = [&](int r) { float* t = q; q += (size_t)r * nenv; return t; };
+  auto take = [&](int r) { float* t = q; q += (size_t)r * np; return t; };
   DevState& s = b->s;
-  s.B = nenv;
+  s.B = np; s.nreal = nenv;
   s.p = take(3); s.R = take(9); s.dq = take(6); s.uq = take(3); s.acc = take(6);
   s.T0 = take(1); s.xs = take(45); s.zs = take(39); s.ys = take(39); s.D = take(45); s.E = take(39);
   s.solx = take(45); s.soly = take(39); s.info = take(4);
   s.task = (int*)take(1); s.tp = take(4); s.pinit = take(3); s.actualT0 = take(1); s.metrics = take(5);
   s.wl_u0 = take(4); s.wlqp = take(25);
   s.qpdata = nullptr;
-  CK(cudaMalloc(&b->d_in, (size_t)28 * nenv * sizeof(float)));
-  CK(cudaMalloc(&b->d_out, (size_t)10 * nenv * sizeof(float)));
+  CK(cudaMalloc(&b->d_in, (size_t)28 * np * sizeof(float)));
+  CK(cudaMalloc(&b->d_out, (size_t)10 * np * sizeof(float)));
+  CK(cudaMemset(b->d_in, 0, (size_t)28 * np * sizeof(float)));
   CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
-#define UMPC_SET_SMEM(T)                                                                                              \
-  CK(cudaFuncSetAttribute(umpc_update_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));      \
-  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
-  UMPC_SET_SMEM(32) UMPC_SET_SMEM(64) UMPC_SET_SMEM(96) UMPC_SET_SMEM(128) UMPC_SET_SMEM(160)
-  b->tpb = 32;  // 5 independent 1-warp CTAs per SM (smem-limited): best measured, smooth tail
+#define UMPC_SET_SMEM(T)                                                                                                     \
+  CK(cudaFuncSetAttribute(umpc_update_kernel<T, SmemStore<T>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024))); \
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SmemStore<T>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+  UMPC_SET_SMEM(32) UMPC_SET_SMEM(64)
+  b->tpb = UMPC_DEFAULT_TPB;
+  if (const char* t = getenv("UMPC_TPB")) {  // tuning/testing knob: same values as umpcBatchSetLaunch
+    const int v = atoi(t);
+    if (v == 32 || v == 64 || v == 128 || v == 256) b->tpb = v;
+  }
   int rc = reset_state(b);
   if (rc) return rc;
   *out = b;
@@ -638,15 +699,16 @@ extern "C" float umpcBatchLastKernelMs(UmpcBatch* b) {
 static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0, const float* dq0,
                          const float* pdes, const float* dpdes, const float* sdes, const float* aT0,
                          float* pn = nullptr, float* Rn = nullptr, float* dqn = nullptr) {
-  const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
+  const int tpb = b->tpb, grid = (b->Bp + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
-#define UMPC_LAUNCH_UPDATE(T)                                                                                        \
-  case T:                                                                                                           \
-    umpc_update_kernel<T><<<grid, T, smem_bytes(T), b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, \
-                                                                 sdes, aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);      \
+#define UMPC_LAUNCH_UPDATE(T, ST, SMEM)                                                                               \
+  case T:                                                                                                             \
+    umpc_update_kernel<T, ST><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, \
+                                                            aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);                  \
     break;
   switch (tpb) {
-    UMPC_LAUNCH_UPDATE(32) UMPC_LAUNCH_UPDATE(64) UMPC_LAUNCH_UPDATE(96) UMPC_LAUNCH_UPDATE(128) UMPC_LAUNCH_UPDATE(160)
+    UMPC_LAUNCH_UPDATE(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_UPDATE(64, SmemStore<64>, smem_bytes(64))
+    UMPC_LAUNCH_UPDATE(128, TmemStore, 0) UMPC_LAUNCH_UPDATE(256, TmemStore, 0)
     default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
   }
   CK(cudaGetLastError());
@@ -668,9 +730,9 @@ extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const 
                                const float* actualT0) {
   if (!b || !uquad || !accdes || !p0 || !R0 || !dq0 || !pdes || !dpdes || !sdes) { g_err = "umpcBatchUpdate: NULL argument"; return UMPC_ERR_ARG; }
   CK(cudaSetDevice(b->device));
-  const size_t B = b->B;
+  const size_t B = b->B, P = b->Bp;
   float* d = b->d_in;
-  float *dp = d, *dR = dp + 3 * B, *ddq = dR + 9 * B, *dpd = ddq + 6 * B, *ddp = dpd + 3 * B, *dsd = ddp + 3 * B, *daT = dsd + 3 * B;
+  float *dp = d, *dR = dp + 3 * P, *ddq = dR + 9 * P, *dpd = ddq + 6 * P, *ddp = dpd + 3 * P, *dsd = ddp + 3 * P, *daT = dsd + 3 * P;
   CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
@@ -678,7 +740,7 @@ extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const 
   CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
-  float *duq = b->d_out, *dacc = duq + 3 * B;
+  float *duq = b->d_out, *dacc = duq + 3 * P;
   int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr);
   if (rc) return rc;
   CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
@@ -698,10 +760,10 @@ extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float
     return UMPC_ERR_ARG;
   }
   CK(cudaSetDevice(b->device));
-  const size_t B = b->B;
-  if (!b->d_next) CK(cudaMalloc(&b->d_next, (size_t)18 * B * sizeof(float)));
+  const size_t B = b->B, P = b->Bp;
+  if (!b->d_next) CK(cudaMalloc(&b->d_next, (size_t)18 * P * sizeof(float)));
   float* d = b->d_in;
-  float *dp = d, *dR = dp + 3 * B, *ddq = dR + 9 * B, *dpd = ddq + 6 * B, *ddp = dpd + 3 * B, *dsd = ddp + 3 * B, *daT = dsd + 3 * B;
+  float *dp = d, *dR = dp + 3 * P, *ddq = dR + 9 * P, *dpd = ddq + 6 * P, *ddp = dpd + 3 * P, *dsd = ddp + 3 * P, *daT = dsd + 3 * P;
   CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
@@ -709,8 +771,8 @@ extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float
   CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
   if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
-  float *duq = b->d_out, *dacc = duq + 3 * B;
-  float *dpn = b->d_next, *dRn = dpn + 3 * B, *ddqn = dRn + 9 * B;
+  float *duq = b->d_out, *dacc = duq + 3 * P;
+  float *dpn = b->d_next, *dRn = dpn + 3 * P, *ddqn = dRn + 9 * P;
   int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr, dpn, dRn, ddqn);
   if (rc) return rc;
   CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
@@ -725,20 +787,20 @@ extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float
 // SoA [k][B] on device <-> [B][k] on host (diagnostics / state exchange; not on the hot path)
 static int get_rows(UmpcBatch* b, const float* dev, int k, float* host) {
   if (!host) return UMPC_OK;
-  const size_t B = b->B;
-  std::vector<float> tmp(B * k);
-  CK(cudaMemcpyAsync(tmp.data(), dev, B * k * 4, cudaMemcpyDeviceToHost, b->stream));
+  const size_t B = b->B, P = b->Bp;
+  std::vector<float> tmp(P * k);
+  CK(cudaMemcpyAsync(tmp.data(), dev, P * k * 4, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   for (size_t e = 0; e < B; ++e)
-    for (int i = 0; i < k; ++i) host[e * k + i] = tmp[(size_t)i * B + e];
+    for (int i = 0; i < k; ++i) host[e * k + i] = tmp[(size_t)i * P + e];
   return UMPC_OK;
 }
 static int put_rows(UmpcBatch* b, float* dev, int k, const float* host) {
-  const size_t B = b->B;
-  std::vector<float> tmp(B * k);
+  const size_t B = b->B, P = b->Bp;
+  std::vector<float> tmp(P * k, 0.0f);
   for (size_t e = 0; e < B; ++e)
-    for (int i = 0; i < k; ++i) tmp[(size_t)i * B + e] = host[e * k + i];
-  CK(cudaMemcpyAsync(dev, tmp.data(), B * k * 4, cudaMemcpyHostToDevice, b->stream));
+    for (int i = 0; i < k; ++i) tmp[(size_t)i * P + e] = host[e * k + i];
+  CK(cudaMemcpyAsync(dev, tmp.data(), P * k * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   return UMPC_OK;
 }
@@ -763,8 +825,8 @@ extern "C" int umpcBatchGetQPData(UmpcBatch* b, float* qp) {
   CK(cudaSetDevice(b->device));
   if (!b->have_qpdata) {
     // first request: allocate; data is produced by the NEXT update
-    CK(cudaMalloc(&b->s.qpdata, (size_t)216 * b->B * sizeof(float)));
-    CK(cudaMemset(b->s.qpdata, 0, (size_t)216 * b->B * sizeof(float)));
+    CK(cudaMalloc(&b->s.qpdata, (size_t)216 * b->Bp * sizeof(float)));
+    CK(cudaMemset(b->s.qpdata, 0, (size_t)216 * b->Bp * sizeof(float)));
     b->have_qpdata = true;
   }
   return get_rows(b, b->s.qpdata, 216, qp);
@@ -780,11 +842,11 @@ extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, c
   if ((rc = put_rows(b, b->s.R, 9, R))) return rc;
   if ((rc = put_rows(b, b->s.dq, 6, dq))) return rc;
   if (task) CK(cudaMemcpy(b->s.task, task, (size_t)b->B * sizeof(int), cudaMemcpyHostToDevice));
-  else CK(cudaMemset(b->s.task, 0, (size_t)b->B * sizeof(int)));
+  else CK(cudaMemset(b->s.task, 0, (size_t)b->Bp * sizeof(int)));
   if (tp) { if ((rc = put_rows(b, b->s.tp, 4, tp))) return rc; }
-  else CK(cudaMemset(b->s.tp, 0, (size_t)4 * b->B * sizeof(float)));
-  CK(cudaMemset(b->s.uq, 0, (size_t)3 * b->B * sizeof(float)));
-  CK(cudaMemset(b->s.metrics, 0, (size_t)5 * b->B * sizeof(float)));
+  else CK(cudaMemset(b->s.tp, 0, (size_t)4 * b->Bp * sizeof(float)));
+  CK(cudaMemset(b->s.uq, 0, (size_t)3 * b->Bp * sizeof(float)));
+  CK(cudaMemset(b->s.metrics, 0, (size_t)5 * b->Bp * sizeof(float)));
   b->step = 0; b->thl = 0.0;
   return UMPC_OK;
 }
@@ -826,15 +888,16 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
   CK(cudaMemcpyAsync(b->d_fire, fire.data(), nsteps, cudaMemcpyHostToDevice, b->stream));
   CK(cudaMemcpyAsync(b->d_t, tv.data(), (size_t)nsteps * sizeof(double), cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
-  const int tpb = b->tpb, grid = (b->B + tpb - 1) / tpb;
+  const int tpb = b->tpb, grid = (b->Bp + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
-#define UMPC_LAUNCH_ROLLOUT(T)                                                                                   \
-  case T:                                                                                                       \
-    umpc_rollout_kernel<T><<<grid, T, smem_bytes(T), b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, \
-                                                                  b->d_t, b->lg);                                \
+#define UMPC_LAUNCH_ROLLOUT(T, ST, SMEM)                                                                              \
+  case T:                                                                                                             \
+    umpc_rollout_kernel<T, ST><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, \
+                                                             b->lg);                                                    \
     break;
   switch (tpb) {
-    UMPC_LAUNCH_ROLLOUT(32) UMPC_LAUNCH_ROLLOUT(64) UMPC_LAUNCH_ROLLOUT(96) UMPC_LAUNCH_ROLLOUT(128) UMPC_LAUNCH_ROLLOUT(160)
+    UMPC_LAUNCH_ROLLOUT(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_ROLLOUT(64, SmemStore<64>, smem_bytes(64))
+    UMPC_LAUNCH_ROLLOUT(128, TmemStore, 0) UMPC_LAUNCH_ROLLOUT(256, TmemStore, 0)
     default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
   }
   CK(cudaGetLastError());
@@ -1090,18 +1153,19 @@ static int wl_single(const WlParams& wp, int mode, float u0[4], WlqpState* qs, c
   float in[12], out[10];
   memcpy(in, h0, 24); memcpy(in + 6, pdotdes, 24);
   CK(cudaMemcpyAsync(b->d_in, in, sizeof(in), cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->s.wl_u0, u0, 16, cudaMemcpyHostToDevice, b->stream));
+  const size_t pitch = (size_t)b->Bp * sizeof(float);  // SoA rows: element i of env 0 sits at i * Bp
+  CK(cudaMemcpy2DAsync(b->s.wl_u0, pitch, u0, 4, 4, 4, cudaMemcpyHostToDevice, b->stream));
   if (qs) {
     float q[25];
     memcpy(q, qs->xs, 16); memcpy(q + 4, qs->zs, 16); memcpy(q + 8, qs->ys, 16); memcpy(q + 12, qs->D, 16);
     memcpy(q + 16, qs->E, 16); q[20] = qs->c; memcpy(q + 21, qs->q0, 16);
-    CK(cudaMemcpyAsync(b->s.wlqp, q, sizeof(q), cudaMemcpyHostToDevice, b->stream));
+    CK(cudaMemcpy2DAsync(b->s.wlqp, pitch, q, 4, 4, 25, cudaMemcpyHostToDevice, b->stream));
   }
   wl_update_kernel<<<1, 32, 0, b->stream>>>(wp, b->s, mode, b->d_out, b->d_out + 4, b->d_in, b->d_in + 6, nullptr);
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(out, b->d_out, sizeof(out), cudaMemcpyDeviceToHost, b->stream));
   float q[25];
-  if (qs) CK(cudaMemcpyAsync(q, b->s.wlqp, sizeof(q), cudaMemcpyDeviceToHost, b->stream));
+  if (qs) CK(cudaMemcpy2DAsync(q, 4, b->s.wlqp, pitch, 4, 25, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   memcpy(u0, out, 16); memcpy(w0, out + 4, 24);
   if (qs) {

@@ -7,9 +7,10 @@
 
 struct HostStore {
   float wds[UMPC_GEN_NWORDS], vf[UMPC_NX];
-  UmpcF4 ldf(int q) const { return UmpcF4{wds[4 * q], wds[4 * q + 1], wds[4 * q + 2], wds[4 * q + 3]}; }
-  UmpcF4 ldb(int q) const { return ldf(q); }
+  void issue(int c, float (&buf)[UMPC_GEN_CHUNK]) const { for (int i = 0; i < UMPC_GEN_CHUNK; ++i) buf[i] = wds[c * UMPC_GEN_CHUNK + i]; }
+  void wait(float (&)[UMPC_GEN_CHUNK]) const {}
   void setW(int e, float v) { wds[e] = v; }
+  void end_writes() {}
   float Vf(int i) const { return vf[i]; }
   void setVf(int i, float v) { vf[i] = v; }
   void begin_iteration(int) {}
