@@ -285,6 +285,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int i = 0; i < UMPC_NC; ++i) E[i] = 1.0f;
     for (int it = 0; it < par.scaling_iters; ++it) {
+      st.sync();  // keep the warps of a CTA on the same code (shared instruction fetch), see TmemStore::sync
       float cn[UMPC_NX], rn[UMPC_NC];
       umpc_gen_norms(cn, rn, D, E, a);
 #pragma unroll
@@ -310,6 +311,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
     {
+      st.sync();
       float G[UMPC_NX], W[UMPC_NC], sgv[UMPC_NX + 1];
       sgv[UMPC_NX] = 0.0f;
 #pragma unroll
@@ -328,6 +330,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setW(UMPC_GEN_OFF_SG + q, umpc_pack2(sgv[2 * q], sgv[2 * q + 1]));
       umpc_gen_factor(G, W, a, st);
+      st.sync();
       st.end_writes();  // the factor is read back by the solve (asynchronous stores of a TMEM-backed scratch)
       // ---- warm start -> hatted, shifted coordinates; the two start vectors of w ---------
       // All global loads are issued before any global store (the compiler cannot move a load across
@@ -365,6 +368,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         if (j < UMPC_NEQ) kapo[j] = kap;
         xs[j] = xs[j] * D[j] - xp[j];
       }
+      st.sync();
       umpc_gen_ATv_add(w0, v0, a);
       umpc_gen_ATv_add(wf, vf, a);
       // constant of the input-column part: w_u = kappa_u + B_u' vhat, vhat = M^-T (w_o - kappa_o), kappa_u = 0
@@ -383,7 +387,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   const float ac = alpha * c;
   const int niter = par.max_iter < 1 ? 1 : par.max_iter;
   for (int it = 0; it < niter; ++it) {
-    st.begin_iteration(it);  // scratch reads of this pass must not be hoisted out of the loop
+    st.begin_iteration(it);
+    st.sync();
     float r[UMPC_NX];
     float m3[3];
 #pragma unroll
@@ -450,6 +455,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   // ---- back to un-shifted coordinates; equality-row duals from g = w - kappa ----------------
   float solx_u[3], solx_dy1[6];
   float R0b[9], dq0b[6];
+  st.sync();
   {
     float zs[UMPC_NC], ys[UMPC_NC];
     float qp_lo[18], yd[6], dyd[6];
@@ -494,6 +500,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
     for (int k = 0; k < 3; ++k) { zs[UMPC_NEQ + k] = z3[k]; ys[UMPC_NEQ + k] = y3[k]; }
     // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
+    st.sync();
     float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
     {
       float Ax[UMPC_NC];
@@ -519,6 +526,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
       }
     }
+    st.sync();
     const float cinv = UMPC_RCP(c);
     dua *= cinv;
     info.iter = niter; info.pri_res = pri; info.dua_res = dua;

@@ -28,13 +28,13 @@
 // UMPC_GEN_CHUNK = 16 words at a time by the generated solve: issue(c, buf) ... wait(buf).
 //
 // (1) SmemStore: shared memory laid out [group of 4 words][thread][4]: a chunk is four 128-bit LDS, a quarter
-//     warp reads 128 contiguous bytes (conflict free).  One-warp CTAs, 7 per SM (31 KB each).
+//     warp reads 128 contiguous bytes (conflict free).  One-warp CTAs, 6 per SM (32 KB each).
 // (2) TmemStore: Blackwell tensor memory (256 KB per SM, 128 lanes x 512 columns x 32 bit) used as PER-THREAD
 //     PRIVATE storage: tcgen05.ld/st.32x32b give thread i of a warp lane (32*(warp%4) + i) and N consecutive
 //     columns -- exactly "word e of my own QP" for every lane, with a warp-uniform address.  256 words per
 //     thread x 8 warps = the whole TMEM; one tcgen05.ld.x16 per chunk, completion by tcgen05.wait::ld.  It
 //     takes the factor traffic off the shared-memory pipe entirely (measured >= 188 B/clk/SM, tests/microbench).
-#define SM_WORDS_USED (UMPC_GEN_OFF_SG + 24)   // 23 pair words, rounded to a 128-bit group
+#define SM_WORDS_USED UMPC_GEN_NWORDS
 #define SM_FLOATS_PER_THREAD SM_WORDS_USED
 
 template <int TPB>
@@ -50,17 +50,21 @@ struct SmemStore {
   __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
 #pragma unroll
     for (int g = 0; g < UMPC_GEN_CHUNK / 4; ++g) {
-      if ((c * (UMPC_GEN_CHUNK / 4) + g) * 4 < SM_WORDS_USED)
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(v[4 * g]), "=f"(v[4 * g + 1]), "=f"(v[4 * g + 2]), "=f"(v[4 * g + 3])
                      : "r"(sbase + (uint32_t)(c * (UMPC_GEN_CHUNK / 4) + g) * gstride));
     }
   }
-  __device__ __forceinline__ void wait(float (&)[UMPC_GEN_CHUNK]) const {}
+  // nothing to wait for (LDS results are scoreboarded); the empty asm pins the buffer to registers at this point
+  __device__ __forceinline__ void wait(float (&v)[UMPC_GEN_CHUNK]) const {
+    asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
+                 "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]));
+  }
   __device__ __forceinline__ void setW(int e, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(e >> 2) * gstride + (uint32_t)(e & 3) * 4u), "f"(v) : "memory");
   }
   __device__ __forceinline__ void end_writes() {}
+  __device__ __forceinline__ void sync() const {}
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
   __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
@@ -90,6 +94,16 @@ struct TmemStore {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tbase + (uint32_t)e), "f"(v) : "memory");
   }
   __device__ __forceinline__ void end_writes() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+  // Optional CTA-wide rendezvous at phase boundaries (-DUMPC_PHASE_SYNC): keeps the warps of a CTA on the same
+  // straight-line code so that each instruction-cache line of this ~250 KB kernel is fetched once per CTA.  Measured
+  // on B200: no gain (0.338 vs 0.327 ms per 65,536 env-steps) -- the once-per-solve code is bound by the LATENCY of
+  // the sequential instruction fetch (ncu: ~10 cycles per cold instruction), which a rendezvous does not shorten,
+  // while unsynchronised warps overlap it with other warps' hot loops.  Off by default.
+#ifdef UMPC_PHASE_SYNC
+  __device__ __forceinline__ void sync() const { __syncthreads(); }
+#else
+  __device__ __forceinline__ void sync() const {}
+#endif
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
   __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
 };
@@ -118,7 +132,7 @@ __device__ __forceinline__ void tmem_release(const uint32_t* slot) {
 
 // ---- global SoA state -------------------------------------------------------------------------
 struct DevState {
-  int B;      // row stride = number of env slots, padded to a multiple of 32 (whole warps only)
+  int B;      // row stride = number of env slots, padded to a multiple of 256 (whole CTAs only)
   int nreal;  // environments the caller asked for
   // plant
   float *p, *R, *dq, *uq, *acc;
@@ -163,7 +177,7 @@ struct GlobIO {
 };
 
 #ifndef UMPC_DEFAULT_TPB
-#define UMPC_DEFAULT_TPB 32
+#define UMPC_DEFAULT_TPB 128  // TMEM scratch, two 4-warp CTAs per SM
 #endif
 
 struct KernelParams {
@@ -193,7 +207,7 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
   uint32_t scratch_base;
   if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
   else scratch_base = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
-  if (e < s.B) {  // B is a multiple of 32: whole warps
+  if (e < s.B) {  // B is a multiple of 256: whole CTAs (the body contains CTA-wide barriers)
   float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -615,7 +629,7 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   }
   CK(cudaSetDevice(device));
   UmpcBatch* b = new UmpcBatch();
-  b->B = nenv; b->Bp = (nenv + 31) & ~31; b->device = device; b->bp = *par;
+  b->B = nenv; b->Bp = (nenv + 255) & ~255; b->device = device; b->bp = *par;  // Bp: whole CTAs of the largest launch shape
   fill_kernel_params(b);
   CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&b->ev0));

@@ -11,6 +11,7 @@ struct HostStore {
   void wait(float (&)[UMPC_GEN_CHUNK]) const {}
   void setW(int e, float v) { wds[e] = v; }
   void end_writes() {}
+  void sync() const {}
   float Vf(int i) const { return vf[i]; }
   void setVf(int i, float v) { vf[i] = v; }
   void begin_iteration(int) {}
