@@ -201,8 +201,8 @@ umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constan
                    float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
                    const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
                    const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata,
-                   float* __restrict__ p_next, float* __restrict__ R_next, float* __restrict__ dq_next) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+                   float* __restrict__ p_next, float* __restrict__ R_next, float* __restrict__ dq_next, int env0) {
+  const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;  // env0: first env of this launch (chunked host-buffer calls)
   __shared__ uint32_t tmem_slot;
   uint32_t scratch_base;
   if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
@@ -509,6 +509,8 @@ extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
 struct UmpcBatch {
   int B = 0, Bp = 0, device = 0, tpb = 128;  // B: caller's env count, Bp: padded to whole warps (device stride)
   cudaStream_t stream = nullptr;
+  cudaStream_t side[3] = {nullptr, nullptr, nullptr};  // chunk pipeline of the host-buffer calls
+  cudaEvent_t side_ev = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
   bool timed = false;
   UmpcBatchParams bp;
@@ -676,6 +678,8 @@ extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums); cudaFree(b->d_next);
   cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
   cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
+  for (int i = 0; i < 3; ++i) if (b->side[i]) cudaStreamDestroy(b->side[i]);
+  if (b->side_ev) cudaEventDestroy(b->side_ev);
   cudaStreamDestroy(b->stream);
   delete b;
 }
@@ -712,13 +716,16 @@ extern "C" float umpcBatchLastKernelMs(UmpcBatch* b) {
 
 static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0, const float* dq0,
                          const float* pdes, const float* dpdes, const float* sdes, const float* aT0,
-                         float* pn = nullptr, float* Rn = nullptr, float* dqn = nullptr) {
-  const int tpb = b->tpb, grid = (b->Bp + tpb - 1) / tpb;
-  CK(cudaEventRecord(b->ev0, b->stream));
+                         float* pn = nullptr, float* Rn = nullptr, float* dqn = nullptr, int env0 = 0, int nenv = -1,
+                         cudaStream_t stream = nullptr) {
+  if (nenv < 0) nenv = b->Bp;        // whole batch (padded env slots included)
+  if (!stream) stream = b->stream;
+  const int tpb = b->tpb, grid = (nenv + tpb - 1) / tpb;
+  if (stream == b->stream) CK(cudaEventRecord(b->ev0, b->stream));
 #define UMPC_LAUNCH_UPDATE(T, ST, SMEM)                                                                               \
   case T:                                                                                                             \
-    umpc_update_kernel<T, ST><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, \
-                                                            aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn);                  \
+    umpc_update_kernel<T, ST><<<grid, T, SMEM, stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, \
+                                                         b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);                      \
     break;
   switch (tpb) {
     UMPC_LAUNCH_UPDATE(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_UPDATE(64, SmemStore<64>, smem_bytes(64))
@@ -726,8 +733,41 @@ static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float*
     default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
   }
   CK(cudaGetLastError());
-  CK(cudaEventRecord(b->ev1, b->stream));
-  b->timed = true;
+  if (stream == b->stream) { CK(cudaEventRecord(b->ev1, b->stream)); b->timed = true; }
+  return UMPC_OK;
+}
+
+// Host-buffer calls: the batch is cut into chunks of whole CTAs and each chunk's H2D copies, kernel and D2H copies
+// go to one of three side streams, so that the copy engines (one per direction) and the SMs work on different
+// chunks at the same time.  arrays: {host pointer, device staging pointer, floats per env}.
+struct HostArr { const float* h_in; float* h_out; float* d; int k; };
+static int run_chunked(UmpcBatch* b, HostArr* in, int nin, HostArr* out, int nout, float* duq, float* dacc, const float* const* din,
+                       const float* daT, float* dpn, float* dRn, float* ddqn) {
+  if (!b->side[0]) {
+    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&b->side[i], cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&b->side_ev, cudaEventDisableTiming));
+  }
+  CK(cudaEventRecord(b->side_ev, b->stream));  // side streams start after whatever is queued on the batch's stream
+  const int B = b->B;
+  static int nchunks = 0;  // UMPC_E2E_CHUNKS: tuning knob (each chunk costs ~12 copy calls of host-side overhead)
+  if (!nchunks) { const char* ev = getenv("UMPC_E2E_CHUNKS"); nchunks = ev ? atoi(ev) : 2;  // measured on B200 + PCIe gen5: 1 -> 0.65 ms, 2 -> 0.47, 4 -> 0.48, 6 -> 0.62 per 65,536 env-steps if (nchunks < 1) nchunks = 1; }
+  int chunk = (B + nchunks - 1) / nchunks;
+  chunk = (chunk + 255) & ~255;
+  if (chunk < 4096) chunk = 4096;              // below this a launch does not fill the GPU anyway
+  int ci = 0;
+  for (int e0 = 0; e0 < B; e0 += chunk, ++ci) {
+    cudaStream_t st = b->side[ci % 3];
+    if (ci < 3) CK(cudaStreamWaitEvent(st, b->side_ev, 0));
+    const int n = e0 + chunk <= B ? chunk : B - e0;
+    for (int a = 0; a < nin; ++a)
+      if (in[a].h_in) CK(cudaMemcpyAsync(in[a].d + (size_t)e0 * in[a].k, in[a].h_in + (size_t)e0 * in[a].k, (size_t)n * in[a].k * 4, cudaMemcpyHostToDevice, st));
+    const int npad = (n + 255) & ~255;  // the last chunk covers the padded env slots of its CTA
+    int rc = launch_update(b, duq, dacc, din[0], din[1], din[2], din[3], din[4], din[5], daT, dpn, dRn, ddqn, e0, npad, st);
+    if (rc) return rc;
+    for (int a = 0; a < nout; ++a)
+      CK(cudaMemcpyAsync(out[a].h_out + (size_t)e0 * out[a].k, out[a].d + (size_t)e0 * out[a].k, (size_t)n * out[a].k * 4, cudaMemcpyDeviceToHost, st));
+  }
+  for (int i = 0; i < 3 && i < ci; ++i) CK(cudaStreamSynchronize(b->side[i]));
   return UMPC_OK;
 }
 
@@ -744,23 +784,15 @@ extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const 
                                const float* actualT0) {
   if (!b || !uquad || !accdes || !p0 || !R0 || !dq0 || !pdes || !dpdes || !sdes) { g_err = "umpcBatchUpdate: NULL argument"; return UMPC_ERR_ARG; }
   CK(cudaSetDevice(b->device));
-  const size_t B = b->B, P = b->Bp;
+  const size_t P = b->Bp;
   float* d = b->d_in;
   float *dp = d, *dR = dp + 3 * P, *ddq = dR + 9 * P, *dpd = ddq + 6 * P, *ddp = dpd + 3 * P, *dsd = ddp + 3 * P, *daT = dsd + 3 * P;
-  CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dpd, pdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
   float *duq = b->d_out, *dacc = duq + 3 * P;
-  int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr);
-  if (rc) return rc;
-  CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaMemcpyAsync(accdes, dacc, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaStreamSynchronize(b->stream));
-  return UMPC_OK;
+  HostArr in[7] = {{p0, nullptr, dp, 3}, {R0, nullptr, dR, 9}, {dq0, nullptr, ddq, 6}, {pdes, nullptr, dpd, 3},
+                   {dpdes, nullptr, ddp, 3}, {sdes, nullptr, dsd, 3}, {actualT0, nullptr, daT, 1}};
+  HostArr out[2] = {{nullptr, uquad, duq, 3}, {nullptr, accdes, dacc, 6}};
+  const float* din[6] = {dp, dR, ddq, dpd, ddp, dsd};
+  return run_chunked(b, in, 7, out, 2, duq, dacc, din, actualT0 ? daT : nullptr, nullptr, nullptr, nullptr);
 }
 
 // umpcUpdate + torque clip + quadrotorNLDyn for B environments with HOST buffers: the batched twin of
@@ -774,28 +806,18 @@ extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float
     return UMPC_ERR_ARG;
   }
   CK(cudaSetDevice(b->device));
-  const size_t B = b->B, P = b->Bp;
+  const size_t P = b->Bp;
   if (!b->d_next) CK(cudaMalloc(&b->d_next, (size_t)18 * P * sizeof(float)));
   float* d = b->d_in;
   float *dp = d, *dR = dp + 3 * P, *ddq = dR + 9 * P, *dpd = ddq + 6 * P, *ddp = dpd + 3 * P, *dsd = ddp + 3 * P, *daT = dsd + 3 * P;
-  CK(cudaMemcpyAsync(dp, p0, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dR, R0, 9 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(ddq, dq0, 6 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dpd, pdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(ddp, dpdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(dsd, sdes, 3 * B * 4, cudaMemcpyHostToDevice, b->stream));
-  if (actualT0) CK(cudaMemcpyAsync(daT, actualT0, B * 4, cudaMemcpyHostToDevice, b->stream));
   float *duq = b->d_out, *dacc = duq + 3 * P;
   float *dpn = b->d_next, *dRn = dpn + 3 * P, *ddqn = dRn + 9 * P;
-  int rc = launch_update(b, duq, dacc, dp, dR, ddq, dpd, ddp, dsd, actualT0 ? daT : nullptr, dpn, dRn, ddqn);
-  if (rc) return rc;
-  CK(cudaMemcpyAsync(uquad, duq, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaMemcpyAsync(accdes, dacc, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaMemcpyAsync(p_next, dpn, 3 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaMemcpyAsync(R_next, dRn, 9 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaMemcpyAsync(dq_next, ddqn, 6 * B * 4, cudaMemcpyDeviceToHost, b->stream));
-  CK(cudaStreamSynchronize(b->stream));
-  return UMPC_OK;
+  HostArr in[7] = {{p0, nullptr, dp, 3}, {R0, nullptr, dR, 9}, {dq0, nullptr, ddq, 6}, {pdes, nullptr, dpd, 3},
+                   {dpdes, nullptr, ddp, 3}, {sdes, nullptr, dsd, 3}, {actualT0, nullptr, daT, 1}};
+  HostArr out[5] = {{nullptr, uquad, duq, 3}, {nullptr, accdes, dacc, 6}, {nullptr, p_next, dpn, 3}, {nullptr, R_next, dRn, 9},
+                    {nullptr, dq_next, ddqn, 6}};
+  const float* din[6] = {dp, dR, ddq, dpd, ddp, dsd};
+  return run_chunked(b, in, 7, out, 5, duq, dacc, din, actualT0 ? daT : nullptr, dpn, dRn, ddqn);
 }
 
 // SoA [k][B] on device <-> [B][k] on host (diagnostics / state exchange; not on the hot path)
