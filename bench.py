@@ -147,6 +147,12 @@ def main():
     ap.add_argument("--tpb", type=int, default=0, help="threads per block override (tuning)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--hl-interval", type=float, default=None,
+                    help="MPC period in ms (controlTest's hlInterval; config 1 uses 5): a step then advances every env by one "
+                         "MPC period (26 plant steps at 5 ms) in one launch.  Extra measurement; the headline line uses None")
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp"],
+                    help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
+                         "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -174,7 +180,17 @@ def main():
     p, R, dq = fast_ics(nenv * world, seed=0)
     lo, hi = shard_range(nenv * world, rank, world)
     p, R, dq = p[lo:hi], R[lo:hi], dq[lo:hi]
-    b = BatchUMPC(nenv, device=local)
+    kw = {}
+    if args.workload != "mc":
+        import util
+        kw = dict(wlMode=1 if args.workload == "cascade-wlcon" else 2, wl_popts=util.load_constants()["popts_waypoint"])
+        args.no_e2e = True  # the host-buffer env-step call has no WL stage
+    spl = 1  # plant steps per launch
+    if args.hl_interval is not None:
+        kw["hlInterval"] = args.hl_interval
+        spl = int(np.floor(args.hl_interval / 0.2 + 1e-9)) + 1  # t - thlPrev > hlInterval on a 0.2 ms grid
+        args.no_e2e = True
+    b = BatchUMPC(nenv, device=local, **kw)
     if args.tpb:
         b.set_launch(args.tpb)
     b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
@@ -187,7 +203,7 @@ def main():
 
     # ---- device-resident leg ------------------------------------------------------------------
     for _ in range(args.warmup):
-        b.rollout(1, sync=False)
+        b.rollout(spl, sync=False)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -196,7 +212,7 @@ def main():
     t0 = time.perf_counter()
     b.timer_start()
     for _ in range(args.steps):
-        b.rollout(1, sync=False)
+        b.rollout(spl, sync=False)
     dev_s = b.timer_stop_ms() * 1e-3
     barrier()
     wall = time.perf_counter() - t0
@@ -235,7 +251,7 @@ def main():
 
     if rank == 0:
         fl = F.our_flops(50)
-        per_launch_flops = (fl["total"] + F.DYN_STEP_FLOPS) * nenv
+        per_launch_flops = (fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
         launch_s = dev_s / args.steps
         peak_tf = b.lib.umpcMeasureFp32Peak(local, 4096)
         achieved_tf = per_launch_flops / launch_s * 1e-12
@@ -257,10 +273,14 @@ def main():
                             "frac": F.BYTES_PER_SOLVE * nenv / launch_s * 1e-9 / hbm_peak,
                             "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"},
                     "ref_algorithm_equiv_tflops": F.reference_algorithm_flops(50) * nenv / launch_s * 1e-12}
-        line = {"metric": METRIC, "value": nenv * world * args.steps / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        line = {"metric": METRIC, "value": spl * nenv * world * args.steps / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(world, nenv),
-                "qp_solves_per_s": nenv * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall / args.steps,
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": dict(workload_config(world, nenv), **({} if args.workload == "mc" else {
+                    "workload": "BASELINE configs[3] shape: %d-env cascade per GPU, UprightMPC2 -> %s -> actualT0 feedback every "
+                                "env-step (robobee_test_controllers.py:162-171), WaypointHover constants" % (
+                                    nenv, "WLCon" if args.workload == "cascade-wlcon" else "true WLQP (40 iterations)")})),
+                "plant_steps_per_launch": spl, "qp_solves_per_s": nenv * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall / args.steps,
                 "gpu_launches": args.steps, "clocks": clocks, "roofline": roofline,
                 "tracking": {"mean_err_mm2": sums[0] / max(sums[3], 1), "mean_eff": sums[1] / max(sums[3], 1),
                              "env_steps_total": sums[3], "non_finite_envs": sums[4]}}
