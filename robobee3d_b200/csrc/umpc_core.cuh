@@ -38,6 +38,15 @@
 #define UMPC_HD inline
 #endif
 
+// Scalar type of the whole update.  float: the C path (uprightmpc2.c is float32 throughout).  double: the Python
+// path (osqp on float64 numpy) -- a translation unit that wants it defines UMPC_REAL double and includes this header
+// inside a namespace of its own (umpc_conv.cu), so both builds can live in one library.
+#ifndef UMPC_REAL
+#define UMPC_REAL float
+#define UMPC_REAL_IS_FLOAT 1
+#endif
+typedef UMPC_REAL ureal;
+
 #define UMPC_NX 45
 #define UMPC_NC 39
 #define UMPC_NEQ 36
@@ -52,54 +61,89 @@
 // Controller parameters (what umpcInit derives, uprightmpc2.c:19-63,116-117) plus the
 // OSQP settings baked into the generated workspace (uprightmpc2/workspace.c:561).
 struct UmpcParams {
-  float dt, g, Tmax;
-  float Qyr[6], Qyf[6], Qdyr[6], Qdyf[6], R[3];
-  float Ibi[3];
+  ureal dt, g, Tmax;
+  ureal Qyr[6], Qyf[6], Qdyr[6], Qdyf[6], R[3];
+  ureal Ibi[3];
   int max_iter;
-  float rho, sigma, alpha, eps_abs, eps_rel;
+  ureal rho, sigma, alpha, eps_abs, eps_rel;
   int scaling_iters;
+  // converged mode (the Python path's OSQP settings, template_controllers.py:190-191): 0 = the C path (uprightmpc2.c:116-117)
+  int check_termination;      // test the residuals every this many iterations and stop when below eps
+  int adaptive_rho_interval;  // re-estimate rho every this many iterations (auxil.c:13-75), refactor when it moves x5
+  ureal adaptive_rho_tol;
 };
 
 // unscaled A0 values that change per update (Ax_data, uprightmpc2.c:160-179)
 struct UmpcAVals {
-  float dt, dtT0, ds[3], db[6];
-  float abs_dt, abs_dtT0, abs_ds0, abs_ds1, abs_ds2, abs_db0, abs_db1, abs_db2, abs_db3, abs_db4, abs_db5;
+  ureal dt, dtT0, ds[3], db[6];
+  ureal abs_dt, abs_dtT0, abs_ds0, abs_ds1, abs_ds2, abs_db0, abs_db1, abs_db2, abs_db3, abs_db4, abs_db5;
 };
 
 // reciprocal / reciprocal square root: MUFU approximations (1-2 ulp) on the device instead of the
-// IEEE division + sqrt slow paths; the host build (tests/hostcheck) keeps the exact forms.
-#if defined(__CUDA_ARCH__)
+// IEEE division + sqrt slow paths; the host build (tests/hostcheck) and the double build keep the exact forms.
+#if defined(__CUDA_ARCH__) && defined(UMPC_REAL_IS_FLOAT)
 #define UMPC_RCP(x) __fdividef(1.0f, (x))
 #define UMPC_RSQRT(x) rsqrtf(x)
-#else
+#elif defined(UMPC_REAL_IS_FLOAT)
 #define UMPC_RCP(x) (1.0f / (x))
 #define UMPC_RSQRT(x) (1.0f / sqrtf(x))
+#else
+#define UMPC_RCP(x) (1.0 / (x))
+#define UMPC_RSQRT(x) (1.0 / sqrt(x))
+#endif
+#ifdef UMPC_REAL_IS_FLOAT
+UMPC_HD ureal umpc_fmax(ureal a, ureal b) { return fmaxf(a, b); }
+UMPC_HD ureal umpc_fmin(ureal a, ureal b) { return fminf(a, b); }
+UMPC_HD ureal umpc_fabs(ureal a) { return fabsf(a); }
+UMPC_HD ureal umpc_sqrt(ureal a) { return sqrtf(a); }
+UMPC_HD ureal umpc_nan() { return nanf(""); }
+#else
+UMPC_HD ureal umpc_fmax(ureal a, ureal b) { return fmax(a, b); }
+UMPC_HD ureal umpc_fmin(ureal a, ureal b) { return fmin(a, b); }
+UMPC_HD ureal umpc_fabs(ureal a) { return fabs(a); }
+UMPC_HD ureal umpc_sqrt(ureal a) { return sqrt(a); }
+UMPC_HD ureal umpc_nan() { return nan(""); }
 #endif
 
 #include "umpc_gen.cuh"
 
-UMPC_HD float umpc_limit_scaling(float v) {
+UMPC_HD int umpc_imin(int a, int b) { return a < b ? a : b; }
+
+UMPC_HD ureal umpc_limit_scaling(ureal v) {
   v = v < 1e-4f ? 1.0f : v;   // MIN_SCALING (constants.h:98)
   return v > 1e4f ? 1e4f : v; // MAX_SCALING
 }
 
-// sigma / D_j^2 pairs are kept as two bf16 halves of one scratch word (8 significant bits, full float range):
-// the term is ~1e-6 of the diagonal of K, and it multiplies xh and (xh - xt) only
-UMPC_HD float umpc_pack2(float a, float b) {
+// sigma / D_j^2 pairs share one scratch word.  float build: two bf16 halves (8 significant bits, full float range);
+// double build: two floats.  The term is ~1e-6 of the diagonal of K, and it multiplies xh and (xh - xt) only.
+#ifdef UMPC_REAL_IS_FLOAT
+UMPC_HD ureal umpc_pack2(ureal a, ureal b) {
   union { float f; unsigned u; } ua, ub, r;
   ua.f = a; ub.f = b;
   r.u = (ua.u >> 16) | (ub.u & 0xffff0000u);
   return r.f;
 }
-UMPC_HD void umpc_unpack2(float w, float& a, float& b) {
+UMPC_HD void umpc_unpack2(ureal w, ureal& a, ureal& b) {
   union { float f; unsigned u; } uw, ua, ub;
   uw.f = w;
   ua.u = uw.u << 16; ub.u = uw.u & 0xffff0000u;
   a = ua.f; b = ub.f;
 }
+#else
+UMPC_HD ureal umpc_pack2(ureal a, ureal b) {
+  union { double d; float f[2]; } r;
+  r.f[0] = (float)a; r.f[1] = (float)b;
+  return r.d;
+}
+UMPC_HD void umpc_unpack2(ureal w, ureal& a, ureal& b) {
+  union { double d; float f[2]; } r;
+  r.d = w;
+  a = (ureal)r.f[0]; b = (ureal)r.f[1];
+}
+#endif
 
 // diagonal of P0 (updateObjective, uprightmpc2.c:182-207)
-UMPC_HD float umpc_px(const UmpcParams& par, int j) {
+UMPC_HD ureal umpc_px(const UmpcParams& par, int j) {
   if (j < 12) return par.Qyr[j % 6];
   if (j < 18) return par.Qyf[j % 6];
   if (j < 30) return par.Qdyr[j % 6];
@@ -110,18 +154,18 @@ UMPC_HD float umpc_px(const UmpcParams& par, int j) {
 // QP data of one update in unscaled form: A0 values, bounds, references.
 struct UmpcQP {
   UmpcAVals a;
-  float lo[UMPC_NC];  // l (== u on rows 0..35)
-  float hi_thr;       // u on rows 36..38
-  float yd[6], dyd[6];
+  ureal lo[UMPC_NC];  // l (== u on rows 0..35)
+  ureal hi_thr;       // u on rows 36..38
+  ureal yd[6], dyd[6];
 };
 
 // template projection (uprightmpc2.c:219-241) + umpcUpdateConstraint (uprightmpc2.c:126-180)
-UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const float p0[3], const float R0[9], const float dq0[6],
-                        const float pdes[3], const float dpdes[3], const float sdes[3], float T0) {
-  const float dt = par.dt;
-  float s0[3], ds0[3], y0[6], dy0[6], y1[6];
+UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const ureal p0[3], const ureal R0[9], const ureal dq0[6],
+                        const ureal pdes[3], const ureal dpdes[3], const ureal sdes[3], ureal T0) {
+  const ureal dt = par.dt;
+  ureal s0[3], ds0[3], y0[6], dy0[6], y1[6];
   UmpcAVals& a = qp.a;
-  const float w0 = dq0[3], w1 = dq0[4];
+  const ureal w0 = dq0[3], w1 = dq0[4];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     s0[i] = R0[6 + i];
@@ -137,10 +181,10 @@ UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const float p0[3], co
     qp.dyd[i] = dpdes[i]; qp.dyd[3 + i] = 0.0f;
   }
   a.dt = dt; a.dtT0 = dt * T0;
-  a.abs_dt = fabsf(a.dt); a.abs_dtT0 = fabsf(a.dtT0);
-  a.abs_ds0 = fabsf(a.ds[0]); a.abs_ds1 = fabsf(a.ds[1]); a.abs_ds2 = fabsf(a.ds[2]);
-  a.abs_db0 = fabsf(a.db[0]); a.abs_db1 = fabsf(a.db[1]); a.abs_db2 = fabsf(a.db[2]);
-  a.abs_db3 = fabsf(a.db[3]); a.abs_db4 = fabsf(a.db[4]); a.abs_db5 = fabsf(a.db[5]);
+  a.abs_dt = umpc_fabs(a.dt); a.abs_dtT0 = umpc_fabs(a.dtT0);
+  a.abs_ds0 = umpc_fabs(a.ds[0]); a.abs_ds1 = umpc_fabs(a.ds[1]); a.abs_ds2 = umpc_fabs(a.ds[2]);
+  a.abs_db0 = umpc_fabs(a.db[0]); a.abs_db1 = umpc_fabs(a.db[1]); a.abs_db2 = umpc_fabs(a.db[2]);
+  a.abs_db3 = umpc_fabs(a.db[3]); a.abs_db4 = umpc_fabs(a.db[4]); a.abs_db5 = umpc_fabs(a.db[5]);
 #pragma unroll
   for (int i = 0; i < UMPC_NC; ++i) qp.lo[i] = 0.0f;
 #pragma unroll
@@ -150,9 +194,9 @@ UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const float p0[3], co
   }
 #pragma unroll
   for (int i = 0; i < 6; ++i) {
-    const float c0 = (i == 2) ? -par.g : 0.0f;
-    const float A0y0 = i < 3 ? T0 * y0[i + 3] : 0.0f;
-    const float A0y1 = i < 3 ? T0 * y1[i + 3] : 0.0f;
+    const ureal c0 = (i == 2) ? -par.g : 0.0f;
+    const ureal A0y0 = i < 3 ? T0 * y0[i + 3] : 0.0f;
+    const ureal A0y1 = i < 3 ? T0 * y1[i + 3] : 0.0f;
     qp.lo[18 + i] = -dy0[i] - dt * A0y0 - dt * c0;
     qp.lo[24 + i] = -dt * A0y1 - dt * c0;
     qp.lo[30 + i] = -dt * c0;
@@ -164,14 +208,14 @@ UMPC_HD void umpc_build(const UmpcParams& par, UmpcQP& qp, const float p0[3], co
 
 // the reference's public QP vectors (UprightMPC_t.l/u/q/Px_data/Ax_data, uprightmpc2.h:36-40),
 // out = l[39] u[39] q[45] Px[45] Ax_data[48]  (vectors()/matrices(), py/uprightmpc2py.cpp:46-51)
-UMPC_HD void umpc_qpdata(const UmpcParams& par, const UmpcQP& qp, float* out) {
+UMPC_HD void umpc_qpdata(const UmpcParams& par, const UmpcQP& qp, ureal* out) {
   for (int i = 0; i < UMPC_NC; ++i) {
     out[i] = qp.lo[i];
     out[UMPC_NC + i] = i < UMPC_NEQ ? qp.lo[i] : qp.hi_thr;
   }
-  float* q = out + 2 * UMPC_NC;
-  float* Px = q + UMPC_NX;
-  float* Ax = Px + UMPC_NX;
+  ureal* q = out + 2 * UMPC_NC;
+  ureal* Px = q + UMPC_NX;
+  ureal* Ax = Px + UMPC_NX;
   for (int j = 0; j < UMPC_NX; ++j) {
     Px[j] = umpc_px(par, j);
     q[j] = j < 36 ? -Px[j] * (j < 18 ? qp.yd[j % 6] : qp.dyd[j % 6]) : 0.0f;
@@ -185,7 +229,7 @@ UMPC_HD void umpc_qpdata(const UmpcParams& par, const UmpcQP& qp, float* out) {
 
 struct UmpcInfo {
   int iter, status;
-  float pri_res, dua_res;
+  ureal pri_res, dua_res;
 };
 
 // Per-QP scratch the iterations re-read every pass (ST).  The kernels back it with shared memory (and a few
@@ -219,7 +263,7 @@ struct UmpcInfo {
 // a constant: w is replaced by a second start vector Vf right after the first right-hand side is formed,
 //     w0 = kappa + A_eq'(W zh0 - yh0),   wf = kappa + A_eq'((2 - alpha) W l - yh0 - (1 - alpha) W zh0),
 //     kappa = c P0 (ydes - xp) - A_eq' W l ,   w1 = wf - alpha w0 + (rest of the update).
-UMPC_HD float umpc_lo_eq(const UmpcParams& par, int i, float stored) {
+UMPC_HD ureal umpc_lo_eq(const UmpcParams& par, int i, ureal stored) {
   // rows 6..17 are 0 and rows 30..35 are -dt*c0 (uprightmpc2.c:139-152): no load needed
   if (i >= 6 && i < 18) return 0.0f;
   if (i >= 30) return i == 32 ? par.dt * par.g : 0.0f;
@@ -227,15 +271,15 @@ UMPC_HD float umpc_lo_eq(const UmpcParams& par, int i, float stored) {
 }
 
 // c * P0_j * ref_j : the constant part of -c q0 (q0 = -P0 .* [ydes x3, dydes x3, 0 x9], uprightmpc2.c:182-207)
-UMPC_HD float umpc_ref(const float (&yd)[6], const float (&dyd)[6], int j) {
+UMPC_HD ureal umpc_ref(const ureal (&yd)[6], const ureal (&dyd)[6], int j) {
   return j < 18 ? yd[j % 6] : (j < 36 ? dyd[j % 6] : 0.0f);
 }
 
-template <class ST, class IO>
-UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], float accdes[6], const float p0[3],
-                         const float R0[9], const float dq0[6], const float pdes[3], const float dpdes[3],
-                         const float sdes[3], float actualT0, float& T0, UmpcInfo& info) {
-  const float dt = par.dt;
+template <bool CONV, class ST, class IO>
+UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], ureal accdes[6], const ureal p0[3],
+                         const ureal R0[9], const ureal dq0[6], const ureal pdes[3], const ureal dpdes[3],
+                         const ureal sdes[3], ureal actualT0, ureal& T0, UmpcInfo& info) {
+  const ureal dt = par.dt;
   if (actualT0 >= 0.0f) T0 = actualT0;
   io.prefetch_warm_start();  // xs/zs/ys are needed only after Ruiz + factor: start pulling them into L2 now
   // The 28 inputs are needed again only after the ADMM loop (bounds for the un-shift, R0/dq0 for accdes): park
@@ -249,8 +293,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   for (int i = 0; i < 6; ++i) io.stash(12 + i, dq0[i]);
   io.stash(27, T0);
   UmpcAVals a;
-  float yd[6], dyd[6], lo_thr, hi_thr;
-  float qp_lo[18];  // run-time equality bounds: rows 0..5 and 18..29
+  ureal yd[6], dyd[6], lo_thr, hi_thr;
+  ureal qp_lo[18];  // run-time equality bounds: rows 0..5 and 18..29
   {
     UmpcQP qp;
     umpc_build(par, qp, p0, R0, dq0, pdes, dpdes, sdes, T0);
@@ -265,65 +309,70 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
   }
 #define UMPC_LO(i) umpc_lo_eq(par, (i), qp_lo[(i) < 6 ? (i) : ((i) >= 18 && (i) < 30 ? (i) - 12 : 0)])
   // ---- constraint type of the thrust rows with the OLD scaling (auxil.c:103-146) --------
-  float W3[3], Wi3[3];
+  ureal W3[3], Wi3[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    const float eo = io.ld_E(UMPC_NEQ + k);
-    const float ls_ = eo * lo_thr, us_ = eo * hi_thr;
-    W3[k] = (us_ - ls_ < 1e-4f) ? 1e3f * par.rho : par.rho;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ (constants.h:69-71)
+    const ureal eo = io.ld_E(UMPC_NEQ + k);
+    const ureal ls_ = eo * lo_thr, us_ = eo * hi_thr;
+    W3[k] = (us_ - ls_ < 1e-4f) ? 1e3f : 1.0f;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ (constants.h:69-71): factor of rho for now
   }
-  const float rho_eq = 1e3f * par.rho;
-  const float alpha = par.alpha, oma = 1.0f - par.alpha;
+  // rho is per-controller state: osqp_update_rho writes settings->rho, which later solves inherit (osqp.c:1270-1330)
+  ureal rho = CONV ? io.ld_rho() : par.rho;
+  const ureal thr_mult[3] = {W3[0], W3[1], W3[2]};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) W3[k] *= rho;
+  const ureal rho_eq = 1e3f * rho;
+  const ureal alpha = par.alpha, oma = 1.0f - par.alpha;
 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
-  float c = 1.0f;
-  float xs[UMPC_NX], w[UMPC_NEQ], kpu[UMPC_NX - UMPC_NEQ], z3[3], y3[3];
+  ureal c = 1.0f;
+  ureal xs[UMPC_NX], w[UMPC_NEQ], kpu[UMPC_NX - UMPC_NEQ], z3[3], y3[3];
   {
-    float D[UMPC_NX], E[UMPC_NC];
+    ureal D[UMPC_NX], E[UMPC_NC];
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) D[j] = 1.0f;
 #pragma unroll
     for (int i = 0; i < UMPC_NC; ++i) E[i] = 1.0f;
     for (int it = 0; it < par.scaling_iters; ++it) {
       st.sync();  // keep the warps of a CTA on the same code (shared instruction fetch), see TmemStore::sync
-      float cn[UMPC_NX], rn[UMPC_NC];
+      ureal cn[UMPC_NX], rn[UMPC_NC];
       umpc_gen_norms(cn, rn, D, E, a);
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float pc = c * umpc_px(par, j) * D[j] * D[j];
-        const float nj = fmaxf(pc, cn[j] * D[j]);
+        const ureal pc = c * umpc_px(par, j) * D[j] * D[j];
+        const ureal nj = umpc_fmax(pc, cn[j] * D[j]);
         D[j] *= UMPC_RSQRT(umpc_limit_scaling(nj));
       }
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) E[i] *= UMPC_RSQRT(umpc_limit_scaling(rn[i] * E[i]));
       // cost normalisation (scaling.c:100-131)
-      float psum = 0.0f, nq = 0.0f;
+      ureal psum = 0.0f, nq = 0.0f;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float px = umpc_px(par, j);
+        const ureal px = umpc_px(par, j);
         psum += c * px * D[j] * D[j];
-        if (j < 36) nq = fmaxf(nq, fabsf(c * D[j] * px * umpc_ref(yd, dyd, j)));
+        if (j < 36) nq = umpc_fmax(nq, umpc_fabs(c * D[j] * px * umpc_ref(yd, dyd, j)));
       }
-      float ct = psum * (1.0f / UMPC_NX);
-      ct = fmaxf(ct, umpc_limit_scaling(nq));
+      ureal ct = psum * (1.0f / UMPC_NX);
+      ct = umpc_fmax(ct, umpc_limit_scaling(nq));
       ct = umpc_limit_scaling(ct);
       c *= UMPC_RCP(ct);
     }
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
     {
       st.sync();
-      float G[UMPC_NX], W[UMPC_NC], sgv[UMPC_NX + 1];
+      ureal G[UMPC_NX], W[UMPC_NC], sgv[UMPC_NX + 1];
       sgv[UMPC_NX] = 0.0f;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float sg = par.sigma * UMPC_RCP(D[j] * D[j]);
+        const ureal sg = par.sigma * UMPC_RCP(D[j] * D[j]);
         sgv[j] = sg;
         G[j] = c * umpc_px(par, j) + sg;
         io.st_D(j, D[j]);
       }
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) {
-        const float rho_i = i < UMPC_NEQ ? rho_eq : W3[i - UMPC_NEQ];
+        const ureal rho_i = i < UMPC_NEQ ? rho_eq : W3[i - UMPC_NEQ];
         W[i] = rho_i * E[i] * E[i];
         io.st_E(i, E[i]);
       }
@@ -336,19 +385,19 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       // All global loads are issued before any global store (the compiler cannot move a load across
       // a store that might alias, and a load -> store -> load chain exposes the full memory latency
       // once per element).
-      float zs0[UMPC_NC], ys0[UMPC_NC];
+      ureal zs0[UMPC_NC], ys0[UMPC_NC];
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) { zs0[i] = io.ld_zs(i); ys0[i] = io.ld_ys(i); }
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) xs[j] = io.ld_xs(j);
-      float lo[UMPC_NEQ], xp[UMPC_NX];
+      ureal lo[UMPC_NEQ], xp[UMPC_NX];
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) lo[i] = UMPC_LO(i);
       umpc_gen_xp(xp, lo, a);
-      float v0[UMPC_NC], vf[UMPC_NC];  // minus W l: the -b of kappa rides along
+      ureal v0[UMPC_NC], vf[UMPC_NC];  // minus W l: the -b of kappa rides along
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) {
-        const float zh = zs0[i] * UMPC_RCP(E[i]), yh = ys0[i] * E[i];
+        const ureal zh = zs0[i] * UMPC_RCP(E[i]), yh = ys0[i] * E[i];
         v0[i] = W[i] * (zh - lo[i]) - yh;
         vf[i] = oma * W[i] * (lo[i] - zh) - yh;   // (2 - alpha) W l - yh - (1 - alpha) W zh - W l
       }
@@ -360,10 +409,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
         W3[k] = W[UMPC_NEQ + k];
         Wi3[k] = UMPC_RCP(W3[k]);
       }
-      float w0[UMPC_NX], wf[UMPC_NX], kapo[UMPC_NEQ];
+      ureal w0[UMPC_NX], wf[UMPC_NX], kapo[UMPC_NEQ];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float kap = c * umpc_px(par, j) * (umpc_ref(yd, dyd, j) - xp[j]);  // 0 on the input columns
+        const ureal kap = c * umpc_px(par, j) * (umpc_ref(yd, dyd, j) - xp[j]);  // 0 on the input columns
         w0[j] = kap; wf[j] = kap;
         if (j < UMPC_NEQ) kapo[j] = kap;
         xs[j] = xs[j] * D[j] - xp[j];
@@ -378,34 +427,48 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
       // The first pass forms r with w0 but must continue from wf:  w1 = wf - alpha w0 + t  (t = the rest of the
       // update).  Written as the regular update (1 - alpha) X + t of a substitute X = (wf - alpha w0) / (1 - alpha),
       // so that the loop body has no first-iteration special case beyond swapping w (alpha != 1: OSQP's 1.6).
-      const float ioma = 1.0f / oma;
+      const ureal ioma = 1.0f / oma;
 #pragma unroll
       for (int j = 0; j < UMPC_NEQ; ++j) { w[j] = w0[j]; st.setVf(j, (wf[j] - alpha * w0[j]) * ioma); }
     }
   }
   // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
-  const float ac = alpha * c;
-  const int niter = par.max_iter < 1 ? 1 : par.max_iter;
-  for (int it = 0; it < niter; ++it) {
+  const ureal ac = alpha * c;
+  const int max_iter = par.max_iter < 1 ? 1 : par.max_iter;
+  // One SEGMENT of iterations, then the residuals.  C path (check_termination = 0): a single segment of max_iter
+  // iterations.  Converged mode: segments of check_termination iterations until the lane's residuals pass
+  // (osqp.c:431-470); a lane that has converged commits its solution at that point and idles along until the
+  // whole warp is done (the scratch requests are warp-collective, so the trip count must be warp-uniform).
+  // CONV is a compile-time flag: the C path's instantiation carries none of this.
+  const int chk_every = CONV ? par.check_termination : 0;
+  const int rho_every = CONV ? par.adaptive_rho_interval : 0;
+  int iter_done = 0;
+  bool done = false;
+  for (;;) {
+  int next_stop = max_iter;  // next iteration count at which the residuals are needed
+  if (chk_every > 0) next_stop = umpc_imin(next_stop, (iter_done / chk_every + 1) * chk_every);
+  if (rho_every > 0) next_stop = umpc_imin(next_stop, (iter_done / rho_every + 1) * rho_every);
+  const int nseg = next_stop - iter_done;
+  for (int it = 0; it < nseg; ++it) {
     st.begin_iteration(it);
     st.sync();
-    float r[UMPC_NX];
-    float m3[3];
+    ureal r[UMPC_NX];
+    ureal m3[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) m3[k] = W3[k] * z3[k] - y3[k];
     // input-column part of w, re-derived from the own-column part every pass: g stays exactly in range(A_eq')
-    float wu[UMPC_NX - UMPC_NEQ];
+    ureal wu[UMPC_NX - UMPC_NEQ];
     umpc_gen_gu_from_go(wu, w, a);
 #pragma unroll
     for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) wu[i] += kpu[i];
 #pragma unroll
     for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
-      float wd[UMPC_GEN_CHUNK];
+      ureal wd[UMPC_GEN_CHUNK];
       st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
       st.wait(wd);
 #pragma unroll
       for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
-        float s2[2];
+        ureal s2[2];
         if (2 * (UMPC_GEN_CHUNK * gq + u) < UMPC_NX) umpc_unpack2(wd[u], s2[0], s2[1]);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -416,27 +479,27 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) r[36 + 3 * k] += m3[k];
-    if (it == 0) {
+    if (iter_done + it == 0) {
 #pragma unroll
       for (int j = 0; j < UMPC_NEQ; ++j) w[j] = st.Vf(j);
     }
     umpc_gen_solve(r, st);
 #pragma unroll
     for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
-      float wd[UMPC_GEN_CHUNK];
+      ureal wd[UMPC_GEN_CHUNK];
       st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
       st.wait(wd);
 #pragma unroll
       for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
-        float s2[2];
+        ureal s2[2];
         if (2 * (UMPC_GEN_CHUNK * gq + u) < UMPC_NX) umpc_unpack2(wd[u], s2[0], s2[1]);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int j = 2 * (UMPC_GEN_CHUNK * gq + u) + h;
           if (j < UMPC_NX) {
-            const float d = xs[j] - r[j];
+            const ureal d = xs[j] - r[j];
             if (j < UMPC_NEQ) {
-              const float t = (ac * umpc_px(par, j)) * r[j] - alpha * (s2[h] * d);
+              const ureal t = (ac * umpc_px(par, j)) * r[j] - alpha * (s2[h] * d);
               w[j < UMPC_NEQ ? j : 0] = oma * w[j < UMPC_NEQ ? j : 0] + t;
             }
             xs[j] -= alpha * d;
@@ -446,22 +509,22 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      const float t = alpha * r[36 + 3 * k] + oma * z3[k];
-      const float zn = fminf(fmaxf(t + Wi3[k] * y3[k], lo_thr), hi_thr);
+      const ureal t = alpha * r[36 + 3 * k] + oma * z3[k];
+      const ureal zn = umpc_fmin(umpc_fmax(t + Wi3[k] * y3[k], lo_thr), hi_thr);
       y3[k] += W3[k] * (t - zn);
       z3[k] = zn;
     }
   }
+  iter_done += nseg;
   // ---- back to un-shifted coordinates; equality-row duals from g = w - kappa ----------------
-  float solx_u[3], solx_dy1[6];
-  float R0b[9], dq0b[6];
   st.sync();
+  bool again = false;
   {
-    float zs[UMPC_NC], ys[UMPC_NC];
-    float qp_lo[18], yd[6], dyd[6];
+    ureal zs[UMPC_NC], ys[UMPC_NC], xf[UMPC_NX];  // xf: the iterate in un-shifted coordinates
+    ureal qp_lo[18], yd[6], dyd[6], R0b[9], dq0b[6];
     UmpcAVals a;
     {
-      float p0b[3], pdb[3], dpdb[3], sdb[3];
+      ureal p0b[3], pdb[3], dpdb[3], sdb[3];
 #pragma unroll
       for (int i = 0; i < 3; ++i) { p0b[i] = io.unstash(i); pdb[i] = io.unstash(18 + i); dpdb[i] = io.unstash(21 + i); sdb[i] = io.unstash(24 + i); }
 #pragma unroll
@@ -476,22 +539,22 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
 #pragma unroll
       for (int i = 18; i < 30; ++i) qp_lo[i - 12] = qp.lo[i];
     }
-    float Dl[UMPC_NX], El[UMPC_NC];  // global loads first, stores after (see the warm-start note)
+    ureal Dl[UMPC_NX], El[UMPC_NC];  // global loads first, stores after (see the warm-start note)
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) Dl[j] = io.ld_D(j);
 #pragma unroll
     for (int i = 0; i < UMPC_NC; ++i) El[i] = io.ld_E(i);
     {
-      float lo[UMPC_NEQ], xp[UMPC_NX], v[UMPC_NEQ];
+      ureal lo[UMPC_NEQ], xp[UMPC_NX], v[UMPC_NEQ];
 #pragma unroll
       for (int i = 0; i < UMPC_NEQ; ++i) lo[i] = UMPC_LO(i);
       umpc_gen_xp(xp, lo, a);
-      float g[UMPC_NX];
+      ureal g[UMPC_NX];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
         // own columns of g - b = A_eq'(v - W l); the input columns are not read by the substitution
         g[j] = j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] - c * umpc_px(par, j) * (umpc_ref(yd, dyd, j) - xp[j]) : 0.0f;
-        xs[j] += xp[j];
+        xf[j] = xs[j] + xp[j];
       }
       umpc_gen_v_from_g(v, g, a);  // v - W l
 #pragma unroll
@@ -501,71 +564,110 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, float uquad[3], 
     for (int k = 0; k < 3; ++k) { zs[UMPC_NEQ + k] = z3[k]; ys[UMPC_NEQ + k] = y3[k]; }
     // ---- residuals, status (update_info + check_termination, auxil.c:567-790) ---------------
     st.sync();
-    float pri = 0.0f, nz = 0.0f, nAx = 0.0f;
+    // un-scaled norms for the termination test; scaled ones (E, D weighted) for the rho estimate (auxil.c:13-75
+    // works on the scaled residual vectors left in z_prev / x_prev)
+    const bool adapt = rho_every > 0;
+    ureal pri = 0.0f, nz = 0.0f, nAx = 0.0f, pri_s = 0.0f, pn_s = 0.0f;
     {
-      float Ax[UMPC_NC];
-      umpc_gen_Ax(Ax, xs, a);
+      ureal Ax[UMPC_NC];
+      umpc_gen_Ax(Ax, xf, a);
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) {
-        pri = fmaxf(pri, fabsf(Ax[i] - zs[i]));
-        nz = fmaxf(nz, fabsf(zs[i]));
-        nAx = fmaxf(nAx, fabsf(Ax[i]));
+        pri = umpc_fmax(pri, umpc_fabs(Ax[i] - zs[i]));
+        nz = umpc_fmax(nz, umpc_fabs(zs[i]));
+        nAx = umpc_fmax(nAx, umpc_fabs(Ax[i]));
+        if (adapt) {
+          pri_s = umpc_fmax(pri_s, umpc_fabs(El[i] * (Ax[i] - zs[i])));
+          pn_s = umpc_fmax(pn_s, El[i] * umpc_fmax(umpc_fabs(zs[i]), umpc_fabs(Ax[i])));
+        }
       }
     }
-    float dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f;
+    ureal dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f, dua_s = 0.0f, dn_s = 0.0f;
     {
-      float Aty[UMPC_NX];
+      ureal Aty[UMPC_NX];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
       umpc_gen_ATv_add(Aty, ys, a);
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const float px = c * umpc_px(par, j) * xs[j];
-        const float qj = -c * umpc_px(par, j) * umpc_ref(yd, dyd, j);
-        dua = fmaxf(dua, fabsf(px + qj + Aty[j]));
-        nq = fmaxf(nq, fabsf(qj)); nAty = fmaxf(nAty, fabsf(Aty[j])); nPx = fmaxf(nPx, fabsf(px));
+        const ureal px = c * umpc_px(par, j) * xf[j];
+        const ureal qj = -c * umpc_px(par, j) * umpc_ref(yd, dyd, j);
+        dua = umpc_fmax(dua, umpc_fabs(px + qj + Aty[j]));
+        nq = umpc_fmax(nq, umpc_fabs(qj)); nAty = umpc_fmax(nAty, umpc_fabs(Aty[j])); nPx = umpc_fmax(nPx, umpc_fabs(px));
+        if (adapt) {
+          dua_s = umpc_fmax(dua_s, umpc_fabs(Dl[j] * (px + qj + Aty[j])));
+          dn_s = umpc_fmax(dn_s, Dl[j] * umpc_fmax(umpc_fabs(qj), umpc_fmax(umpc_fabs(Aty[j]), umpc_fabs(px))));
+        }
       }
     }
     st.sync();
-    const float cinv = UMPC_RCP(c);
+    const ureal cinv = UMPC_RCP(c);
     dua *= cinv;
-    info.iter = niter; info.pri_res = pri; info.dua_res = dua;
-    const float ep = par.eps_abs + par.eps_rel * fmaxf(nz, nAx);
-    const float ed = par.eps_abs + par.eps_rel * cinv * fmaxf(fmaxf(nq, nAty), nPx);
+    const ureal ep = par.eps_abs + par.eps_rel * umpc_fmax(nz, nAx);
+    const ureal ed = par.eps_abs + par.eps_rel * cinv * umpc_fmax(umpc_fmax(nq, nAty), nPx);
+    const bool last = iter_done >= max_iter;
+    const bool check = last || (chk_every > 0 && iter_done % chk_every == 0);
     int status;
     if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;  // OSQP_INFTY (auxil.c:706-716)
+    else if (!check) status = UMPC_ST_UNSOLVED;
     else if (pri < ep && dua < ed) status = UMPC_ST_SOLVED;
-    else if (pri < 10.0f * ep && dua < 10.0f * ed) status = UMPC_ST_SOLVED_INACCURATE;  // osqp.c:564-568
-    else status = UMPC_ST_MAX_ITER;
-    info.status = status;
+    else if (last && pri < 10.0f * ep && dua < 10.0f * ed) status = UMPC_ST_SOLVED_INACCURATE;  // osqp.c:564-568
+    else status = last ? UMPC_ST_MAX_ITER : UMPC_ST_UNSOLVED;
     // ---- store_solution (auxil.c:527-562); warm start back to OSQP's scaled coordinates ---
-    const bool bad = status == UMPC_ST_NON_CVX;
-    const float nanv = nanf("");
+    // committed once per lane: when its test passes, or at the iteration limit
+    const bool commit = !done && status != UMPC_ST_UNSOLVED;
+    if (commit) {
+      info.iter = iter_done; info.pri_res = pri; info.dua_res = dua; info.status = status;
+      const bool bad = status == UMPC_ST_NON_CVX;
+      const ureal nanv = umpc_nan();
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) {
-      const float sx = bad ? nanv : xs[j];
-      io.st_solx(j, sx);
-      io.st_xs(j, bad ? 0.0f : xs[j] * UMPC_RCP(Dl[j]));
-      if (j >= 18 && j < 24) solx_dy1[j - 18] = sx;
-      if (j >= 36 && j < 39) solx_u[j - 36] = sx;
+      for (int j = 0; j < UMPC_NX; ++j) {
+        const ureal sx = bad ? nanv : xf[j];
+        io.st_solx(j, sx);
+        io.st_xs(j, bad ? 0.0f : xf[j] * UMPC_RCP(Dl[j]));
+      }
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) {
+        const ureal e = El[i];
+        io.st_soly(i, bad ? nanv : ys[i] * cinv);
+        io.st_zs(i, bad ? 0.0f : zs[i] * e);
+        io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));
+      }
+      if (CONV) io.st_rho(rho);
+      // ---- extraction (uprightmpc2.c:252-269) ----------------------------------------------
+      const ureal nb = bad ? nanv : 0.0f;
+      T0 += xf[36] + nb;
+      uquad[0] = T0; uquad[1] = xf[37] + nb; uquad[2] = xf[38] + nb;
+      const ureal t0 = R0b[0] * xf[21] + R0b[1] * xf[22] + R0b[2] * xf[23];
+      const ureal t1 = R0b[3] * xf[21] + R0b[4] * xf[22] + R0b[5] * xf[23];
+      const ureal dq1[6] = {xf[18], xf[19], xf[20], -t1, t0, 0.0f};
+#pragma unroll
+      for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt + nb;
+      done = true;
     }
+    again = CONV && !st.all(done);
+    // ---- adaptive rho (auxil.c:13-75 + osqp_update_rho, osqp.c:1270-1330): per lane; the refactor is executed by
+    // the whole warp when any live lane moved (lanes that did not keep their rho: same factor again)
+    if (CONV && again && adapt && iter_done % rho_every == 0) {
+      const ureal pr = pri_s * UMPC_RCP(pn_s + 1e-10f), dr = dua_s * UMPC_RCP(dn_s + 1e-10f);
+      ureal est = rho * umpc_sqrt(pr * UMPC_RCP(dr + 1e-10f));
+      est = umpc_fmin(umpc_fmax(est, 1e-6f), 1e6f);  // RHO_MIN, RHO_MAX (constants.h:69-70)
+      const bool move = !done && (est > rho * par.adaptive_rho_tol || est < rho * UMPC_RCP(par.adaptive_rho_tol));
+      if (!st.all(!move)) {
+        if (move) rho = est;
+        ureal G[UMPC_NX], W[UMPC_NC];
 #pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) {
-      const float e = El[i];
-      io.st_soly(i, bad ? nanv : ys[i] * cinv);
-      io.st_zs(i, bad ? 0.0f : zs[i] * e);
-      io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));
+        for (int j = 0; j < UMPC_NX; ++j) G[j] = c * umpc_px(par, j) + par.sigma * UMPC_RCP(Dl[j] * Dl[j]);
+#pragma unroll
+        for (int i = 0; i < UMPC_NC; ++i) W[i] = (i < UMPC_NEQ ? 1e3f : thr_mult[i < UMPC_NEQ ? 0 : i - UMPC_NEQ]) * rho * El[i] * El[i];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { W3[k] = W[UMPC_NEQ + k]; Wi3[k] = UMPC_RCP(W3[k]); }
+        umpc_gen_factor(G, W, a, st);
+        st.end_writes();
+      }
     }
   }
-  // ---- extraction (uprightmpc2.c:252-269) ---------------------------------------------------
-  T0 += solx_u[0];
-  uquad[0] = T0; uquad[1] = solx_u[1]; uquad[2] = solx_u[2];
-  {
-    const float t0 = R0b[0] * solx_dy1[3] + R0b[1] * solx_dy1[4] + R0b[2] * solx_dy1[5];
-    const float t1 = R0b[3] * solx_dy1[3] + R0b[4] * solx_dy1[4] + R0b[5] * solx_dy1[5];
-    const float dq1[6] = {solx_dy1[0], solx_dy1[1], solx_dy1[2], -t1, t0, 0.0f};
-#pragma unroll
-    for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt;
+  if (!again) break;
   }
 #undef UMPC_LO
 }

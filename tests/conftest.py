@@ -16,11 +16,12 @@ def pytest_configure(config):
     if not all(os.path.exists(p) for p in need) or (os.path.isdir("/root/reference") and not binding.have_ref()):
         binding.build(ref=os.path.isdir("/root/reference"))
     hc = os.path.join(ROOT, "tests", "hostcheck")
-    so = os.path.join(hc, "libhostcheck.so")
     srcs = [os.path.join(hc, "hostcheck.cpp")] + [os.path.join(ROOT, "robobee3d_b200", "csrc", f)
                                                    for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh")]
-    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
-        subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-o", so, srcs[0]], check=True)
+    for name, defs in (("libhostcheck.so", []), ("libhostcheck64.so", ["-DUMPC_REAL=double"])):
+        so = os.path.join(hc, name)
+        if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+            subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-ffp-contract=off"] + defs + ["-o", so, srcs[0]], check=True)
 
 
 def has_cuda():

@@ -124,3 +124,37 @@ def test_device_formulation_on_host_matches_reference_golden():
             assert int(o["info"][0]) == 50
             assert np.abs(uq - gold["uquad"][e, c]).max() <= TOL_X_REL * max(1.0, np.abs(gold["x"][e, c]).max())
     print("hostcheck worst rel err vs reference C: %.2e" % worst)
+
+
+def test_converged_formulation_on_host_matches_oracle_f64():
+    """converged mode (termination test every 25 iterations, rho re-estimated every 100, osqp.c:431-500) of the device
+    code, compiled for the host in double, against the oracle's float64 OSQP restatement and the golden solutions of
+    the reference's vendored OSQP in float64: same iteration counts, solutions within 10 eps_abs + eps_rel |x*|."""
+    sys.path.insert(0, os.path.join(ROOT, "tests", "hostcheck"))
+    import hc
+    from oracle import binding as OB
+    gold = np.load(os.path.join(GOLDEN, "umpc_seq.npz"))
+    conv = np.load(os.path.join(GOLDEN, "umpc_conv.npz"))
+    d = util.load_constants()["umpc_defaults"]
+    B, ncall = gold["p"].shape[:2]
+    for e in range(0, B, 3):
+        h = hc.HostUMPC(d, f64=True)
+        h.set_converged()
+        o = OB.OracleUMPC("f64")
+        o.set_converged()
+        for c in range(ncall):
+            a = (gold["p"][e, c], gold["R"][e, c], gold["dq"][e, c], gold["pdes"][e, c], gold["dpdes"][e, c], gold["sdes"][e, c],
+                 float(gold["aT0"][e, c]))
+            uq, acc = h.update(*a)
+            uo, ao = o.update(*a)
+            g = h.get()
+            x, y, info = o.solution()
+            assert int(g["info"][0]) == info["iter"] and int(g["info"][1]) == info["status"] == 1, (e, c)
+            assert np.abs(g["x"] - x).max() <= 10 * 1e-4 + 1e-4 * np.abs(x).max()
+            assert np.abs(g["y"] - y).max() <= 10 * 1e-4 + 1e-4 * np.abs(y).max()
+            tol = 10 * 1e-4 + 1e-4 * np.abs(x).max()
+            assert np.abs(uq - uo).max() <= tol and np.abs(acc - ao).max() <= tol / d["dt"]
+            if c == 0:
+                xr = conv["x"][e]
+                assert int(g["info"][0]) == int(conv["iter"][e])
+                assert np.abs(g["x"] - xr).max() <= 10 * 1e-4 + 1e-4 * np.abs(xr).max()
