@@ -130,6 +130,14 @@ typedef struct {
   /* 1: the task's initialPos has integer dtype, as in controlTest (uprightmpc2.py:94-104 builds p with
    * np.array([0, 0, 0]); flight_tasks' in-place `posdes[i] += x` then truncates pdes toward zero). 0: float. */
   int intInitialPos;
+  /* Converged mode = the reference's PYTHON path (template_controllers.py:190-258: osqp on float64, eps_abs = eps_rel
+   * = 1e-4, OSQP's defaults otherwise).  checkTermination > 0 selects it: the batch then solves in float64, tests the
+   * residuals every checkTermination iterations (OSQP default 25), stops each QP when they pass or at maxIter (OSQP
+   * default 4000) and re-estimates rho every adaptiveRhoInterval iterations (0 = never; OSQP's automatic interval
+   * works out to 100 for this QP).  0 (default): the C path -- float32, exactly maxIter iterations (uprightmpc2.c:116-117). */
+  int checkTermination;
+  int adaptiveRhoInterval;
+  float epsAbs, epsRel; /* <= 0: 1e-4 */
 } UmpcBatchParams;
 
 void umpcBatchDefaults(UmpcBatchParams *par);

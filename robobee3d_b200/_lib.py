@@ -26,6 +26,7 @@ class UmpcBatchParams(C.Structure):
         ("wl_u0", C.c_float * 4), ("wl_umin", C.c_float * 4), ("wl_umax", C.c_float * 4), ("wl_dumax", C.c_float * 4),
         ("wl_Qw", C.c_float * 6), ("wl_controlRate", C.c_float), ("wl_popts", C.c_float * 90),
         ("wlqpCheckTermination", C.c_int), ("intInitialPos", C.c_int),
+        ("checkTermination", C.c_int), ("adaptiveRhoInterval", C.c_int), ("epsAbs", C.c_float), ("epsRel", C.c_float),
     ]
 
 

@@ -20,7 +20,8 @@ DEFAULTS = dict(dt=5.0, g=9.81e-3, TtoWmax=2.0, ws=1e1, wds=1e3, wpr=1.0, wpf=5.
                 wlMode=0, wl_u0=(140.0, 0.0, 0.0, 0.0), wl_umin=(90.0, -0.5, -0.2, -0.1),
                 wl_umax=(240.0, 0.5, 0.2, 0.1), wl_dumax=(5e3, 10.0, 10.0, 10.0),
                 wl_Qw=(1.0, 1.0, 1.0, 0.1, 0.1, 0.1), wl_controlRate=1000.0, wl_popts=None,
-                wlqpCheckTermination=25, intInitialPos=0)
+                wlqpCheckTermination=25, intInitialPos=0,
+                checkTermination=0, adaptiveRhoInterval=0, epsAbs=1e-4, epsRel=1e-4)
 
 
 def _f32(a, shape=None):
@@ -43,7 +44,8 @@ def make_params(**kw):
     p = _lib.UmpcBatchParams()
     _lib.load().umpcBatchDefaults(C.byref(p))
     for k in ("dt", "g", "TtoWmax", "ws", "wds", "wpr", "wpf", "wvr", "wvf", "wthrust", "wmom", "maxIter",
-              "dtsim", "taulim", "mb", "wlMode", "wl_controlRate", "wlqpCheckTermination", "intInitialPos"):
+              "dtsim", "taulim", "mb", "wlMode", "wl_controlRate", "wlqpCheckTermination", "intInitialPos",
+              "checkTermination", "adaptiveRhoInterval", "epsAbs", "epsRel"):
         setattr(p, k, d[k])
     p.hlInterval = -1.0 if d["hlInterval"] is None else float(d["hlInterval"])
     p.tpert = -1.0 if d["tpert"] is None else float(d["tpert"])

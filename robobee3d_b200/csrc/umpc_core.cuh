@@ -47,8 +47,10 @@
 #endif
 typedef UMPC_REAL ureal;
 
+#ifndef UMPC_NX  // also in include/umpc_b200.h
 #define UMPC_NX 45
 #define UMPC_NC 39
+#endif
 #define UMPC_NEQ 36
 
 // OSQP status values (uprightmpc2/constants.h:17-31)
@@ -317,7 +319,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     W3[k] = (us_ - ls_ < 1e-4f) ? 1e3f : 1.0f;  // RHO_TOL, RHO_EQ_OVER_RHO_INEQ (constants.h:69-71): factor of rho for now
   }
   // rho is per-controller state: osqp_update_rho writes settings->rho, which later solves inherit (osqp.c:1270-1330)
-  ureal rho = CONV ? io.ld_rho() : par.rho;
+  ureal rho = par.rho;
+  if constexpr (CONV) rho = io.ld_rho();
   const ureal thr_mult[3] = {W3[0], W3[1], W3[2]};
 #pragma unroll
   for (int k = 0; k < 3; ++k) W3[k] *= rho;
@@ -446,8 +449,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
   bool done = false;
   for (;;) {
   int next_stop = max_iter;  // next iteration count at which the residuals are needed
-  if (chk_every > 0) next_stop = umpc_imin(next_stop, (iter_done / chk_every + 1) * chk_every);
-  if (rho_every > 0) next_stop = umpc_imin(next_stop, (iter_done / rho_every + 1) * rho_every);
+  if constexpr (CONV) {
+    if (chk_every > 0) next_stop = umpc_imin(next_stop, (iter_done / chk_every + 1) * chk_every);
+    if (rho_every > 0) next_stop = umpc_imin(next_stop, (iter_done / rho_every + 1) * rho_every);
+  }
   const int nseg = next_stop - iter_done;
   for (int it = 0; it < nseg; ++it) {
     st.begin_iteration(it);
@@ -606,7 +611,8 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     const ureal ep = par.eps_abs + par.eps_rel * umpc_fmax(nz, nAx);
     const ureal ed = par.eps_abs + par.eps_rel * cinv * umpc_fmax(umpc_fmax(nq, nAty), nPx);
     const bool last = iter_done >= max_iter;
-    const bool check = last || (chk_every > 0 && iter_done % chk_every == 0);
+    bool check = last;
+    if constexpr (CONV) check = last || (chk_every > 0 && iter_done % chk_every == 0);
     int status;
     if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;  // OSQP_INFTY (auxil.c:706-716)
     else if (!check) status = UMPC_ST_UNSOLVED;
@@ -633,7 +639,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
         io.st_zs(i, bad ? 0.0f : zs[i] * e);
         io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));
       }
-      if (CONV) io.st_rho(rho);
+      if constexpr (CONV) io.st_rho(rho);
       // ---- extraction (uprightmpc2.c:252-269) ----------------------------------------------
       const ureal nb = bad ? nanv : 0.0f;
       T0 += xf[36] + nb;
@@ -645,10 +651,10 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt + nb;
       done = true;
     }
-    again = CONV && !st.all(done);
+    if constexpr (CONV) again = !st.all(done);
     // ---- adaptive rho (auxil.c:13-75 + osqp_update_rho, osqp.c:1270-1330): per lane; the refactor is executed by
     // the whole warp when any live lane moved (lanes that did not keep their rho: same factor again)
-    if (CONV && again && adapt && iter_done % rho_every == 0) {
+    if constexpr (CONV) if (again && adapt && iter_done % rho_every == 0) {
       const ureal pr = pri_s * UMPC_RCP(pn_s + 1e-10f), dr = dua_s * UMPC_RCP(dn_s + 1e-10f);
       ureal est = rho * umpc_sqrt(pr * UMPC_RCP(dr + 1e-10f));
       est = umpc_fmin(umpc_fmax(est, 1e-6f), 1e6f);  // RHO_MIN, RHO_MAX (constants.h:69-70)

@@ -19,8 +19,8 @@
 #include <mutex>
 
 #include "umpc_core.cuh"
-#include "sim_core.cuh"
-#include "wl_core.cuh"
+#include "umpc_dev.cuh"
+#include "umpc_conv.h"
 #include "../../include/umpc_b200.h"
 
 // ---- per-QP scratch stores ---------------------------------------------------------------------------
@@ -130,21 +130,6 @@ __device__ __forceinline__ void tmem_release(const uint32_t* slot) {
   if ((threadIdx.x >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*slot), "n"(ncols) : "memory");
 }
 
-// ---- global SoA state -------------------------------------------------------------------------
-struct DevState {
-  int B;      // row stride = number of env slots, padded to a multiple of 256 (whole CTAs only)
-  int nreal;  // environments the caller asked for
-  // plant
-  float *p, *R, *dq, *uq, *acc;
-  // controller
-  float *T0, *xs, *zs, *ys, *D, *E, *solx, *soly, *info, *qpdata;
-  // tasks / loop
-  int* task;
-  float *tp, *pinit, *actualT0, *metrics;
-  // WL stage
-  float *wl_u0, *wlqp;  // wlqp: 25 floats per env (WlqpState)
-};
-
 struct GlobIO {
   const DevState& s;
   int e;
@@ -180,237 +165,45 @@ struct GlobIO {
 #define UMPC_DEFAULT_TPB 128  // TMEM scratch, two 4-warp CTAs per SM
 #endif
 
-struct KernelParams {
-  UmpcParams mpc;
-  SimParams sim;
-};
+typedef KernelParamsT<UmpcParams> KernelParams;
 
 extern __shared__ float g_smem[];
 
-__device__ __forceinline__ void store_info(const DevState& s, int e, const UmpcInfo& info) {
-  s.info[(size_t)0 * s.B + e] = (float)info.iter;
-  s.info[(size_t)1 * s.B + e] = (float)info.status;
-  s.info[(size_t)2 * s.B + e] = info.pri_res;
-  s.info[(size_t)3 * s.B + e] = info.dua_res;
-}
-
-// ---- kernel 1: one umpcUpdate per environment, inputs in [B][k] (the C-ABI's layout) ---------
-template <int TPB, class ST>
-__global__ void __launch_bounds__(TPB, ST::kTmem ? 1 : 224 / TPB)
-umpc_update_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s, float* __restrict__ uquad,
-                   float* __restrict__ accdes, const float* __restrict__ p0, const float* __restrict__ R0,
-                   const float* __restrict__ dq0, const float* __restrict__ pdes, const float* __restrict__ dpdes,
-                   const float* __restrict__ sdes, const float* __restrict__ actualT0, int want_qpdata,
-                   float* __restrict__ p_next, float* __restrict__ R_next, float* __restrict__ dq_next, int env0) {
-  const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;  // env0: first env of this launch (chunked host-buffer calls)
-  __shared__ uint32_t tmem_slot;
-  uint32_t scratch_base;
-  if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
-  else scratch_base = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
-  if (e < s.B) {  // B is a multiple of 256: whole CTAs (the body contains CTA-wide barriers)
-  float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    p[i] = p0[(size_t)e * 3 + i]; pd[i] = pdes[(size_t)e * 3 + i];
-    dpd[i] = dpdes[(size_t)e * 3 + i]; sd[i] = sdes[(size_t)e * 3 + i];
+// The C path's SOLVER policy (umpc_dev.cuh): float32, scratch store ST, exactly max_iter iterations.
+template <int TPB_, class ST>
+struct SolverF32 {
+  typedef UmpcParams Params;
+  static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
+  ST st;
+  template <int TPB>
+  static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) {
+    if (ST::kTmem) return tmem_acquire<TPB>(slot);
+    return (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
   }
-#pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = R0[(size_t)e * 9 + i];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) dq[i] = dq0[(size_t)e * 6 + i];
-  const float aT0 = actualT0 ? actualT0[e] : -1.0f;
-  float T0 = s.T0[e];
-  if (want_qpdata) {
+  template <int TPB>
+  static __device__ __forceinline__ void release(const uint32_t* slot) {
+    if (ST::kTmem) tmem_release<TPB>(slot);
+  }
+  __device__ __forceinline__ void init(uint32_t scratch_base, const DevState& s, int e) { st.init(scratch_base, s.soly + e, s.B); }
+  __device__ __forceinline__ void qpdata(const Params& par, const DevState& s, int e, const float p[3], const float R[9],
+                                         const float dq[6], const float pd[3], const float dpd[3], const float sd[3], float aT0) {
     UmpcQP qp;
-    umpc_build(kp.mpc, qp, p, R, dq, pd, dpd, sd, aT0 >= 0.0f ? aT0 : T0);
+    umpc_build(par, qp, p, R, dq, pd, dpd, sd, aT0 >= 0.0f ? aT0 : s.T0[e]);
     float out[216];
-    umpc_qpdata(kp.mpc, qp, out);
+    umpc_qpdata(par, qp, out);
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
   }
-  ST st;
-  st.init(scratch_base, s.soly + e, s.B);
-  GlobIO io(s, e);
-  float uq[3], acc[6];
-  UmpcInfo info;
-  umpc_update(kp.mpc, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
-  s.T0[e] = T0;
-  store_info(s, e, info);
-#pragma unroll
-  for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; s.uq[(size_t)i * s.B + e] = uq[i]; }
-#pragma unroll
-  for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; s.acc[(size_t)i * s.B + e] = acc[i]; }
-  if (p_next) {
-    // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
-    // (inputs re-read: they were not kept in registers over the solve)
-#pragma unroll
-    for (int i = 0; i < 3; ++i) p[i] = *(volatile const float*)(p0 + (size_t)e * 3 + i);
-#pragma unroll
-    for (int i = 0; i < 9; ++i) R[i] = *(volatile const float*)(R0 + (size_t)e * 9 + i);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) dq[i] = *(volatile const float*)(dq0 + (size_t)e * 6 + i);
-    uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
-    uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
-    sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) p_next[(size_t)e * 3 + i] = p[i];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) R_next[(size_t)e * 9 + i] = R[i];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) dq_next[(size_t)e * 6 + i] = dq[i];
+  __device__ __forceinline__ void update(const Params& par, const DevState& s, int e, float uq[3], float acc[6], const float p[3],
+                                         const float R[9], const float dq[6], const float pd[3], const float dpd[3],
+                                         const float sd[3], float aT0) {
+    GlobIO io(s, e);
+    float T0 = s.T0[e];
+    UmpcInfo info;
+    umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+    s.T0[e] = T0;
+    store_info(s, e, info.iter, info.status, info.pri_res, info.dua_res);
   }
-  }
-  if (ST::kTmem) tmem_release<TPB>(&tmem_slot);
-}
-
-// ---- kernel 2: fused closed loop (uprightmpc2.py:87-159) -------------------------------------
-// Per plant step: task -> [umpcUpdate when the host-computed schedule fires] -> [WL stage] ->
-// torque clip -> rigid-body step -> metric sums.  Plant state stays in registers for the
-// whole launch; the warm start is re-read from HBM at each solve (1 KB per ~5e4 flop).
-struct LogBuf {
-  int env, cap;
-  float *y, *u;  // [cap][12], [cap][3]
 };
-
-__device__ __forceinline__ void load_wlqp(const DevState& s, int e, WlqpState& w) {
-  const float* b = s.wlqp + e;
-  const size_t B = s.B;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    w.xs[i] = b[(0 + i) * B]; w.zs[i] = b[(4 + i) * B]; w.ys[i] = b[(8 + i) * B];
-    w.D[i] = b[(12 + i) * B]; w.E[i] = b[(16 + i) * B]; w.q0[i] = b[(21 + i) * B];
-  }
-  w.c = b[20 * B];
-}
-__device__ __forceinline__ void store_wlqp(const DevState& s, int e, const WlqpState& w) {
-  float* b = s.wlqp + e;
-  const size_t B = s.B;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    b[(0 + i) * B] = w.xs[i]; b[(4 + i) * B] = w.zs[i]; b[(8 + i) * B] = w.ys[i];
-    b[(12 + i) * B] = w.D[i]; b[(16 + i) * B] = w.E[i]; b[(21 + i) * B] = w.q0[i];
-  }
-  b[20 * B] = w.c;
-}
-
-// WL stage after an MPC update (accController, robobee_test_controllers.py:165-171)
-__device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp, const DevState& s, int e, const float R[9],
-                                      const float acc[6]) {
-  float h0[6], pdd[6], u0[4], w0[6];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    h0[i] = R[3 * i + 2] * sim.mb * sim.g; h0[3 + i] = 0.0f;
-    pdd[i] = sim.mb * acc[i]; pdd[3 + i] = sim.Ib[i] * acc[3 + i];
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) u0[i] = s.wl_u0[(size_t)i * s.B + e];
-  if (sim.wl_mode == 1) {
-    wl_con_update(wlp, u0, w0, h0, pdd);
-  } else {
-    WlqpState w;
-    load_wlqp(s, e, w);
-    wlqp_update(wlp, w, u0, w0, h0, pdd, nullptr, nullptr);
-    store_wlqp(s, e, w);
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) s.wl_u0[(size_t)i * s.B + e] = u0[i];
-  s.actualT0[e] = w0[2] / sim.mb;
-}
-
-template <int TPB, class ST>
-__global__ void __launch_bounds__(TPB, ST::kTmem ? 1 : 224 / TPB)
-umpc_rollout_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ DevState s,
-                    const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
-                    const double* __restrict__ tvals, LogBuf lg) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  __shared__ uint32_t tmem_slot;
-  uint32_t scratch_base;
-  if (ST::kTmem) scratch_base = tmem_acquire<TPB>(&tmem_slot);
-  else scratch_base = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
-  if (e < s.B) {
-  const size_t B = s.B;
-  float p[3], R[9], dq[6], uq[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) { p[i] = s.p[i * B + e]; uq[i] = s.uq[i * B + e]; }
-#pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = s.R[i * B + e];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) dq[i] = s.dq[i * B + e];
-  const int task = s.task[e];
-  float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
-  float pert_done = s.metrics[4 * B + e];
-  ST st;
-  st.init(scratch_base, s.soly + e, s.B);
-  GlobIO io(s, e);
-  for (int k = 0; k < nsteps; ++k) {
-    const double t = tvals[k];
-    if (task == SIM_TASK_HELIX && kp.sim.tpert >= 0.0f && t > (double)kp.sim.tpert && pert_done == 0.0f) {
-      dq[1] += 2.0f; pert_done = 1.0f;
-    }
-    if (fire[k]) {
-      // the task's reference is consumed by the controller only: evaluate it when the MPC fires
-      float pdes[3], dpdes[3], sdes[3];
-      {
-        float pinit[3], tp[4];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) pinit[i] = s.pinit[i * B + e];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) tp[i] = s.tp[i * B + e];
-        sim_task(task, t, pinit, tp, kp.sim.int_pos, pdes, dpdes, sdes);
-      }
-      float acc[6], T0 = s.T0[e];
-      const float aT0 = kp.sim.wl_mode ? s.actualT0[e] : -1.0f;
-      UmpcInfo info;
-      // plant state and metric sums through memory across the solve: they are not touched by it, and the
-      // ADMM loop needs every register
-#pragma unroll
-      for (int i = 0; i < 3; ++i) s.p[i * B + e] = p[i];
-#pragma unroll
-      for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
-#pragma unroll
-      for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
-      s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
-      umpc_update(kp.mpc, st, io, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0, T0, info);
-      s.T0[e] = T0;
-      store_info(s, e, info);
-#pragma unroll
-      for (int i = 0; i < 6; ++i) s.acc[i * B + e] = acc[i];
-#pragma unroll
-      for (int i = 0; i < 3; ++i) p[i] = *(volatile float*)(s.p + i * B + e);
-#pragma unroll
-      for (int i = 0; i < 9; ++i) R[i] = *(volatile float*)(s.R + i * B + e);
-#pragma unroll
-      for (int i = 0; i < 6; ++i) dq[i] = *(volatile float*)(s.dq + i * B + e);
-      err = *(volatile float*)(s.metrics + 0 * B + e); eff = *(volatile float*)(s.metrics + 1 * B + e);
-      nsolve = *(volatile float*)(s.metrics + 2 * B + e); nstep = *(volatile float*)(s.metrics + 3 * B + e);
-      if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, s, e, R, acc);
-      nsolve += 1.0f;
-    }
-    uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
-    uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
-    sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
-    err += p[0] * p[0] + p[1] * p[1] + p[2] * p[2];
-    eff += uq[1] * uq[1] + uq[2] * uq[2];
-    nstep += 1.0f;
-    if (e == lg.env && step0 + k < lg.cap) {
-      float* y = lg.y + (size_t)(step0 + k) * 12;
-      float* u = lg.u + (size_t)(step0 + k) * 3;
-#pragma unroll
-      for (int i = 0; i < 3; ++i) { y[i] = p[i]; y[3 + i] = R[6 + i]; u[i] = uq[i]; }
-#pragma unroll
-      for (int i = 0; i < 6; ++i) y[6 + i] = dq[i];
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 3; ++i) { s.p[i * B + e] = p[i]; s.uq[i * B + e] = uq[i]; }
-#pragma unroll
-  for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
-  s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
-  s.metrics[4 * B + e] = pert_done;
-  }
-  if (ST::kTmem) tmem_release<TPB>(&tmem_slot);
-}
 
 // ---- kernel 3: WL stage alone (drop-in wlConUpdate / wlControllerUpdate, batch of B) ---------
 __global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __grid_constant__ DevState s, int mode,
@@ -517,6 +310,7 @@ struct UmpcBatch {
   KernelParams kp;
   WlParams wlp;
   DevState s;
+  UmpcConv* conv = nullptr;  // converged mode (float64 solver state, umpc_conv.cu); nullptr: the C path
   float* slab = nullptr;
   size_t slab_floats = 0;
   // staging ([B][k] layout of the C-ABI)
@@ -610,6 +404,7 @@ static int reset_state(UmpcBatch* b) {
   for (int e = 0; e < b->Bp; ++e) tmp[e] = -1.0f;
   CK(cudaMemcpyAsync(b->s.actualT0, tmp.data(), (size_t)b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
+  if (b->conv) CK((cudaError_t)umpc_conv_reset(b->conv, &b->s, b->stream));
   b->step = 0; b->thl = 0.0;
   return UMPC_OK;
 }
@@ -652,13 +447,15 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   s.task = (int*)take(1); s.tp = take(4); s.pinit = take(3); s.actualT0 = take(1); s.metrics = take(5);
   s.wl_u0 = take(4); s.wlqp = take(25);
   s.qpdata = nullptr;
+  s.c64 = nullptr;
+  if (par->checkTermination > 0) CK((cudaError_t)umpc_conv_create(&b->conv, np, par, &s));
   CK(cudaMalloc(&b->d_in, (size_t)28 * np * sizeof(float)));
   CK(cudaMalloc(&b->d_out, (size_t)10 * np * sizeof(float)));
   CK(cudaMemset(b->d_in, 0, (size_t)28 * np * sizeof(float)));
   CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
 #define UMPC_SET_SMEM(T)                                                                                                     \
-  CK(cudaFuncSetAttribute(umpc_update_kernel<T, SmemStore<T>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024))); \
-  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SmemStore<T>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+  CK(cudaFuncSetAttribute(umpc_update_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024))); \
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
   UMPC_SET_SMEM(32) UMPC_SET_SMEM(64)
   b->tpb = UMPC_DEFAULT_TPB;
   if (const char* t = getenv("UMPC_TPB")) {  // tuning/testing knob: same values as umpcBatchSetLaunch
@@ -675,6 +472,7 @@ extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   if (!b) return;
   cudaSetDevice(b->device);
   cudaStreamSynchronize(b->stream);
+  umpc_conv_destroy(b->conv);
   cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums); cudaFree(b->d_next);
   cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
   cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
@@ -722,9 +520,15 @@ static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float*
   if (!stream) stream = b->stream;
   const int tpb = b->tpb, grid = (nenv + tpb - 1) / tpb;
   if (stream == b->stream) CK(cudaEventRecord(b->ev0, b->stream));
+  if (b->conv) {
+    CK((cudaError_t)umpc_conv_launch_update(b->conv, &b->kp.sim, &b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0,
+                                            b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0, nenv, stream));
+    if (stream == b->stream) { CK(cudaEventRecord(b->ev1, b->stream)); b->timed = true; }
+    return UMPC_OK;
+  }
 #define UMPC_LAUNCH_UPDATE(T, ST, SMEM)                                                                               \
   case T:                                                                                                             \
-    umpc_update_kernel<T, ST><<<grid, T, SMEM, stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, \
+    umpc_update_kernel<T, SolverF32<T, ST>><<<grid, T, SMEM, stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, \
                                                          b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);                      \
     break;
   switch (tpb) {
@@ -928,9 +732,17 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
   CK(cudaStreamSynchronize(b->stream));
   const int tpb = b->tpb, grid = (b->Bp + tpb - 1) / tpb;
   CK(cudaEventRecord(b->ev0, b->stream));
+  if (b->conv) {
+    CK((cudaError_t)umpc_conv_launch_rollout(b->conv, &b->kp.sim, &b->s, &b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg,
+                                             b->stream));
+    CK(cudaEventRecord(b->ev1, b->stream));
+    b->timed = true;
+    b->step += nsteps;
+    return UMPC_OK;
+  }
 #define UMPC_LAUNCH_ROLLOUT(T, ST, SMEM)                                                                              \
   case T:                                                                                                             \
-    umpc_rollout_kernel<T, ST><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, \
+    umpc_rollout_kernel<T, SolverF32<T, ST>><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, \
                                                              b->lg);                                                    \
     break;
   switch (tpb) {
