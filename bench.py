@@ -153,6 +153,9 @@ def main():
     ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
+    ap.add_argument("--converged", action="store_true",
+                    help="converged mode (the reference's Python path: float64 ADMM to eps 1e-4, check every 25, adaptive rho "
+                         "every 100, max 4000).  Extra measurement, not the driver's line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -185,6 +188,9 @@ def main():
         import util
         kw = dict(wlMode=1 if args.workload == "cascade-wlcon" else 2, wl_popts=util.load_constants()["popts_waypoint"])
         args.no_e2e = True  # the host-buffer env-step call has no WL stage
+    if args.converged:
+        kw.update(maxIter=4000, checkTermination=25, adaptiveRhoInterval=100)
+        args.no_e2e = True
     spl = 1  # plant steps per launch
     if args.hl_interval is not None:
         kw["hlInterval"] = args.hl_interval
@@ -249,8 +255,9 @@ def main():
                "call": "umpcBatchEnvStep (pinned host buffers; umpcUpdate + clip + quadrotorNLDyn per env)"}
         b2.close()
 
+    mean_iter = float(b.solve_info()["iter"].mean()) if args.converged else 50.0
     if rank == 0:
-        fl = F.our_flops(50)
+        fl = F.our_flops(mean_iter)
         per_launch_flops = (fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
         launch_s = dev_s / args.steps
         peak_tf = b.lib.umpcMeasureFp32Peak(local, 4096)
@@ -275,7 +282,7 @@ def main():
                     "ref_algorithm_equiv_tflops": F.reference_algorithm_flops(50) * nenv / launch_s * 1e-12}
         line = {"metric": METRIC, "value": spl * nenv * world * args.steps / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "vs_baseline": None, "dtype": "f64" if args.converged else "f32", "data": "synthetic",
                 "config": dict(workload_config(world, nenv), **({} if args.workload == "mc" else {
                     "workload": "BASELINE configs[3] shape: %d-env cascade per GPU, UprightMPC2 -> %s -> actualT0 feedback every "
                                 "env-step (robobee_test_controllers.py:162-171), WaypointHover constants" % (
@@ -286,6 +293,11 @@ def main():
                              "env_steps_total": sums[3], "non_finite_envs": sums[4]}}
         if e2e:
             line["e2e"] = e2e
+        if args.converged:
+            line["converged_mode"] = {"mean_iter_last_step": mean_iter, "max_iter": 4000, "check_termination": 25,
+                                      "adaptive_rho_interval": 100, "eps": 1e-4,
+                                      "note": "extra measurement: float64 kernel (umpc_conv.cu), scratch in HBM/L2; roofline "
+                                              "above is still quoted against the FP32 pipe peak and does not apply"}
         if world == 1 and not args.no_cpu:
             from oracle import binding as OB
             cores = os.cpu_count() or 1

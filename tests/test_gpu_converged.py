@@ -111,3 +111,29 @@ def test_converged_rollout_matches_reference_python_loop(cuda_required):
     pf, _, _, _ = b.state()
     assert np.abs(pf - pf[0]).max() == 0.0
     b.close()
+
+
+def test_python_controller_dropin(cuda_required):
+    """robobee3d_b200.template_controllers.UprightMPC2 / createMPC: the reference's Python class surface
+    (template_controllers.py:169-280) over the converged-mode kernel, vs the float64 oracle on a warm-started sequence"""
+    from oracle import binding as OB
+    from robobee3d_b200.template_controllers import createMPC
+    gold = np.load(os.path.join(GOLDEN, "umpc_seq.npz"))
+    pyver, cver = createMPC()
+    o = OB.OracleUMPC("f64")
+    o.set_converged()
+    e = 5
+    for c in range(gold["p"].shape[1]):
+        a = (gold["p"][e, c], gold["R"][e, c], gold["dq"][e, c], gold["pdes"][e, c], gold["dpdes"][e, c], gold["sdes"][e, c],
+             float(gold["aT0"][e, c]))
+        u, acc = pyver.update(*a)
+        uo, ao = o.update(*a)
+        x, y, info = o.solution()
+        tol = 10 * EPS + EPS * np.abs(x).max()
+        assert u.shape == (3,) and acc.shape == (6,) and pyver.prevsol.shape == (45,)
+        assert np.abs(u - uo).max() <= tol and np.abs(pyver.prevsol - x).max() <= tol
+        assert np.abs(acc - pyver.getAccDes(gold["R"][e, c], gold["dq"][e, c])).max() <= 1e-5 * max(1.0, np.abs(acc).max())
+        assert pyver.info["status"] == 1 and abs(pyver.T0 - u[0]) < 1e-7
+    uc, _ = cver.update(*a[:6], a[6])
+    assert np.isfinite(uc).all()
+    pyver.close()

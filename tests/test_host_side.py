@@ -61,6 +61,9 @@ def test_no_cpu_fallback_without_device():
     with pytest.raises(RuntimeError):
         uprightmpc2py.UprightMPC2C(d["dt"], d["g"], d["TtoWmax"], d["ws"], d["wds"], d["wpr"], d["wpf"], d["wvr"], d["wvf"],
                                    d["wthrust"], d["wmom"], d["Ib"], d["maxIter"])
+    from robobee3d_b200 import template_controllers
+    with pytest.raises(RuntimeError):
+        template_controllers.createMPC()
     # raw C-ABI: error code + message, outputs poisoned with NaN
     L = _lib.load()
     up = _lib.UprightMPC_t()
