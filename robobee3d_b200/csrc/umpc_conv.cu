@@ -55,6 +55,10 @@ struct GlobStore64 {
   }
   __device__ __forceinline__ void wait(double (&)[UMPC_GEN_CHUNK]) const {}
   __device__ __forceinline__ void setW(int e, double v) { __stcg(w + (size_t)e * B, v); }
+  __device__ __forceinline__ void setChunk(int c, const double (&v)[UMPC_GEN_CHUNK]) {
+#pragma unroll
+    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) __stcg(w + (size_t)(c * UMPC_GEN_CHUNK + i) * B, v[i]);
+  }
   __device__ __forceinline__ void end_writes() {}
   __device__ __forceinline__ void sync() const {}
   __device__ __forceinline__ bool all(bool p) const { return __all_sync(0xffffffffu, p); }

@@ -73,6 +73,7 @@ struct UmpcParams {
   int check_termination;      // test the residuals every this many iterations and stop when below eps
   int adaptive_rho_interval;  // re-estimate rho every this many iterations (auxil.c:13-75), refactor when it moves x5
   ureal adaptive_rho_tol;
+  int debug_phase;  // measurement aid (UMPC_DEBUG_PHASE): 1 = stop after set-up, 2 = stop after the ADMM loop; 0 = normal
 };
 
 // unscaled A0 values that change per update (Ax_data, uprightmpc2.c:160-179)
@@ -380,7 +381,15 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
         io.st_E(i, E[i]);
       }
 #pragma unroll
-      for (int q = 0; q < (UMPC_NX + 1) / 2; ++q) st.setW(UMPC_GEN_OFF_SG + q, umpc_pack2(sgv[2 * q], sgv[2 * q + 1]));
+      for (int cq = 0; cq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++cq) {
+        ureal ck[UMPC_GEN_CHUNK];
+#pragma unroll
+        for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
+          const int q = cq * UMPC_GEN_CHUNK + u;
+          ck[u] = q < (UMPC_NX + 1) / 2 ? umpc_pack2(sgv[q < (UMPC_NX + 1) / 2 ? 2 * q : 0], sgv[q < (UMPC_NX + 1) / 2 ? 2 * q + 1 : 0]) : (ureal)0;
+        }
+        st.setChunk(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + cq, ck);
+      }
       umpc_gen_factor(G, W, a, st);
       st.sync();
       st.end_writes();  // the factor is read back by the solve (asynchronous stores of a TMEM-backed scratch)
@@ -434,6 +443,17 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
 #pragma unroll
       for (int j = 0; j < UMPC_NEQ; ++j) { w[j] = w0[j]; st.setVf(j, (wf[j] - alpha * w0[j]) * ioma); }
     }
+  }
+  if (par.debug_phase == 1) {
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) io.st_solx(j, xs[j]);
+#pragma unroll
+    for (int j = 0; j < UMPC_NEQ; ++j) io.st_soly(j, w[j] + (j < 9 ? kpu[j] : 0) + (j < 3 ? z3[j] + y3[j] + W3[j] : 0));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) uquad[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) accdes[i] = 0;
+    return;
   }
   // ---- ADMM (osqp.c:352-500; fixed rho: adaptive_rho_interval = 0 in workspace.c:561) -----
   const ureal ac = alpha * c;
@@ -521,6 +541,17 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     }
   }
   iter_done += nseg;
+  if (par.debug_phase == 2) {
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) io.st_solx(j, xs[j]);
+#pragma unroll
+    for (int j = 0; j < UMPC_NEQ; ++j) io.st_soly(j, w[j] + (j < 3 ? z3[j] + y3[j] : 0));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) uquad[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) accdes[i] = 0;
+    return;
+  }
   // ---- back to un-shifted coordinates; equality-row duals from g = w - kappa ----------------
   st.sync();
   bool again = false;

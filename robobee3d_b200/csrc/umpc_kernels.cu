@@ -63,6 +63,12 @@ struct SmemStore {
   __device__ __forceinline__ void setW(int e, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(e >> 2) * gstride + (uint32_t)(e & 3) * 4u), "f"(v) : "memory");
   }
+  __device__ __forceinline__ void setChunk(int c, const float (&v)[UMPC_GEN_CHUNK]) {
+#pragma unroll
+    for (int g = 0; g < UMPC_GEN_CHUNK / 4; ++g)
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sbase + (uint32_t)(c * (UMPC_GEN_CHUNK / 4) + g) * gstride),
+                   "f"(v[4 * g]), "f"(v[4 * g + 1]), "f"(v[4 * g + 2]), "f"(v[4 * g + 3]) : "memory");
+  }
   __device__ __forceinline__ void end_writes() {}
   __device__ __forceinline__ void sync() const {}
   __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
@@ -92,6 +98,12 @@ struct TmemStore {
   }
   __device__ __forceinline__ void setW(int e, float v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tbase + (uint32_t)e), "f"(v) : "memory");
+  }
+  __device__ __forceinline__ void setChunk(int c, const float (&v)[UMPC_GEN_CHUNK]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(tbase + (uint32_t)c * UMPC_GEN_CHUNK), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]),
+        "f"(v[7]), "f"(v[8]), "f"(v[9]), "f"(v[10]), "f"(v[11]), "f"(v[12]), "f"(v[13]), "f"(v[14]), "f"(v[15]) : "memory");
   }
   __device__ __forceinline__ void end_writes() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
   // Optional CTA-wide rendezvous at phase boundaries (-DUMPC_PHASE_SYNC): keeps the warps of a CTA on the same
@@ -134,15 +146,9 @@ struct GlobIO {
   const DevState& s;
   int e;
   __device__ __forceinline__ GlobIO(const DevState& s_, int e_) : s(s_), e(e_) {}
-  __device__ __forceinline__ void prefetch_warm_start() const {
-#pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) asm volatile("prefetch.global.L2 [%0];" ::"l"(s.xs + (size_t)j * s.B + e));
-#pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(s.zs + (size_t)i * s.B + e));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(s.ys + (size_t)i * s.B + e));
-    }
-  }
+  // (a prefetch.global.L2 of the 123 warm-start rows here cost ~500 once-per-solve instructions -- address arithmetic
+  // plus CCTL -- for a latency that the 123 independent loads issued together later overlap anyway; removed)
+  __device__ __forceinline__ void prefetch_warm_start() const {}
   // inputs parked over the ADMM loop (solx is dead until the solution is stored); volatile read-back so that the
   // compiler cannot keep the values in registers instead
   __device__ __forceinline__ void stash(int k, float v) { s.solx[(size_t)k * s.B + e] = v; }
@@ -360,6 +366,7 @@ static void fill_kernel_params(UmpcBatch* b) {
   // generated settings (uprightmpc2/workspace.c:561) + uprightmpc2.c:116-117
   m.max_iter = p.maxIter; m.rho = 0.1f; m.sigma = 1e-6f; m.alpha = 1.6f; m.eps_abs = 1e-4f; m.eps_rel = 1e-4f;
   m.scaling_iters = 10;
+  if (const char* dp = getenv("UMPC_DEBUG_PHASE")) m.debug_phase = atoi(dp);  // measurement aid, see umpc_core.cuh
   SimParams& sm = b->kp.sim;
   sm.dtsim = (float)p.dtsim; sm.hl_interval = (float)p.hlInterval; sm.taulim = p.taulim; sm.tpert = p.tpert;
   for (int i = 0; i < 3; ++i) sm.Ib[i] = p.Ib[i];

@@ -13,7 +13,7 @@ def _par_type(real):
                     ('Qdyr', real * 6), ('Qdyf', real * 6), ('R', real * 3), ('Ibi', real * 3),
                     ('max_iter', C.c_int), ('rho', real), ('sigma', real), ('alpha', real), ('eps_abs', real),
                     ('eps_rel', real), ('scaling_iters', C.c_int), ('check_termination', C.c_int),
-                    ('adaptive_rho_interval', C.c_int), ('adaptive_rho_tol', real)]
+                    ('adaptive_rho_interval', C.c_int), ('adaptive_rho_tol', real), ('debug_phase', C.c_int)]
     return Par
 
 
