@@ -188,6 +188,10 @@ int umpcBatchGetLog(UmpcBatch *b, float *y, float *u, int nsteps);
 int umpcBatchSync(UmpcBatch *b);
 /* device pointers for zero-copy use from torch / other CUDA code (SoA, [k][B]) */
 void *umpcBatchDevPtr(UmpcBatch *b, const char *name);
+/* per-environment cost weights w[B][8] = (ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom): every env is its own createMPC(**kwargs)
+ * (template_controllers.py:260) -- the reference's weight sweep gainTuningSims (uprightmpc2.py:272-303) as ONE batch.
+ * NULL restores the batch-wide parameters.  float32 path: TMEM launch shape (128 threads per block) only. */
+int umpcBatchSetWeights(UmpcBatch *b, const float *w);
 /* CUDA-event time (ms) of the last kernel sequence launched by the Update or Rollout calls */
 float umpcBatchLastKernelMs(UmpcBatch *b);
 /* CUDA events on the batch's stream around any sequence of calls: Start records, StopMs records + waits */

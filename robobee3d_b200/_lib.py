@@ -58,7 +58,7 @@ EXPORTS = [
     "umpcBatchDefaults", "umpcLastError", "umpcBatchCreate", "umpcBatchDestroy", "umpcBatchSize", "umpcBatchReset",
     "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
     "umpcBatchGetState", "umpcBatchRollout", "umpcBatchGetMetrics", "umpcBatchReduceMetrics", "umpcBatchSetLog",
-    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch",
+    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchSetWeights", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch",
     "umpcMeasureFp32Peak",
 ]
 
@@ -102,6 +102,7 @@ def load():
     L.umpcBatchTimerStopMs.argtypes = [vp]
     L.umpcBatchTimerStopMs.restype = C.c_float
     L.umpcBatchSetLaunch.argtypes = [vp, C.c_int]
+    L.umpcBatchSetWeights.argtypes = [vp, vp]
     L.umpcMeasureFp32Peak.argtypes = [C.c_int, C.c_int]
     L.umpcMeasureFp32Peak.restype = C.c_double
     f = C.c_float

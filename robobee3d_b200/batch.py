@@ -86,6 +86,23 @@ class BatchUMPC:
     def reset(self):
         _lib.check(self.lib.umpcBatchReset(self.h), "umpcBatchReset")
 
+    WEIGHT_NAMES = ("ws", "wds", "wpr", "wpf", "wvr", "wvf", "wthrust", "wmom")
+
+    def set_weights(self, **kw):
+        """Per-environment cost weights: every env becomes its own createMPC(**kwargs) (template_controllers.py:260).
+        Each keyword is a scalar or an array of B values; weights not given keep the batch-wide value.
+        set_weights() with no arguments restores the batch-wide parameters."""
+        if not kw:
+            _lib.check(self.lib.umpcBatchSetWeights(self.h, None), "umpcBatchSetWeights")
+            return
+        bad = [k for k in kw if k not in self.WEIGHT_NAMES]
+        if bad:
+            raise TypeError("unknown weight(s) %s" % bad)
+        w = np.empty((self.B, 8), np.float32)
+        for i, k in enumerate(self.WEIGHT_NAMES):
+            w[:, i] = np.broadcast_to(np.asarray(kw.get(k, getattr(self.params, k)), np.float32), (self.B,))
+        _lib.check(self.lib.umpcBatchSetWeights(self.h, _vp(w)), "umpcBatchSetWeights")
+
     def set_launch(self, threads_per_block):
         _lib.check(self.lib.umpcBatchSetLaunch(self.h, int(threads_per_block)), "umpcBatchSetLaunch")
 

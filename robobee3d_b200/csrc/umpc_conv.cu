@@ -130,6 +130,11 @@ struct SolverF64 {
     GlobIO64 io(s, e);
     double T0 = s.c64[(size_t)C64_T0 * s.B + e];
     umpc64::UmpcInfo info;
+    if (s.wts) {  // per-environment weights (warp-uniform branch)
+      Params pe = par;
+      load_env_weights(pe, s, e);
+      umpc64::umpc_update<true>(pe, st, io, uq_, acc_, p_, R_, dq_, pd_, dpd_, sd_, (double)aT0, T0, info);
+    } else
     umpc64::umpc_update<true>(par, st, io, uq_, acc_, p_, R_, dq_, pd_, dpd_, sd_, (double)aT0, T0, info);
     s.c64[(size_t)C64_T0 * s.B + e] = T0;
     s.T0[e] = (float)T0;

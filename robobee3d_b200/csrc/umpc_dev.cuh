@@ -26,7 +26,24 @@ struct DevState {
   float *wl_u0, *wlqp;  // wlqp: 25 floats per env (WlqpState)
   // converged mode only: controller state and per-QP scratch in double, rows of B (layout: umpc_conv.cu)
   double* c64;
+  // optional per-environment cost weights, 8 rows of B: ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom (the arguments the
+  // reference's weight sweep varies per run, uprightmpc2.py:272-303); nullptr: the batch-wide parameters
+  float* wts;
 };
+
+// fills the weight vectors of a parameter struct (umpcInit, uprightmpc2.c:19-63) from the per-env rows
+template <class P>
+__device__ __forceinline__ void load_env_weights(P& par, const DevState& s, int e) {
+  const size_t B = s.B;
+  const float ws = s.wts[0 * B + e], wds = s.wts[1 * B + e], wpr = s.wts[2 * B + e], wpf = s.wts[3 * B + e];
+  const float wvr = s.wts[4 * B + e], wvf = s.wts[5 * B + e], wth = s.wts[6 * B + e], wmo = s.wts[7 * B + e];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    par.Qyr[i] = wpr; par.Qyf[i] = wpf; par.Qyr[3 + i] = ws; par.Qyf[3 + i] = ws;
+    par.Qdyr[i] = wvr; par.Qdyf[i] = wvf; par.Qdyr[3 + i] = wds; par.Qdyf[3 + i] = wds;
+  }
+  par.R[0] = wth; par.R[1] = wmo; par.R[2] = wmo;
+}
 
 template <class MPC>
 struct KernelParamsT {

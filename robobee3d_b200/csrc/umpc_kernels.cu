@@ -176,7 +176,9 @@ typedef KernelParamsT<UmpcParams> KernelParams;
 extern __shared__ float g_smem[];
 
 // The C path's SOLVER policy (umpc_dev.cuh): float32, scratch store ST, exactly max_iter iterations.
-template <int TPB_, class ST>
+// PERENV: cost weights per environment (DevState::wts) instead of the batch-wide ones; a separate instantiation so
+// that the default kernel keeps its weights as constant-bank operands.
+template <int TPB_, class ST, bool PERENV = false>
 struct SolverF32 {
   typedef UmpcParams Params;
   static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
@@ -205,7 +207,13 @@ struct SolverF32 {
     GlobIO io(s, e);
     float T0 = s.T0[e];
     UmpcInfo info;
-    umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+    if constexpr (PERENV) {
+      Params pe = par;
+      load_env_weights(pe, s, e);
+      umpc_update<false>(pe, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+    } else {
+      umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+    }
     s.T0[e] = T0;
     store_info(s, e, info.iter, info.status, info.pri_res, info.dua_res);
   }
@@ -454,6 +462,7 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   s.task = (int*)take(1); s.tp = take(4); s.pinit = take(3); s.actualT0 = take(1); s.metrics = take(5);
   s.wl_u0 = take(4); s.wlqp = take(25);
   s.qpdata = nullptr;
+  s.wts = nullptr;
   s.c64 = nullptr;
   if (par->checkTermination > 0) CK((cudaError_t)umpc_conv_create(&b->conv, np, par, &s));
   CK(cudaMalloc(&b->d_in, (size_t)28 * np * sizeof(float)));
@@ -480,6 +489,7 @@ extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   cudaSetDevice(b->device);
   cudaStreamSynchronize(b->stream);
   umpc_conv_destroy(b->conv);
+  cudaFree(b->s.wts);
   cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums); cudaFree(b->d_next);
   cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
   cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
@@ -538,6 +548,10 @@ static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float*
     umpc_update_kernel<T, SolverF32<T, ST>><<<grid, T, SMEM, stream>>>(b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, \
                                                          b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);                      \
     break;
+  if (b->s.wts) {  // per-env weights: TMEM launch shape only
+    umpc_update_kernel<128, SolverF32<128, TmemStore, true>><<<(nenv + 127) / 128, 128, 0, stream>>>(
+        b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);
+  } else
   switch (tpb) {
     UMPC_LAUNCH_UPDATE(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_UPDATE(64, SmemStore<64>, smem_bytes(64))
     UMPC_LAUNCH_UPDATE(128, TmemStore, 0) UMPC_LAUNCH_UPDATE(256, TmemStore, 0)
@@ -700,6 +714,25 @@ extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, c
   return UMPC_OK;
 }
 
+// per-environment cost weights [B][8] = (ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom) per env; NULL: back to the
+// batch-wide parameters.  What the reference's weight sweep varies per run (uprightmpc2.py:272-303).
+extern "C" int umpcBatchSetWeights(UmpcBatch* b, const float* w) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  if (!w) { cudaFree(b->s.wts); b->s.wts = nullptr; return UMPC_OK; }
+  if (!b->s.wts) CK(cudaMalloc(&b->s.wts, (size_t)8 * b->Bp * sizeof(float)));
+  // padded env slots get the batch-wide weights (they run on zero state and are never read back)
+  const UmpcBatchParams& p = b->bp;
+  const float def[8] = {p.ws, p.wds, p.wpr, p.wpf, p.wvr, p.wvf, p.wthrust, p.wmom};
+  const size_t B = b->B, P = b->Bp;
+  std::vector<float> tmp(P * 8);
+  for (size_t e = 0; e < P; ++e)
+    for (int i = 0; i < 8; ++i) tmp[(size_t)i * P + e] = e < B ? w[e * 8 + i] : def[i];
+  CK(cudaMemcpy(b->s.wts, tmp.data(), P * 8 * sizeof(float), cudaMemcpyHostToDevice));
+  return UMPC_OK;
+}
+
 extern "C" int umpcBatchGetState(UmpcBatch* b, float* p, float* R, float* dq, float* uquad) {
   if (!b) return UMPC_ERR_ARG;
   CK(cudaSetDevice(b->device));
@@ -752,6 +785,10 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
     umpc_rollout_kernel<T, SolverF32<T, ST>><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, \
                                                              b->lg);                                                    \
     break;
+  if (b->s.wts) {
+    umpc_rollout_kernel<128, SolverF32<128, TmemStore, true>><<<(b->Bp + 127) / 128, 128, 0, b->stream>>>(
+        b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+  } else
   switch (tpb) {
     UMPC_LAUNCH_ROLLOUT(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_ROLLOUT(64, SmemStore<64>, smem_bytes(64))
     UMPC_LAUNCH_ROLLOUT(128, TmemStore, 0) UMPC_LAUNCH_ROLLOUT(256, TmemStore, 0)
