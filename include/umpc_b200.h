@@ -186,7 +186,10 @@ int umpcBatchReduceMetrics(UmpcBatch *b, double *sums8);
 int umpcBatchSetLog(UmpcBatch *b, int env, int capacity_steps);
 int umpcBatchGetLog(UmpcBatch *b, float *y, float *u, int nsteps);
 int umpcBatchSync(UmpcBatch *b);
-/* device pointers for zero-copy use from torch / other CUDA code (SoA, [k][B]) */
+/* device pointers for zero-copy use from torch / other CUDA code.  The state is a tiled struct of arrays
+ * float[B/32][ROWS][32] ("slab"): the named pointers ("p", "R", "xs", ...) address the row block of env 0; element i
+ * of env e is at ptr[(e / 32) * ROWS * 32 + i * 32 + e % 32] (ROWS: robobee3d_b200/csrc/umpc_dev.cuh).
+ * "stage_in"/"stage_out" are the [env][k] staging buffers of the host-buffer calls, "stream" the batch's stream. */
 void *umpcBatchDevPtr(UmpcBatch *b, const char *name);
 /* per-environment cost weights w[B][8] = (ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom): every env is its own createMPC(**kwargs)
  * (template_controllers.py:260) -- the reference's weight sweep gainTuningSims (uprightmpc2.py:272-303) as ONE batch.

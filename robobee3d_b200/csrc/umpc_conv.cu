@@ -68,11 +68,10 @@ struct GlobStore64 {
 
 // controller state in double; the float rows of DevState are kept as mirrors for the getters of the C-ABI
 struct GlobIO64 {
-  const DevState& s;
+  float* eb;  // float mirrors: the env's rows of the tiled slab (umpc_dev.cuh)
   double* c;
   size_t B;
-  int e;
-  __device__ __forceinline__ GlobIO64(const DevState& s_, int e_) : s(s_), c(s_.c64 + e_), B(s_.B), e(e_) {}
+  __device__ __forceinline__ GlobIO64(const DevState& s_, int e_) : eb(env_base(s_, e_)), c(s_.c64 + e_), B(s_.B) {}
   __device__ __forceinline__ void prefetch_warm_start() const {}
   __device__ __forceinline__ void stash(int k, double v) { c[(size_t)(C64_STASH + k) * B] = v; }
   __device__ __forceinline__ double unstash(int k) const { return *(volatile const double*)(c + (size_t)(C64_STASH + k) * B); }
@@ -83,13 +82,13 @@ struct GlobIO64 {
   __device__ __forceinline__ double ld_ys(int i) const { return c[(size_t)(C64_YS + i) * B]; }
   __device__ __forceinline__ double ld_D(int j) const { return c[(size_t)(C64_D + j) * B]; }
   __device__ __forceinline__ double ld_E(int i) const { return c[(size_t)(C64_E + i) * B]; }
-  __device__ __forceinline__ void st_xs(int j, double v) { c[(size_t)(C64_XS + j) * B] = v; s.xs[(size_t)j * B + e] = (float)v; }
-  __device__ __forceinline__ void st_zs(int i, double v) { c[(size_t)(C64_ZS + i) * B] = v; s.zs[(size_t)i * B + e] = (float)v; }
-  __device__ __forceinline__ void st_ys(int i, double v) { c[(size_t)(C64_YS + i) * B] = v; s.ys[(size_t)i * B + e] = (float)v; }
-  __device__ __forceinline__ void st_D(int j, double v) { c[(size_t)(C64_D + j) * B] = v; s.D[(size_t)j * B + e] = (float)v; }
-  __device__ __forceinline__ void st_E(int i, double v) { c[(size_t)(C64_E + i) * B] = v; s.E[(size_t)i * B + e] = (float)v; }
-  __device__ __forceinline__ void st_solx(int j, double v) { s.solx[(size_t)j * B + e] = (float)v; }
-  __device__ __forceinline__ void st_soly(int i, double v) { s.soly[(size_t)i * B + e] = (float)v; }
+  __device__ __forceinline__ void st_xs(int j, double v) { c[(size_t)(C64_XS + j) * B] = v; eb[ROWF(ROW_XS + j)] = (float)v; }
+  __device__ __forceinline__ void st_zs(int i, double v) { c[(size_t)(C64_ZS + i) * B] = v; eb[ROWF(ROW_ZS + i)] = (float)v; }
+  __device__ __forceinline__ void st_ys(int i, double v) { c[(size_t)(C64_YS + i) * B] = v; eb[ROWF(ROW_YS + i)] = (float)v; }
+  __device__ __forceinline__ void st_D(int j, double v) { c[(size_t)(C64_D + j) * B] = v; eb[ROWF(ROW_D + j)] = (float)v; }
+  __device__ __forceinline__ void st_E(int i, double v) { c[(size_t)(C64_E + i) * B] = v; eb[ROWF(ROW_E + i)] = (float)v; }
+  __device__ __forceinline__ void st_solx(int j, double v) { eb[ROWF(ROW_SOLX + j)] = (float)v; }
+  __device__ __forceinline__ void st_soly(int i, double v) { eb[ROWF(ROW_SOLY + i)] = (float)v; }
 };
 
 // SOLVER policy of the kernel templates in umpc_dev.cuh
@@ -137,8 +136,8 @@ struct SolverF64 {
     } else
     umpc64::umpc_update<true>(par, st, io, uq_, acc_, p_, R_, dq_, pd_, dpd_, sd_, (double)aT0, T0, info);
     s.c64[(size_t)C64_T0 * s.B + e] = T0;
-    s.T0[e] = (float)T0;
-    store_info(s, e, info.iter, info.status, (float)info.pri_res, (float)info.dua_res);
+    io.eb[ROWF(ROW_T0)] = (float)T0;
+    store_info(io.eb, info.iter, info.status, (float)info.pri_res, (float)info.dua_res);
 #pragma unroll
     for (int i = 0; i < 3; ++i) uq[i] = (float)uq_[i];
 #pragma unroll

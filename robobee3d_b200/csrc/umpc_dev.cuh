@@ -11,19 +11,37 @@
 #include "sim_core.cuh"
 #include "wl_core.cuh"
 
-// ---- global SoA state -------------------------------------------------------------------------
+// ---- global state: struct of arrays, tiled by warp ------------------------------------------------
+// One slab float[B/32][UMPC_ROWS][32]: the 32 envs of a warp own one contiguous tile (46 KB) in which row r of
+// lane l sits at r*32 + l.  A warp's access to one component is one 128-byte line as in a plain [row][env] layout,
+// but every row of an env is at a COMPILE-TIME offset from ONE per-thread base pointer (env_base), so a load/store is
+// a single instruction with an immediate offset.  With a run-time row stride every access cost a 64-bit add-with-carry
+// pair plus a live address register pair: ~2,300 of the ~10,000 once-per-solve SASS instructions and a good part of
+// the spills (profiles/r01c_phase_and_occupancy_sweeps.txt).
+enum {
+  ROW_P = 0, ROW_R = ROW_P + 3, ROW_DQ = ROW_R + 9, ROW_UQ = ROW_DQ + 6, ROW_ACC = ROW_UQ + 3,          // plant
+  ROW_T0 = ROW_ACC + 6, ROW_XS = ROW_T0 + 1, ROW_ZS = ROW_XS + 45, ROW_YS = ROW_ZS + 39,                // controller:
+  ROW_D = ROW_YS + 39, ROW_E = ROW_D + 45, ROW_SOLX = ROW_E + 39, ROW_SOLY = ROW_SOLX + 45,             //  warm start, scaling,
+  ROW_INFO = ROW_SOLY + 39,                                                                              //  solution, info
+  ROW_TASK = ROW_INFO + 4, ROW_TP = ROW_TASK + 1, ROW_PINIT = ROW_TP + 4, ROW_AT0 = ROW_PINIT + 3,      // task / loop
+  ROW_METRICS = ROW_AT0 + 1,
+  ROW_WLU0 = ROW_METRICS + 5, ROW_WLQP = ROW_WLU0 + 4,                                                   // WL stage (25 = WlqpState)
+  UMPC_ROWS = ROW_WLQP + 25
+};
+#define ROWF(r) ((r) * 32)  // float offset of row r inside a tile
+
 struct DevState {
-  int B;      // row stride = number of env slots, padded to a multiple of 256 (whole CTAs only)
+  int B;      // number of env slots, padded to a multiple of 256 (whole CTAs only)
   int nreal;  // environments the caller asked for
-  // plant
+  float* slab;
+  // HOST-side handles = address of the row block of ENV 0 (slab + ROWF(ROW_x)); env e's element i is at
+  // handle[tile_off(e) + 32 i].  Device code goes through env_base() instead.
   float *p, *R, *dq, *uq, *acc;
-  // controller
-  float *T0, *xs, *zs, *ys, *D, *E, *solx, *soly, *info, *qpdata;
-  // tasks / loop
+  float *T0, *xs, *zs, *ys, *D, *E, *solx, *soly, *info;
   int* task;
   float *tp, *pinit, *actualT0, *metrics;
-  // WL stage
-  float *wl_u0, *wlqp;  // wlqp: 25 floats per env (WlqpState)
+  float *wl_u0, *wlqp;
+  float* qpdata;  // diagnostics, plain [216][B]; allocated on request
   // converged mode only: controller state and per-QP scratch in double, rows of B (layout: umpc_conv.cu)
   double* c64;
   // optional per-environment cost weights, 8 rows of B: ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom (the arguments the
@@ -45,6 +63,9 @@ __device__ __forceinline__ void load_env_weights(P& par, const DevState& s, int 
   par.R[0] = wth; par.R[1] = wmo; par.R[2] = wmo;
 }
 
+__host__ __device__ __forceinline__ size_t tile_off(int e) { return (size_t)(e >> 5) * (UMPC_ROWS * 32) + (size_t)(e & 31); }
+__device__ __forceinline__ float* env_base(const DevState& s, int e) { return s.slab + tile_off(e); }
+
 template <class MPC>
 struct KernelParamsT {
   MPC mpc;
@@ -56,16 +77,16 @@ struct LogBuf {
   float *y, *u;  // [cap][12], [cap][3]
 };
 
-__device__ __forceinline__ void store_info(const DevState& s, int e, int iter, int status, float pri_res, float dua_res) {
-  s.info[(size_t)0 * s.B + e] = (float)iter;
-  s.info[(size_t)1 * s.B + e] = (float)status;
-  s.info[(size_t)2 * s.B + e] = pri_res;
-  s.info[(size_t)3 * s.B + e] = dua_res;
+__device__ __forceinline__ void store_info(float* eb, int iter, int status, float pri_res, float dua_res) {
+  eb[ROWF(ROW_INFO + 0)] = (float)iter;
+  eb[ROWF(ROW_INFO + 1)] = (float)status;
+  eb[ROWF(ROW_INFO + 2)] = pri_res;
+  eb[ROWF(ROW_INFO + 3)] = dua_res;
 }
 
-__device__ __forceinline__ void load_wlqp(const DevState& s, int e, WlqpState& w) {
-  const float* b = s.wlqp + e;
-  const size_t B = s.B;
+__device__ __forceinline__ void load_wlqp(const float* eb, WlqpState& w) {
+  const float* b = eb + ROWF(ROW_WLQP);
+  constexpr int B = 32;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     w.xs[i] = b[(0 + i) * B]; w.zs[i] = b[(4 + i) * B]; w.ys[i] = b[(8 + i) * B];
@@ -73,9 +94,9 @@ __device__ __forceinline__ void load_wlqp(const DevState& s, int e, WlqpState& w
   }
   w.c = b[20 * B];
 }
-__device__ __forceinline__ void store_wlqp(const DevState& s, int e, const WlqpState& w) {
-  float* b = s.wlqp + e;
-  const size_t B = s.B;
+__device__ __forceinline__ void store_wlqp(float* eb, const WlqpState& w) {
+  float* b = eb + ROWF(ROW_WLQP);
+  constexpr int B = 32;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     b[(0 + i) * B] = w.xs[i]; b[(4 + i) * B] = w.zs[i]; b[(8 + i) * B] = w.ys[i];
@@ -85,8 +106,8 @@ __device__ __forceinline__ void store_wlqp(const DevState& s, int e, const WlqpS
 }
 
 // WL stage after an MPC update (accController, robobee_test_controllers.py:165-171)
-static __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp, const DevState& s, int e,
-                                             const float R[9], const float acc[6]) {
+static __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParams& wlp, float* eb, const float R[9],
+                                             const float acc[6]) {
   float h0[6], pdd[6], u0[4], w0[6];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -94,18 +115,18 @@ static __device__ __noinline__ void wl_stage(const SimParams& sim, const WlParam
     pdd[i] = sim.mb * acc[i]; pdd[3 + i] = sim.Ib[i] * acc[3 + i];
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) u0[i] = s.wl_u0[(size_t)i * s.B + e];
+  for (int i = 0; i < 4; ++i) u0[i] = eb[ROWF(ROW_WLU0 + i)];
   if (sim.wl_mode == 1) {
     wl_con_update(wlp, u0, w0, h0, pdd);
   } else {
     WlqpState w;
-    load_wlqp(s, e, w);
+    load_wlqp(eb, w);
     wlqp_update(wlp, w, u0, w0, h0, pdd, nullptr, nullptr);
-    store_wlqp(s, e, w);
+    store_wlqp(eb, w);
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) s.wl_u0[(size_t)i * s.B + e] = u0[i];
-  s.actualT0[e] = w0[2] / sim.mb;
+  for (int i = 0; i < 4; ++i) eb[ROWF(ROW_WLU0 + i)] = u0[i];
+  eb[ROWF(ROW_AT0)] = w0[2] / sim.mb;
 }
 
 // A SOLVER policy provides
@@ -143,15 +164,16 @@ umpc_update_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params
 #pragma unroll
   for (int i = 0; i < 6; ++i) dq[i] = dq0[(size_t)e * 6 + i];
   const float aT0 = actualT0 ? actualT0[e] : -1.0f;
+  float* const eb = env_base(s, e);
   SOLVER sol;
   sol.init(scratch_base, s, e);
   if (want_qpdata) sol.qpdata(kp.mpc, s, e, p, R, dq, pd, dpd, sd, aT0);
   float uq[3], acc[6];
   sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pd, dpd, sd, aT0);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; s.uq[(size_t)i * s.B + e] = uq[i]; }
+  for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; eb[ROWF(ROW_UQ + i)] = uq[i]; }
 #pragma unroll
-  for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; s.acc[(size_t)i * s.B + e] = acc[i]; }
+  for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; eb[ROWF(ROW_ACC + i)] = acc[i]; }
   if (p_next) {
     // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
     // (inputs re-read: they were not kept in registers over the solve)
@@ -188,17 +210,17 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   __shared__ uint32_t tmem_slot;
   const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);
   if (e < s.B) {
-  const size_t B = s.B;
+  float* const eb = env_base(s, e);
   float p[3], R[9], dq[6], uq[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { p[i] = s.p[i * B + e]; uq[i] = s.uq[i * B + e]; }
+  for (int i = 0; i < 3; ++i) { p[i] = eb[ROWF(ROW_P + i)]; uq[i] = eb[ROWF(ROW_UQ + i)]; }
 #pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = s.R[i * B + e];
+  for (int i = 0; i < 9; ++i) R[i] = eb[ROWF(ROW_R + i)];
 #pragma unroll
-  for (int i = 0; i < 6; ++i) dq[i] = s.dq[i * B + e];
-  const int task = s.task[e];
-  float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e], nsolve = s.metrics[2 * B + e], nstep = s.metrics[3 * B + e];
-  float pert_done = s.metrics[4 * B + e];
+  for (int i = 0; i < 6; ++i) dq[i] = eb[ROWF(ROW_DQ + i)];
+  const int task = ((const int*)eb)[ROWF(ROW_TASK)];
+  float err = eb[ROWF(ROW_METRICS + 0)], eff = eb[ROWF(ROW_METRICS + 1)], nsolve = eb[ROWF(ROW_METRICS + 2)], nstep = eb[ROWF(ROW_METRICS + 3)];
+  float pert_done = eb[ROWF(ROW_METRICS + 4)];
   SOLVER sol;
   sol.init(scratch_base, s, e);
   for (int k = 0; k < nsteps; ++k) {
@@ -212,34 +234,34 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
       {
         float pinit[3], tp[4];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) pinit[i] = s.pinit[i * B + e];
+        for (int i = 0; i < 3; ++i) pinit[i] = eb[ROWF(ROW_PINIT + i)];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) tp[i] = s.tp[i * B + e];
+        for (int i = 0; i < 4; ++i) tp[i] = eb[ROWF(ROW_TP + i)];
         sim_task(task, t, pinit, tp, kp.sim.int_pos, pdes, dpdes, sdes);
       }
       float acc[6];
-      const float aT0 = kp.sim.wl_mode ? s.actualT0[e] : -1.0f;
+      const float aT0 = kp.sim.wl_mode ? eb[ROWF(ROW_AT0)] : -1.0f;
       // plant state and metric sums through memory across the solve: they are not touched by it, and the
       // ADMM loop needs every register
 #pragma unroll
-      for (int i = 0; i < 3; ++i) s.p[i * B + e] = p[i];
+      for (int i = 0; i < 3; ++i) eb[ROWF(ROW_P + i)] = p[i];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
+      for (int i = 0; i < 9; ++i) eb[ROWF(ROW_R + i)] = R[i];
 #pragma unroll
-      for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
-      s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
+      for (int i = 0; i < 6; ++i) eb[ROWF(ROW_DQ + i)] = dq[i];
+      eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 2)] = nsolve; eb[ROWF(ROW_METRICS + 3)] = nstep;
       sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0);
 #pragma unroll
-      for (int i = 0; i < 6; ++i) s.acc[i * B + e] = acc[i];
+      for (int i = 0; i < 6; ++i) eb[ROWF(ROW_ACC + i)] = acc[i];
 #pragma unroll
-      for (int i = 0; i < 3; ++i) p[i] = *(volatile float*)(s.p + i * B + e);
+      for (int i = 0; i < 3; ++i) p[i] = *(volatile float*)(eb + ROWF(ROW_P + i));
 #pragma unroll
-      for (int i = 0; i < 9; ++i) R[i] = *(volatile float*)(s.R + i * B + e);
+      for (int i = 0; i < 9; ++i) R[i] = *(volatile float*)(eb + ROWF(ROW_R + i));
 #pragma unroll
-      for (int i = 0; i < 6; ++i) dq[i] = *(volatile float*)(s.dq + i * B + e);
-      err = *(volatile float*)(s.metrics + 0 * B + e); eff = *(volatile float*)(s.metrics + 1 * B + e);
-      nsolve = *(volatile float*)(s.metrics + 2 * B + e); nstep = *(volatile float*)(s.metrics + 3 * B + e);
-      if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, s, e, R, acc);
+      for (int i = 0; i < 6; ++i) dq[i] = *(volatile float*)(eb + ROWF(ROW_DQ + i));
+      err = *(volatile float*)(eb + ROWF(ROW_METRICS + 0)); eff = *(volatile float*)(eb + ROWF(ROW_METRICS + 1));
+      nsolve = *(volatile float*)(eb + ROWF(ROW_METRICS + 2)); nstep = *(volatile float*)(eb + ROWF(ROW_METRICS + 3));
+      if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, eb, R, acc);
       nsolve += 1.0f;
     }
     uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
@@ -258,13 +280,13 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
     }
   }
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { s.p[i * B + e] = p[i]; s.uq[i * B + e] = uq[i]; }
+  for (int i = 0; i < 3; ++i) { eb[ROWF(ROW_P + i)] = p[i]; eb[ROWF(ROW_UQ + i)] = uq[i]; }
 #pragma unroll
-  for (int i = 0; i < 9; ++i) s.R[i * B + e] = R[i];
+  for (int i = 0; i < 9; ++i) eb[ROWF(ROW_R + i)] = R[i];
 #pragma unroll
-  for (int i = 0; i < 6; ++i) s.dq[i * B + e] = dq[i];
-  s.metrics[0 * B + e] = err; s.metrics[1 * B + e] = eff; s.metrics[2 * B + e] = nsolve; s.metrics[3 * B + e] = nstep;
-  s.metrics[4 * B + e] = pert_done;
+  for (int i = 0; i < 6; ++i) eb[ROWF(ROW_DQ + i)] = dq[i];
+  eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 2)] = nsolve; eb[ROWF(ROW_METRICS + 3)] = nstep;
+  eb[ROWF(ROW_METRICS + 4)] = pert_done;
   }
   SOLVER::template release<TPB>(&tmem_slot);
 }

@@ -42,9 +42,8 @@ struct SmemStore {
   static constexpr bool kTmem = false;
   static constexpr uint32_t gstride = TPB * 16u;  // byte stride between groups: compile-time -> immediate offsets
   uint32_t sbase;  // shared-window byte address of this thread's first group
-  float* vf;       // global scratch for the first-iteration fix-up (aliases soly, dead until the end)
-  int B;
-  __device__ __forceinline__ void init(uint32_t sbase_, float* vf_, int B_) { sbase = sbase_; vf = vf_; B = B_; }
+  float* vf;       // global scratch for the first-iteration fix-up (the env's soly rows, dead until the end)
+  __device__ __forceinline__ void init(uint32_t sbase_, float* vf_) { sbase = sbase_; vf = vf_; }
   __device__ __forceinline__ void begin_iteration(int) {}
   // volatile: keeps the generated request order (the software pipeline) and re-loads every pass
   __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
@@ -71,16 +70,15 @@ struct SmemStore {
   }
   __device__ __forceinline__ void end_writes() {}
   __device__ __forceinline__ void sync() const {}
-  __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
-  __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
+  __device__ __forceinline__ float Vf(int i) const { return vf[ROWF(i)]; }
+  __device__ __forceinline__ void setVf(int i, float v) { vf[ROWF(i)] = v; }
 };
 
 struct TmemStore {
   static constexpr bool kTmem = true;
   uint32_t tbase;  // TMEM address of this warp's word 0: lane block 32*(warp%4), column block 256*(warp/4)
   float* vf;
-  int B;
-  __device__ __forceinline__ void init(uint32_t tbase_, float* vf_, int B_) { tbase = tbase_; vf = vf_; B = B_; }
+  __device__ __forceinline__ void init(uint32_t tbase_, float* vf_) { tbase = tbase_; vf = vf_; }
   __device__ __forceinline__ void begin_iteration(int) {}
   __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
     asm volatile(
@@ -116,8 +114,8 @@ struct TmemStore {
 #else
   __device__ __forceinline__ void sync() const {}
 #endif
-  __device__ __forceinline__ float Vf(int i) const { return vf[(size_t)i * B]; }
-  __device__ __forceinline__ void setVf(int i, float v) { vf[(size_t)i * B] = v; }
+  __device__ __forceinline__ float Vf(int i) const { return vf[ROWF(i)]; }
+  __device__ __forceinline__ void setVf(int i, float v) { vf[ROWF(i)] = v; }
 };
 
 // TMEM allocation for a CTA of TPB threads: (TPB / 128) * 256 columns, all 128 lanes.  Warp 0 allocates and frees.
@@ -143,28 +141,27 @@ __device__ __forceinline__ void tmem_release(const uint32_t* slot) {
 }
 
 struct GlobIO {
-  const DevState& s;
-  int e;
-  __device__ __forceinline__ GlobIO(const DevState& s_, int e_) : s(s_), e(e_) {}
+  float* eb;  // env_base(): every row of this env at a compile-time offset
+  __device__ __forceinline__ explicit GlobIO(float* eb_) : eb(eb_) {}
   // (a prefetch.global.L2 of the 123 warm-start rows here cost ~500 once-per-solve instructions -- address arithmetic
   // plus CCTL -- for a latency that the 123 independent loads issued together later overlap anyway; removed)
   __device__ __forceinline__ void prefetch_warm_start() const {}
   // inputs parked over the ADMM loop (solx is dead until the solution is stored); volatile read-back so that the
   // compiler cannot keep the values in registers instead
-  __device__ __forceinline__ void stash(int k, float v) { s.solx[(size_t)k * s.B + e] = v; }
-  __device__ __forceinline__ float unstash(int k) const { return *(volatile const float*)(s.solx + (size_t)k * s.B + e); }
-  __device__ __forceinline__ float ld_xs(int j) const { return s.xs[(size_t)j * s.B + e]; }
-  __device__ __forceinline__ float ld_zs(int i) const { return s.zs[(size_t)i * s.B + e]; }
-  __device__ __forceinline__ float ld_ys(int i) const { return s.ys[(size_t)i * s.B + e]; }
-  __device__ __forceinline__ float ld_D(int j) const { return s.D[(size_t)j * s.B + e]; }
-  __device__ __forceinline__ float ld_E(int i) const { return s.E[(size_t)i * s.B + e]; }
-  __device__ __forceinline__ void st_xs(int j, float v) { s.xs[(size_t)j * s.B + e] = v; }
-  __device__ __forceinline__ void st_zs(int i, float v) { s.zs[(size_t)i * s.B + e] = v; }
-  __device__ __forceinline__ void st_ys(int i, float v) { s.ys[(size_t)i * s.B + e] = v; }
-  __device__ __forceinline__ void st_D(int j, float v) { s.D[(size_t)j * s.B + e] = v; }
-  __device__ __forceinline__ void st_E(int i, float v) { s.E[(size_t)i * s.B + e] = v; }
-  __device__ __forceinline__ void st_solx(int j, float v) { s.solx[(size_t)j * s.B + e] = v; }
-  __device__ __forceinline__ void st_soly(int i, float v) { s.soly[(size_t)i * s.B + e] = v; }
+  __device__ __forceinline__ void stash(int k, float v) { eb[ROWF(ROW_SOLX + k)] = v; }
+  __device__ __forceinline__ float unstash(int k) const { return *(volatile const float*)(eb + ROWF(ROW_SOLX + k)); }
+  __device__ __forceinline__ float ld_xs(int j) const { return eb[ROWF(ROW_XS + j)]; }
+  __device__ __forceinline__ float ld_zs(int i) const { return eb[ROWF(ROW_ZS + i)]; }
+  __device__ __forceinline__ float ld_ys(int i) const { return eb[ROWF(ROW_YS + i)]; }
+  __device__ __forceinline__ float ld_D(int j) const { return eb[ROWF(ROW_D + j)]; }
+  __device__ __forceinline__ float ld_E(int i) const { return eb[ROWF(ROW_E + i)]; }
+  __device__ __forceinline__ void st_xs(int j, float v) { eb[ROWF(ROW_XS + j)] = v; }
+  __device__ __forceinline__ void st_zs(int i, float v) { eb[ROWF(ROW_ZS + i)] = v; }
+  __device__ __forceinline__ void st_ys(int i, float v) { eb[ROWF(ROW_YS + i)] = v; }
+  __device__ __forceinline__ void st_D(int j, float v) { eb[ROWF(ROW_D + j)] = v; }
+  __device__ __forceinline__ void st_E(int i, float v) { eb[ROWF(ROW_E + i)] = v; }
+  __device__ __forceinline__ void st_solx(int j, float v) { eb[ROWF(ROW_SOLX + j)] = v; }
+  __device__ __forceinline__ void st_soly(int i, float v) { eb[ROWF(ROW_SOLY + i)] = v; }
 };
 
 #ifndef UMPC_DEFAULT_TPB
@@ -183,6 +180,7 @@ struct SolverF32 {
   typedef UmpcParams Params;
   static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
   ST st;
+  float* eb;
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) {
     if (ST::kTmem) return tmem_acquire<TPB>(slot);
@@ -192,11 +190,14 @@ struct SolverF32 {
   static __device__ __forceinline__ void release(const uint32_t* slot) {
     if (ST::kTmem) tmem_release<TPB>(slot);
   }
-  __device__ __forceinline__ void init(uint32_t scratch_base, const DevState& s, int e) { st.init(scratch_base, s.soly + e, s.B); }
+  __device__ __forceinline__ void init(uint32_t scratch_base, const DevState& s, int e) {
+    eb = env_base(s, e);
+    st.init(scratch_base, eb + ROWF(ROW_SOLY));
+  }
   __device__ __forceinline__ void qpdata(const Params& par, const DevState& s, int e, const float p[3], const float R[9],
                                          const float dq[6], const float pd[3], const float dpd[3], const float sd[3], float aT0) {
     UmpcQP qp;
-    umpc_build(par, qp, p, R, dq, pd, dpd, sd, aT0 >= 0.0f ? aT0 : s.T0[e]);
+    umpc_build(par, qp, p, R, dq, pd, dpd, sd, aT0 >= 0.0f ? aT0 : eb[ROWF(ROW_T0)]);
     float out[216];
     umpc_qpdata(par, qp, out);
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = out[k];
@@ -204,8 +205,8 @@ struct SolverF32 {
   __device__ __forceinline__ void update(const Params& par, const DevState& s, int e, float uq[3], float acc[6], const float p[3],
                                          const float R[9], const float dq[6], const float pd[3], const float dpd[3],
                                          const float sd[3], float aT0) {
-    GlobIO io(s, e);
-    float T0 = s.T0[e];
+    GlobIO io(eb);
+    float T0 = eb[ROWF(ROW_T0)];
     UmpcInfo info;
     if constexpr (PERENV) {
       Params pe = par;
@@ -214,8 +215,8 @@ struct SolverF32 {
     } else {
       umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
     }
-    s.T0[e] = T0;
-    store_info(s, e, info.iter, info.status, info.pri_res, info.dua_res);
+    eb[ROWF(ROW_T0)] = T0;
+    store_info(eb, info.iter, info.status, info.pri_res, info.dua_res);
   }
 };
 
@@ -225,22 +226,23 @@ __global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __g
                                  const float* __restrict__ pdotdes, float* __restrict__ info2) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= s.nreal) return;
+  float* const eb = env_base(s, e);
   float h[6], pd[6], u0[4], w0[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) { h[i] = h0[(size_t)e * 6 + i]; pd[i] = pdotdes[(size_t)e * 6 + i]; }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) u0[i] = s.wl_u0[(size_t)i * s.B + e];
+  for (int i = 0; i < 4; ++i) u0[i] = eb[ROWF(ROW_WLU0 + i)];
   int iter = 0, status = 0;
   if (mode == 1) {
     wl_con_update(wlp, u0, w0, h, pd);
   } else {
     WlqpState w;
-    load_wlqp(s, e, w);
+    load_wlqp(eb, w);
     wlqp_update(wlp, w, u0, w0, h, pd, &iter, &status);
-    store_wlqp(s, e, w);
+    store_wlqp(eb, w);
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) { s.wl_u0[(size_t)i * s.B + e] = u0[i]; u1[(size_t)e * 4 + i] = u0[i]; }
+  for (int i = 0; i < 4; ++i) { eb[ROWF(ROW_WLU0 + i)] = u0[i]; u1[(size_t)e * 4 + i] = u0[i]; }
 #pragma unroll
   for (int i = 0; i < 6; ++i) w0o[(size_t)e * 6 + i] = w0[i];
   if (info2) { info2[(size_t)e * 2] = (float)iter; info2[(size_t)e * 2 + 1] = (float)status; }
@@ -250,14 +252,14 @@ __global__ void wl_update_kernel(const __grid_constant__ WlParams wlp, const __g
 __global__ void reduce_metrics_kernel(const __grid_constant__ DevState s, double* __restrict__ out8) {
   double a[6] = {0, 0, 0, 0, 0, 0};
   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < s.nreal; e += gridDim.x * blockDim.x) {
-    const size_t B = s.B;
-    const float err = s.metrics[0 * B + e], eff = s.metrics[1 * B + e];
-    const float ns = s.metrics[3 * B + e];
+    const float* eb = env_base(s, e);
+    const float err = eb[ROWF(ROW_METRICS + 0)], eff = eb[ROWF(ROW_METRICS + 1)];
+    const float ns = eb[ROWF(ROW_METRICS + 3)];
     bool bad = !(isfinite(err) && isfinite(eff));
 #pragma unroll
-    for (int i = 0; i < 3; ++i) bad = bad || !isfinite(s.p[i * B + e]);
+    for (int i = 0; i < 3; ++i) bad = bad || !isfinite(eb[ROWF(ROW_P + i)]);
     if (!bad) { a[0] += err; a[1] += eff; a[5] = fmax(a[5], ns > 0 ? (double)err / ns : 0.0); }
-    a[2] += s.metrics[2 * B + e]; a[3] += ns; a[4] += bad ? 1.0 : 0.0;
+    a[2] += eb[ROWF(ROW_METRICS + 2)]; a[3] += ns; a[4] += bad ? 1.0 : 0.0;
   }
 #pragma unroll
   for (int k = 0; k < 6; ++k)
@@ -277,6 +279,14 @@ __global__ void reduce_metrics_kernel(const __grid_constant__ DevState s, double
       old = atomicCAS(addr, assumed, (unsigned long long)__double_as_longlong(a[5]));
     } while (assumed != old);
   }
+}
+
+// ---- kernel 4b: set rows [row0, row0+k) of every env to a value (state initialisation) ---------------
+__global__ void fill_rows_kernel(float* __restrict__ slab, int nslots, int row0, int k, float v) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nslots) return;
+  float* eb = slab + tile_off(e);
+  for (int i = 0; i < k; ++i) eb[ROWF(row0 + i)] = v;
 }
 
 // ---- kernel 5: FP32 pipe peak (independent FFMA chains in registers) --------------------------
@@ -406,18 +416,21 @@ extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
   return UMPC_OK;
 }
 
+static int fill_rows(UmpcBatch* b, int row0, int k, float v) {
+  fill_rows_kernel<<<(b->Bp + 255) / 256, 256, 0, b->stream>>>(b->slab, b->Bp, row0, k, v);
+  CK(cudaGetLastError());
+  return UMPC_OK;
+}
+
 static int reset_state(UmpcBatch* b) {
   CK(cudaMemsetAsync(b->slab, 0, b->slab_floats * sizeof(float), b->stream));
   // D = E = 1 ; WL u0 ; wlqp D = E = c = 1 ; actualT0 = -1
-  std::vector<float> ones((size_t)b->Bp * 45, 1.0f);
-  CK(cudaMemcpyAsync(b->s.D, ones.data(), (size_t)45 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->s.E, ones.data(), (size_t)39 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->s.wlqp + (size_t)12 * b->Bp, ones.data(), (size_t)9 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
-  std::vector<float> tmp((size_t)b->Bp * 4);
-  for (int i = 0; i < 4; ++i) for (int e = 0; e < b->Bp; ++e) tmp[(size_t)i * b->Bp + e] = b->bp.wl_u0[i];
-  CK(cudaMemcpyAsync(b->s.wl_u0, tmp.data(), (size_t)4 * b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
-  for (int e = 0; e < b->Bp; ++e) tmp[e] = -1.0f;
-  CK(cudaMemcpyAsync(b->s.actualT0, tmp.data(), (size_t)b->Bp * 4, cudaMemcpyHostToDevice, b->stream));
+  int rc;
+  if ((rc = fill_rows(b, ROW_D, 45 + 39, 1.0f))) return rc;       // D and E are adjacent
+  if ((rc = fill_rows(b, ROW_WLQP + 12, 9, 1.0f))) return rc;
+  for (int i = 0; i < 4; ++i)
+    if ((rc = fill_rows(b, ROW_WLU0 + i, 1, b->bp.wl_u0[i]))) return rc;
+  if ((rc = fill_rows(b, ROW_AT0, 1, -1.0f))) return rc;
   CK(cudaStreamSynchronize(b->stream));
   if (b->conv) CK((cudaError_t)umpc_conv_reset(b->conv, &b->s, b->stream));
   b->step = 0; b->thl = 0.0;
@@ -446,21 +459,18 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&b->ev0));
   CK(cudaEventCreate(&b->ev1));
-  // one slab, SoA rows of B floats
-  const int rows = 3 + 9 + 6 + 3 + 6 /*plant*/ + 1 + 45 + 39 + 39 + 45 + 39 + 45 + 39 + 4 /*ctrl*/ + 1 /*task*/ + 4 + 3 + 1 + 5 +
-                   4 + 25;
+  // one slab, tiled struct of arrays float[Bp/32][UMPC_ROWS][32] (umpc_dev.cuh)
   const int np = b->Bp;
-  b->slab_floats = (size_t)rows * np;
+  b->slab_floats = (size_t)UMPC_ROWS * np;
   CK(cudaMalloc(&b->slab, b->slab_floats * sizeof(float)));
-  float* q = b->slab;
-  auto take = [&](int r) { float* t = q; q += (size_t)r * np; return t; };
   DevState& s = b->s;
-  s.B = np; s.nreal = nenv;
-  s.p = take(3); s.R = take(9); s.dq = take(6); s.uq = take(3); s.acc = take(6);
-  s.T0 = take(1); s.xs = take(45); s.zs = take(39); s.ys = take(39); s.D = take(45); s.E = take(39);
-  s.solx = take(45); s.soly = take(39); s.info = take(4);
-  s.task = (int*)take(1); s.tp = take(4); s.pinit = take(3); s.actualT0 = take(1); s.metrics = take(5);
-  s.wl_u0 = take(4); s.wlqp = take(25);
+  s.B = np; s.nreal = nenv; s.slab = b->slab;
+  auto row = [&](int r) { return b->slab + ROWF(r); };  // host handles: the row block of env 0
+  s.p = row(ROW_P); s.R = row(ROW_R); s.dq = row(ROW_DQ); s.uq = row(ROW_UQ); s.acc = row(ROW_ACC);
+  s.T0 = row(ROW_T0); s.xs = row(ROW_XS); s.zs = row(ROW_ZS); s.ys = row(ROW_YS); s.D = row(ROW_D); s.E = row(ROW_E);
+  s.solx = row(ROW_SOLX); s.soly = row(ROW_SOLY); s.info = row(ROW_INFO);
+  s.task = (int*)row(ROW_TASK); s.tp = row(ROW_TP); s.pinit = row(ROW_PINIT); s.actualT0 = row(ROW_AT0); s.metrics = row(ROW_METRICS);
+  s.wl_u0 = row(ROW_WLU0); s.wlqp = row(ROW_WLQP);
   s.qpdata = nullptr;
   s.wts = nullptr;
   s.c64 = nullptr;
@@ -647,8 +657,31 @@ extern "C" int umpcBatchEnvStep(UmpcBatch* b, float* uquad, float* accdes, float
   return run_chunked(b, in, 7, out, 5, duq, dacc, din, actualT0 ? daT : nullptr, dpn, dRn, ddqn);
 }
 
-// SoA [k][B] on device <-> [B][k] on host (diagnostics / state exchange; not on the hot path)
-static int get_rows(UmpcBatch* b, const float* dev, int k, float* host) {
+// tiled SoA on device <-> [B][k] on host (diagnostics / state exchange; not on the hot path).  `dev` is a host handle
+// of DevState (row block of env 0): the k rows of every tile are gathered with one strided 2-D copy.
+static int get_rows(UmpcBatch* b, const void* dev, int k, void* host_) {
+  if (!host_) return UMPC_OK;
+  float* host = (float*)host_;
+  const size_t B = b->B, nt = b->Bp / 32;
+  std::vector<float> tmp(nt * k * 32);
+  CK(cudaMemcpy2DAsync(tmp.data(), (size_t)k * 128, dev, (size_t)UMPC_ROWS * 128, (size_t)k * 128, nt, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  for (size_t e = 0; e < B; ++e)
+    for (int i = 0; i < k; ++i) host[e * k + i] = tmp[((e >> 5) * k + i) * 32 + (e & 31)];
+  return UMPC_OK;
+}
+static int put_rows(UmpcBatch* b, void* dev, int k, const void* host_) {
+  const float* host = (const float*)host_;
+  const size_t B = b->B, nt = b->Bp / 32;
+  std::vector<float> tmp(nt * k * 32, 0.0f);
+  for (size_t e = 0; e < B; ++e)
+    for (int i = 0; i < k; ++i) tmp[((e >> 5) * k + i) * 32 + (e & 31)] = host[e * k + i];
+  CK(cudaMemcpy2DAsync(dev, (size_t)UMPC_ROWS * 128, tmp.data(), (size_t)k * 128, (size_t)k * 128, nt, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+// plain [k][Bp] rows (the optional QP-data dump)
+static int get_rows_soa(UmpcBatch* b, const float* dev, int k, float* host) {
   if (!host) return UMPC_OK;
   const size_t B = b->B, P = b->Bp;
   std::vector<float> tmp(P * k);
@@ -656,15 +689,6 @@ static int get_rows(UmpcBatch* b, const float* dev, int k, float* host) {
   CK(cudaStreamSynchronize(b->stream));
   for (size_t e = 0; e < B; ++e)
     for (int i = 0; i < k; ++i) host[e * k + i] = tmp[(size_t)i * P + e];
-  return UMPC_OK;
-}
-static int put_rows(UmpcBatch* b, float* dev, int k, const float* host) {
-  const size_t B = b->B, P = b->Bp;
-  std::vector<float> tmp(P * k, 0.0f);
-  for (size_t e = 0; e < B; ++e)
-    for (int i = 0; i < k; ++i) tmp[(size_t)i * P + e] = host[e * k + i];
-  CK(cudaMemcpyAsync(dev, tmp.data(), P * k * 4, cudaMemcpyHostToDevice, b->stream));
-  CK(cudaStreamSynchronize(b->stream));
   return UMPC_OK;
 }
 
@@ -692,7 +716,7 @@ extern "C" int umpcBatchGetQPData(UmpcBatch* b, float* qp) {
     CK(cudaMemset(b->s.qpdata, 0, (size_t)216 * b->Bp * sizeof(float)));
     b->have_qpdata = true;
   }
-  return get_rows(b, b->s.qpdata, 216, qp);
+  return get_rows_soa(b, b->s.qpdata, 216, qp);
 }
 
 extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, const float* dq, const int* task,
@@ -704,12 +728,13 @@ extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, c
   if ((rc = put_rows(b, b->s.pinit, 3, p))) return rc;
   if ((rc = put_rows(b, b->s.R, 9, R))) return rc;
   if ((rc = put_rows(b, b->s.dq, 6, dq))) return rc;
-  if (task) CK(cudaMemcpy(b->s.task, task, (size_t)b->B * sizeof(int), cudaMemcpyHostToDevice));
-  else CK(cudaMemset(b->s.task, 0, (size_t)b->Bp * sizeof(int)));
+  if (task) { if ((rc = put_rows(b, b->s.task, 1, task))) return rc; }  // 4-byte ints travel as bit patterns
+  else if ((rc = fill_rows(b, ROW_TASK, 1, 0.0f))) return rc;
   if (tp) { if ((rc = put_rows(b, b->s.tp, 4, tp))) return rc; }
-  else CK(cudaMemset(b->s.tp, 0, (size_t)4 * b->Bp * sizeof(float)));
-  CK(cudaMemset(b->s.uq, 0, (size_t)3 * b->Bp * sizeof(float)));
-  CK(cudaMemset(b->s.metrics, 0, (size_t)5 * b->Bp * sizeof(float)));
+  else if ((rc = fill_rows(b, ROW_TP, 4, 0.0f))) return rc;
+  if ((rc = fill_rows(b, ROW_UQ, 3, 0.0f))) return rc;
+  if ((rc = fill_rows(b, ROW_METRICS, 5, 0.0f))) return rc;
+  CK(cudaStreamSynchronize(b->stream));
   b->step = 0; b->thl = 0.0;
   return UMPC_OK;
 }
@@ -851,7 +876,7 @@ extern "C" void* umpcBatchDevPtr(UmpcBatch* b, const char* name) {
       {"p", s.p}, {"R", s.R}, {"dq", s.dq}, {"uq", s.uq}, {"acc", s.acc}, {"T0", s.T0}, {"xs", s.xs}, {"zs", s.zs},
       {"ys", s.ys}, {"D", s.D}, {"E", s.E}, {"solx", s.solx}, {"soly", s.soly}, {"info", s.info}, {"task", s.task},
       {"tp", s.tp}, {"pinit", s.pinit}, {"actualT0", s.actualT0}, {"metrics", s.metrics}, {"wl_u0", s.wl_u0},
-      {"wlqp", s.wlqp}, {"stage_in", b->d_in}, {"stage_out", b->d_out}, {"stream", (void*)b->stream}};
+      {"wlqp", s.wlqp}, {"slab", s.slab}, {"stage_in", b->d_in}, {"stage_out", b->d_out}, {"stream", (void*)b->stream}};
   for (auto& t : tab)
     if (!strcmp(t.n, name)) return t.p;
   return nullptr;
@@ -1047,7 +1072,7 @@ static int wl_single(const WlParams& wp, int mode, float u0[4], WlqpState* qs, c
   float in[12], out[10];
   memcpy(in, h0, 24); memcpy(in + 6, pdotdes, 24);
   CK(cudaMemcpyAsync(b->d_in, in, sizeof(in), cudaMemcpyHostToDevice, b->stream));
-  const size_t pitch = (size_t)b->Bp * sizeof(float);  // SoA rows: element i of env 0 sits at i * Bp
+  const size_t pitch = 32 * sizeof(float);  // tiled SoA: element i of env 0 sits at 32 i (umpc_dev.cuh)
   CK(cudaMemcpy2DAsync(b->s.wl_u0, pitch, u0, 4, 4, 4, cudaMemcpyHostToDevice, b->stream));
   if (qs) {
     float q[25];
