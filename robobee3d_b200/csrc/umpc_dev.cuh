@@ -152,7 +152,9 @@ umpc_update_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params
   const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;  // env0: first env of this launch (chunked host-buffer calls)
   __shared__ uint32_t tmem_slot;
   const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
-  if (e < s.B) {  // B is a multiple of 256: whole CTAs (the body contains CTA-wide barriers)
+  // No bounds test: B and every launch's env range are multiples of 256, so all threads of the grid own an env slot.
+  // (A thread-dependent branch around the body would also keep ptxas from using the uniform datapath inside it.)
+  {
   float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -209,7 +211,7 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   __shared__ uint32_t tmem_slot;
   const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);
-  if (e < s.B) {
+  {
   float* const eb = env_base(s, e);
   float p[3], R[9], dq[6], uq[3];
 #pragma unroll
