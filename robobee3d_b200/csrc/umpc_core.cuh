@@ -110,6 +110,9 @@ UMPC_HD ureal umpc_nan() { return nan(""); }
 
 #include "umpc_gen.cuh"
 
+// scratch words behind the (UMPC_NX + 1) / 2 sigma/D^2 pairs: the 9 loop-invariant input-column constants (kpu)
+#define UMPC_KPU_POS (UMPC_GEN_OFF_SG + (UMPC_NX + 1) / 2)
+
 UMPC_HD int umpc_imin(int a, int b) { return a < b ? a : b; }
 
 UMPC_HD ureal umpc_limit_scaling(ureal v) {
@@ -330,7 +333,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
   ureal c = 1.0f;
-  ureal xs[UMPC_NX], w[UMPC_NEQ], kpu[UMPC_NX - UMPC_NEQ], z3[3], y3[3];
+  ureal xs[UMPC_NX], w[UMPC_NEQ], z3[3], y3[3];
   {
     ureal D[UMPC_NX], E[UMPC_NC];
 #pragma unroll
@@ -433,9 +436,15 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       umpc_gen_ATv_add(w0, v0, a);
       umpc_gen_ATv_add(wf, vf, a);
       // constant of the input-column part: w_u = kappa_u + B_u' vhat, vhat = M^-T (w_o - kappa_o), kappa_u = 0
-      umpc_gen_gu_from_go(kpu, kapo, a);
+      // It is loop-invariant: parked in the spare words behind the sigma/D^2 pairs of the scratch (same chunk as the
+      // pairs of the input columns, so the loop gets it with a load it issues anyway) instead of 9 registers.
+      {
+        ureal kpu[UMPC_NX - UMPC_NEQ];
+        umpc_gen_gu_from_go(kpu, kapo, a);
 #pragma unroll
-      for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) kpu[i] = -kpu[i];
+        for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) st.setW(UMPC_KPU_POS + i, -kpu[i]);
+        st.end_writes();
+      }
       // The first pass forms r with w0 but must continue from wf:  w1 = wf - alpha w0 + t  (t = the rest of the
       // update).  Written as the regular update (1 - alpha) X + t of a substitute X = (wf - alpha w0) / (1 - alpha),
       // so that the loop body has no first-iteration special case beyond swapping w (alpha != 1: OSQP's 1.6).
@@ -448,7 +457,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
 #pragma unroll
     for (int j = 0; j < UMPC_NX; ++j) io.st_solx(j, xs[j]);
 #pragma unroll
-    for (int j = 0; j < UMPC_NEQ; ++j) io.st_soly(j, w[j] + (j < 9 ? kpu[j] : 0) + (j < 3 ? z3[j] + y3[j] + W3[j] : 0));
+    for (int j = 0; j < UMPC_NEQ; ++j) io.st_soly(j, w[j] + (j < 3 ? z3[j] + y3[j] + W3[j] : 0));
 #pragma unroll
     for (int i = 0; i < 3; ++i) uquad[i] = 0;
 #pragma unroll
@@ -485,8 +494,6 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     ureal wu[UMPC_NX - UMPC_NEQ];
     umpc_gen_gu_from_go(wu, w, a);
 #pragma unroll
-    for (int i = 0; i < UMPC_NX - UMPC_NEQ; ++i) wu[i] += kpu[i];
-#pragma unroll
     for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
       ureal wd[UMPC_GEN_CHUNK];
       st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
@@ -498,7 +505,13 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int j = 2 * (UMPC_GEN_CHUNK * gq + u) + h;
-          if (j < UMPC_NX) r[j] = s2[h] * xs[j] + (j < UMPC_NEQ ? w[j < UMPC_NEQ ? j : 0] : wu[j >= UMPC_NEQ && j < UMPC_NX ? j - UMPC_NEQ : 0]);
+          if (j < UMPC_NEQ) r[j < UMPC_NEQ ? j : 0] = s2[h] * xs[j < UMPC_NEQ ? j : 0] + w[j < UMPC_NEQ ? j : 0];
+          else if (j < UMPC_NX) {  // input columns: w_u = kpu + B_u' vhat, kpu from the chunk's spare words
+            const int i = j >= UMPC_NEQ && j < UMPC_NX ? j - UMPC_NEQ : 0;
+            constexpr int kq = UMPC_KPU_POS - UMPC_GEN_OFF_SG - UMPC_GEN_CHUNK * ((UMPC_KPU_POS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK);
+            static_assert((UMPC_NX - 1) / 2 / UMPC_GEN_CHUNK == (UMPC_KPU_POS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK, "kpu rides in the chunk of the input columns' pairs");
+            r[j < UMPC_NX ? j : 0] = s2[h] * xs[j < UMPC_NX ? j : 0] + (wu[i] + wd[kq + i < UMPC_GEN_CHUNK ? kq + i : 0]);
+          }
         }
       }
     }
