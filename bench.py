@@ -270,9 +270,10 @@ def main():
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
                     # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the ncu --set full capture summarised in
-                    # profiles/r01c_ncu_full_umpc_rollout_kernel_tmem.txt (50.5 + 126.3 MB per launch of 65,536 envs; the
-                    # algorithmic figure is 2,172 B x 65,536 = 142 MB); only known for that launch shape
-                    "traffic": 176.74e6 if (nenv == 65536 and spl == 1 and args.workload == "mc" and not args.converged) else None,
+                    # profiles/r01e_ncu_full_umpc_rollout_kernel_tmem.txt (42.4 + 35.3 MB per launch of 65,536 envs; the
+                    # algorithmic figure is 2,172 B x 65,536 = 142 MB -- part of the 96 MB state slab stays in the 126 MB L2
+                    # from one launch to the next); only known for that launch shape
+                    "traffic": 77.7e6 if (nenv == 65536 and spl == 1 and args.workload == "mc" and not args.converged) else None,
                     "kernel": "umpc_rollout_kernel",
                     "note": "FP32 CUDA-core pipe bound (arithmetic intensity %.0f flop/B vs ridge ~11): peak = FFMA "
                             "microbenchmark run in this process (MEASURED_PEAKS.json has no FP32 figure); achieved = "
