@@ -2,12 +2,16 @@
 //
 // Mapping: ONE THREAD PER ENVIRONMENT.  Every QP has the same sparsity, so the whole
 // update is straight-line code with compile-time indices (umpc_gen.cuh); the ADMM
-// vectors live in registers, the per-QP factor of K (167 + 45 values), alpha*W, sigma/D^2
-// and the bounds live in shared memory laid out [entry][thread] (bank = thread, conflict
-// free), and the warm start / plant state live in HBM as struct-of-arrays [k][B] so that
-// a warp's loads of one component are one 128-byte line.  There is no inter-thread
-// communication at all; the kernels are bound by the FP32 pipe and shared-memory
-// bandwidth, not by HBM (DESIGN.md has the byte/flop accounting).
+// vectors live in registers, the per-QP factor of K (167 + 45 values) and the sigma/D^2
+// pairs live in a 256-word per-thread scratch in TENSOR MEMORY (tcgen05.ld/st; a
+// shared-memory store with the same interface is the second launch shape), and the warm
+// start / plant state live in HBM as a struct of arrays tiled by warp (umpc_dev.cuh): a
+// warp's access to one component is one 128-byte line at an immediate offset from one
+// base pointer.  There is no inter-thread communication at all; the kernels are bound by
+// the FP32 pipe / instruction issue, not by HBM (DESIGN.md has the byte/flop accounting).
+// The kernel templates themselves are in umpc_dev.cuh (shared with umpc_conv.cu, the
+// float64 converged mode); this file holds the float32 solver policy, the scratch stores,
+// the WL / reduction kernels and the host side of the C-ABI.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
