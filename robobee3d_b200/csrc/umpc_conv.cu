@@ -26,7 +26,7 @@ namespace umpc64 {
 #include "umpc_core.cuh"
 }  // namespace umpc64
 
-// ---- rows of the double slab DevState::c64 (each row: B doubles) -----------------------------------------------
+// ---- rows of the double slab DevState::c64, tiled by warp like the float slab: double[B/32][C64_ROWS][32] ---------
 enum {
   C64_T0 = 0,
   C64_RHO = 1,
@@ -41,52 +41,54 @@ enum {
   C64_ROWS = C64_SCR + UMPC_GEN_NWORDS
 };
 
+#define ROWD(r) ((r) * 32)  // double offset of row r inside a tile
+__host__ __device__ __forceinline__ size_t tile_off64(int e) { return (size_t)(e >> 5) * (C64_ROWS * 32) + (size_t)(e & 31); }
+
 struct GlobStore64 {
-  double* w;   // this env's column of the scratch rows
+  double* w;   // this env's scratch rows (immediate offsets from here)
   double* vf;
-  size_t B;
-  __device__ __forceinline__ void init(double* c64, size_t B_, int e) {
-    B = B_; w = c64 + (size_t)C64_SCR * B + e; vf = c64 + (size_t)C64_VF * B + e;
+  __device__ __forceinline__ void init(double* c64, int e) {
+    double* cb = c64 + tile_off64(e);
+    w = cb + ROWD(C64_SCR); vf = cb + ROWD(C64_VF);
   }
   __device__ __forceinline__ void begin_iteration(int) {}
   __device__ __forceinline__ void issue(int c, double (&v)[UMPC_GEN_CHUNK]) const {
 #pragma unroll
-    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) v[i] = __ldcg(w + (size_t)(c * UMPC_GEN_CHUNK + i) * B);
+    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) v[i] = __ldcg(w + ROWD(c * UMPC_GEN_CHUNK + i));
   }
   __device__ __forceinline__ void wait(double (&)[UMPC_GEN_CHUNK]) const {}
-  __device__ __forceinline__ void setW(int e, double v) { __stcg(w + (size_t)e * B, v); }
+  __device__ __forceinline__ void setW(int e, double v) { __stcg(w + ROWD(e), v); }
   __device__ __forceinline__ void setChunk(int c, const double (&v)[UMPC_GEN_CHUNK]) {
 #pragma unroll
-    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) __stcg(w + (size_t)(c * UMPC_GEN_CHUNK + i) * B, v[i]);
+    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) __stcg(w + ROWD(c * UMPC_GEN_CHUNK + i), v[i]);
   }
   __device__ __forceinline__ void end_writes() {}
   __device__ __forceinline__ void sync() const {}
   __device__ __forceinline__ bool all(bool p) const { return __all_sync(0xffffffffu, p); }
-  __device__ __forceinline__ double Vf(int i) const { return __ldcg(vf + (size_t)i * B); }
-  __device__ __forceinline__ void setVf(int i, double v) { __stcg(vf + (size_t)i * B, v); }
+  __device__ __forceinline__ double Vf(int i) const { return __ldcg(vf + ROWD(i)); }
+  __device__ __forceinline__ void setVf(int i, double v) { __stcg(vf + ROWD(i), v); }
 };
 
 // controller state in double; the float rows of DevState are kept as mirrors for the getters of the C-ABI
 struct GlobIO64 {
   float* eb;  // float mirrors: the env's rows of the tiled slab (umpc_dev.cuh)
-  double* c;
-  size_t B;
-  __device__ __forceinline__ GlobIO64(const DevState& s_, int e_) : eb(env_base(s_, e_)), c(s_.c64 + e_), B(s_.B) {}
+  double* c;  // the env's rows of the double slab
+  __device__ __forceinline__ GlobIO64(const DevState& s_, int e_) : eb(env_base(s_, e_)), c(s_.c64 + tile_off64(e_)) {}
   __device__ __forceinline__ void prefetch_warm_start() const {}
-  __device__ __forceinline__ void stash(int k, double v) { c[(size_t)(C64_STASH + k) * B] = v; }
-  __device__ __forceinline__ double unstash(int k) const { return *(volatile const double*)(c + (size_t)(C64_STASH + k) * B); }
-  __device__ __forceinline__ double ld_rho() const { return c[(size_t)C64_RHO * B]; }
-  __device__ __forceinline__ void st_rho(double v) { c[(size_t)C64_RHO * B] = v; }
-  __device__ __forceinline__ double ld_xs(int j) const { return c[(size_t)(C64_XS + j) * B]; }
-  __device__ __forceinline__ double ld_zs(int i) const { return c[(size_t)(C64_ZS + i) * B]; }
-  __device__ __forceinline__ double ld_ys(int i) const { return c[(size_t)(C64_YS + i) * B]; }
-  __device__ __forceinline__ double ld_D(int j) const { return c[(size_t)(C64_D + j) * B]; }
-  __device__ __forceinline__ double ld_E(int i) const { return c[(size_t)(C64_E + i) * B]; }
-  __device__ __forceinline__ void st_xs(int j, double v) { c[(size_t)(C64_XS + j) * B] = v; eb[ROWF(ROW_XS + j)] = (float)v; }
-  __device__ __forceinline__ void st_zs(int i, double v) { c[(size_t)(C64_ZS + i) * B] = v; eb[ROWF(ROW_ZS + i)] = (float)v; }
-  __device__ __forceinline__ void st_ys(int i, double v) { c[(size_t)(C64_YS + i) * B] = v; eb[ROWF(ROW_YS + i)] = (float)v; }
-  __device__ __forceinline__ void st_D(int j, double v) { c[(size_t)(C64_D + j) * B] = v; eb[ROWF(ROW_D + j)] = (float)v; }
-  __device__ __forceinline__ void st_E(int i, double v) { c[(size_t)(C64_E + i) * B] = v; eb[ROWF(ROW_E + i)] = (float)v; }
+  __device__ __forceinline__ void stash(int k, double v) { c[ROWD(C64_STASH + k)] = v; }
+  __device__ __forceinline__ double unstash(int k) const { return *(volatile const double*)(c + ROWD(C64_STASH + k)); }
+  __device__ __forceinline__ double ld_rho() const { return c[ROWD(C64_RHO)]; }
+  __device__ __forceinline__ void st_rho(double v) { c[ROWD(C64_RHO)] = v; }
+  __device__ __forceinline__ double ld_xs(int j) const { return c[ROWD(C64_XS + j)]; }
+  __device__ __forceinline__ double ld_zs(int i) const { return c[ROWD(C64_ZS + i)]; }
+  __device__ __forceinline__ double ld_ys(int i) const { return c[ROWD(C64_YS + i)]; }
+  __device__ __forceinline__ double ld_D(int j) const { return c[ROWD(C64_D + j)]; }
+  __device__ __forceinline__ double ld_E(int i) const { return c[ROWD(C64_E + i)]; }
+  __device__ __forceinline__ void st_xs(int j, double v) { c[ROWD(C64_XS + j)] = v; eb[ROWF(ROW_XS + j)] = (float)v; }
+  __device__ __forceinline__ void st_zs(int i, double v) { c[ROWD(C64_ZS + i)] = v; eb[ROWF(ROW_ZS + i)] = (float)v; }
+  __device__ __forceinline__ void st_ys(int i, double v) { c[ROWD(C64_YS + i)] = v; eb[ROWF(ROW_YS + i)] = (float)v; }
+  __device__ __forceinline__ void st_D(int j, double v) { c[ROWD(C64_D + j)] = v; eb[ROWF(ROW_D + j)] = (float)v; }
+  __device__ __forceinline__ void st_E(int i, double v) { c[ROWD(C64_E + i)] = v; eb[ROWF(ROW_E + i)] = (float)v; }
   __device__ __forceinline__ void st_solx(int j, double v) { eb[ROWF(ROW_SOLX + j)] = (float)v; }
   __device__ __forceinline__ void st_soly(int i, double v) { eb[ROWF(ROW_SOLY + i)] = (float)v; }
 };
@@ -100,7 +102,7 @@ struct SolverF64 {
   static __device__ __forceinline__ uint32_t acquire(uint32_t*) { return 0u; }
   template <int TPB>
   static __device__ __forceinline__ void release(const uint32_t*) {}
-  __device__ __forceinline__ void init(uint32_t, const DevState& s, int e) { st.init(s.c64, (size_t)s.B, e); }
+  __device__ __forceinline__ void init(uint32_t, const DevState& s, int e) { st.init(s.c64, e); }
   __device__ __forceinline__ void qpdata(const Params& par, const DevState& s, int e, const float p[3], const float R[9],
                                          const float dq[6], const float pd[3], const float dpd[3], const float sd[3], float aT0) {
     double p_[3], R_[9], dq_[6], pd_[3], dpd_[3], sd_[3];
@@ -111,7 +113,7 @@ struct SolverF64 {
 #pragma unroll
     for (int i = 0; i < 6; ++i) dq_[i] = dq[i];
     umpc64::UmpcQP qp;
-    umpc64::umpc_build(par, qp, p_, R_, dq_, pd_, dpd_, sd_, aT0 >= 0.0f ? (double)aT0 : s.c64[(size_t)C64_T0 * s.B + e]);
+    umpc64::umpc_build(par, qp, p_, R_, dq_, pd_, dpd_, sd_, aT0 >= 0.0f ? (double)aT0 : s.c64[tile_off64(e) + ROWD(C64_T0)]);
     double out[216];
     umpc64::umpc_qpdata(par, qp, out);
     for (int k = 0; k < 216; ++k) s.qpdata[(size_t)k * s.B + e] = (float)out[k];
@@ -127,7 +129,7 @@ struct SolverF64 {
 #pragma unroll
     for (int i = 0; i < 6; ++i) dq_[i] = dq[i];
     GlobIO64 io(s, e);
-    double T0 = s.c64[(size_t)C64_T0 * s.B + e];
+    double T0 = io.c[ROWD(C64_T0)];
     umpc64::UmpcInfo info;
     if (s.wts) {  // per-environment weights (warp-uniform branch)
       Params pe = par;
@@ -135,7 +137,7 @@ struct SolverF64 {
       umpc64::umpc_update<true>(pe, st, io, uq_, acc_, p_, R_, dq_, pd_, dpd_, sd_, (double)aT0, T0, info);
     } else
     umpc64::umpc_update<true>(par, st, io, uq_, acc_, p_, R_, dq_, pd_, dpd_, sd_, (double)aT0, T0, info);
-    s.c64[(size_t)C64_T0 * s.B + e] = T0;
+    io.c[ROWD(C64_T0)] = T0;
     io.eb[ROWF(ROW_T0)] = (float)T0;
     store_info(io.eb, info.iter, info.status, (float)info.pri_res, (float)info.dua_res);
 #pragma unroll
@@ -152,7 +154,7 @@ struct UmpcConv {
   umpc64::UmpcParams mpc;
   double* slab = nullptr;
   int Bp = 0;
-  int tpb = 128;
+  int tpb = 64;  // measured: 64 slightly ahead of 128 (UMPC_CONV_TPB to override)
 };
 
 int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState* s) {
@@ -187,15 +189,21 @@ int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState
   return 0;
 }
 
+__global__ void fill_rows64_kernel(double* __restrict__ slab, int nslots, int row0, int k, double v) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= nslots) return;
+  double* cb = slab + tile_off64(e);
+  for (int i = 0; i < k; ++i) cb[ROWD(row0 + i)] = v;
+}
+
 int umpc_conv_reset(UmpcConv* c, const DevState* s, cudaStream_t stream) {
   const size_t P = c->Bp;
   cudaError_t e = cudaMemsetAsync(c->slab, 0, (size_t)C64_ROWS * P * sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
-  std::vector<double> v((size_t)UMPC_NX * P, 1.0);
-  if ((e = cudaMemcpyAsync(c->slab + (size_t)C64_D * P, v.data(), (size_t)UMPC_NX * P * 8, cudaMemcpyHostToDevice, stream))) return (int)e;
-  if ((e = cudaMemcpyAsync(c->slab + (size_t)C64_E * P, v.data(), (size_t)UMPC_NC * P * 8, cudaMemcpyHostToDevice, stream))) return (int)e;
-  std::vector<double> r(P, c->mpc.rho);
-  if ((e = cudaMemcpyAsync(c->slab + (size_t)C64_RHO * P, r.data(), P * 8, cudaMemcpyHostToDevice, stream))) return (int)e;
+  const int grid = (c->Bp + 255) / 256;
+  fill_rows64_kernel<<<grid, 256, 0, stream>>>(c->slab, c->Bp, C64_D, UMPC_NX + UMPC_NC, 1.0);  // D and E are adjacent
+  fill_rows64_kernel<<<grid, 256, 0, stream>>>(c->slab, c->Bp, C64_RHO, 1, c->mpc.rho);
+  if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
   (void)s;
   return (int)cudaStreamSynchronize(stream);
 }
