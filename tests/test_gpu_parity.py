@@ -135,3 +135,37 @@ def test_dropin_single_controller_matches_golden(cuda_required, gold):
             x, y = up.solution()
             _close_rel(x, gold["x"][e, c], TOL_X_REL, "x")
             assert up.info()["iter"] == 50
+
+
+def test_host_buffer_calls_pinned_graph_path_equals_pageable_path(cuda_required):
+    """umpcBatchUpdate / umpcBatchEnvStep with PINNED host buffers replay a captured CUDA graph of the chunk pipeline;
+    with pageable numpy buffers they issue the copies directly.  Same kernels, same results -- bit for bit -- over
+    several calls (the graph is replayed), after a change of buffers (re-capture), and for a ragged batch size."""
+    import torch
+    from robobee3d_b200.batch import BatchUMPC
+    for B in (20000, 4097):
+        p, R, dq = util.config2_states(B, seed=5)
+        Rc = np.ascontiguousarray(R.transpose(0, 2, 1).reshape(B, 9), np.float32)
+        f = lambda a: np.ascontiguousarray(a, np.float32)
+        z3, e3 = f(np.zeros((B, 3))), f(np.tile([0, 0, 1.0], (B, 1)))
+        pin = lambda a: torch.from_numpy(np.array(a, np.float32, copy=True)).pin_memory()
+        bg, bd = BatchUMPC(B), BatchUMPC(B)
+        # closed loop through the env-step call: state buffers are overwritten in place
+        sp, sR, sdq = pin(p), pin(Rc), pin(dq)
+        uq, acc = pin(np.zeros((B, 3))), pin(np.zeros((B, 6)))
+        hpd, hdp, hsd = pin(z3), pin(z3), pin(e3)
+        np_p, np_R, np_dq = f(p).copy(), Rc.copy(), f(dq).copy()
+        np_uq, np_acc = np.zeros((B, 3), np.float32), np.zeros((B, 6), np.float32)
+        for step in range(4):
+            bg.env_step_raw(uq, acc, sp, sR, sdq, hpd, hdp, hsd)
+            bd.env_step_raw(np_uq, np_acc, np_p, np_R, np_dq, z3, z3, e3)
+            assert np.array_equal(uq.numpy(), np_uq) and np.array_equal(acc.numpy(), np_acc), (B, step)
+            assert np.array_equal(sp.numpy(), np_p) and np.array_equal(sR.numpy(), np_R) and np.array_equal(sdq.numpy(), np_dq)
+        # different buffers -> the graph is captured again; update call (no plant step), with and without actualT0
+        uq2, acc2 = pin(np.zeros((B, 3))), pin(np.zeros((B, 6)))
+        aT0 = np.full(B, 9.81e-3, np.float32)
+        for a_pin, a_np in ((pin(aT0), aT0), (None, None)):
+            bg.update_raw(sp, sR, sdq, hpd, hdp, hsd, a_pin, uq2, acc2)
+            bd.update_raw(np_p, np_R, np_dq, z3, z3, e3, a_np, np_uq, np_acc)
+            assert np.array_equal(uq2.numpy(), np_uq) and np.array_equal(acc2.numpy(), np_acc)
+        bg.close(); bd.close()
