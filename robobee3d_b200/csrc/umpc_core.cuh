@@ -672,30 +672,41 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     if (commit) {
       info.iter = iter_done; info.pri_res = pri; info.dua_res = dua; info.status = status;
       const bool bad = status == UMPC_ST_NON_CVX;
-      const ureal nanv = umpc_nan();
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const ureal sx = bad ? nanv : xf[j];
-        io.st_solx(j, sx);
-        io.st_xs(j, bad ? 0.0f : xf[j] * UMPC_RCP(Dl[j]));
+        io.st_solx(j, xf[j]);
+        io.st_xs(j, xf[j] * UMPC_RCP(Dl[j]));
       }
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) {
         const ureal e = El[i];
-        io.st_soly(i, bad ? nanv : ys[i] * cinv);
-        io.st_zs(i, bad ? 0.0f : zs[i] * e);
-        io.st_ys(i, bad ? 0.0f : ys[i] * UMPC_RCP(e));
+        io.st_soly(i, ys[i] * cinv);
+        io.st_zs(i, zs[i] * e);
+        io.st_ys(i, ys[i] * UMPC_RCP(e));
       }
       if constexpr (CONV) io.st_rho(rho);
       // ---- extraction (uprightmpc2.c:252-269) ----------------------------------------------
-      const ureal nb = bad ? nanv : 0.0f;
-      T0 += xf[36] + nb;
-      uquad[0] = T0; uquad[1] = xf[37] + nb; uquad[2] = xf[38] + nb;
+      T0 += xf[36];
+      uquad[0] = T0; uquad[1] = xf[37]; uquad[2] = xf[38];
       const ureal t0 = R0b[0] * xf[21] + R0b[1] * xf[22] + R0b[2] * xf[23];
       const ureal t1 = R0b[3] * xf[21] + R0b[4] * xf[22] + R0b[5] * xf[23];
       const ureal dq1[6] = {xf[18], xf[19], xf[20], -t1, t0, 0.0f};
 #pragma unroll
-      for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt + nb;
+      for (int i = 0; i < 6; ++i) accdes[i] = (dq1[i] - dq0b[i]) / dt;
+      if (bad) {
+        // residuals beyond OSQP_INFTY: solution NaN, iterates cold-started (auxil.c:538-561).  A branch of its own, after
+        // the regular stores, so that the normal path carries no per-element selects.
+        const ureal nanv = umpc_nan();
+#pragma unroll
+        for (int j = 0; j < UMPC_NX; ++j) { io.st_solx(j, nanv); io.st_xs(j, 0.0f); }
+#pragma unroll
+        for (int i = 0; i < UMPC_NC; ++i) { io.st_soly(i, nanv); io.st_zs(i, 0.0f); io.st_ys(i, 0.0f); }
+        T0 = nanv;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) uquad[i] = nanv;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) accdes[i] = nanv;
+      }
       done = true;
     }
     if constexpr (CONV) again = !st.all(done);
