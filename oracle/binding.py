@@ -328,3 +328,116 @@ def cpu_env_steps(ics18, nsteps, procs):
     wall = time.perf_counter() - t0
     done = sum(r[0] for r in res)
     return done, max(r[1] for r in res), wall, kind
+
+
+# ---- planar dir-tran MPC (config 5): oracle/dirtran_oracle.c, oracle/_ref/libref_planar_f32.so -------------------
+def dt_settings(eps=1e-5, rho=0.1, sigma=1e-6, alpha=1.6, max_iter=4000, check=25, adapt=25, tol=5.0):
+    return np.array([eps, eps, rho, sigma, alpha, max_iter, check, adapt, tol], dtype=np.float64)
+
+
+def _dt_lib(flavour):
+    L = _private_copy(os.path.join(HERE, "liboracle_dt_%s.so" % flavour))
+    L.dto_create.restype = C.c_void_p
+    L.dto_create.argtypes = [C.c_int, C.c_double, DP, DP, DP]
+    L.dto_destroy.argtypes = [C.c_void_p]
+    L.dto_set_ctrl.argtypes = [C.c_void_p, DP]
+    L.dto_update.argtypes = [C.c_void_p, DP, DP, DP]
+    L.dto_get.argtypes = [C.c_void_p, DP, DP, DP]
+    L.dto_qpdata.argtypes = [C.c_void_p, DP, DP, DP, DP, DP]
+    L.dto_plant.argtypes = [C.c_void_p, DP, DP, C.c_double, C.c_int]
+    L.dto_rollout.argtypes = [C.c_void_p, DP, DP, C.c_int, C.c_double, C.c_int, DP, DP, DP]
+    L.dto_raw_solve.argtypes = [C.c_int, C.c_int, DP, DP, DP, DP, DP, DP, DP, DP, DP]
+    return L
+
+
+class OracleDirTran:
+    """CPU restatement of LTVMPC(PlanarThrustStrokeDev(rescale=True), N, wx, wu, scaling=0, ...) + the plant."""
+    HOVER_WX = np.array([100, 100, 1, 10, 10, 0.1]) / 0.03   # mpc_thrust_strokedev.py:30,118
+    HOVER_WU = np.array([0.01, 0.01])
+
+    def __init__(self, N=5, dt=0.03, wx=None, wu=None, flavour="f64", **st):
+        self.L = _dt_lib(flavour)
+        self.N = N
+        self.n = (N + 1) * 6 + N * 2
+        self.m = self.n + (N + 1) * 6
+        wx = _d(self.HOVER_WX if wx is None else wx); wu = _d(self.HOVER_WU if wu is None else wu)
+        self.st = dt_settings(**st)
+        self.h = self.L.dto_create(N, dt, _p(wx), _p(wu), _p(self.st))
+        assert self.h, "N too large for the oracle's caps"
+
+    def __del__(self):
+        try:
+            self.L.dto_destroy(self.h)
+        except Exception:
+            pass
+
+    def set_ctrl(self, c):
+        self.L.dto_set_ctrl(self.h, _p(_d(c)))
+
+    def update(self, x0, xr):
+        u = np.zeros(2)
+        st = self.L.dto_update(self.h, _p(_d(x0)), _p(_d(xr)), _p(u))
+        return u, st
+
+    def solution(self):
+        x = np.zeros(self.n); y = np.zeros(self.m); info = np.zeros(6)
+        self.L.dto_get(self.h, _p(x), _p(y), _p(info))
+        return x, y, info
+
+    def qpdata(self):
+        Pd = np.zeros(self.n); A = np.zeros((self.m, self.n)); q = np.zeros(self.n); l = np.zeros(self.m); u = np.zeros(self.m)
+        self.L.dto_qpdata(self.h, _p(Pd), _p(A), _p(q), _p(l), _p(u))
+        return Pd, A, q, l, u
+
+    def plant(self, x, u, sim_dt=0.0005, nsub=60):
+        x = _d(x).copy()
+        self.L.dto_plant(self.h, _p(x), _p(_d(u)), sim_dt, nsub)
+        return x
+
+    def rollout(self, x, xr, nsteps, sim_dt=0.0005, nsub=60):
+        x = _d(x).copy()
+        X = np.zeros((nsteps, 6)); U = np.zeros((nsteps, 2)); it = np.zeros(nsteps)
+        bad = self.L.dto_rollout(self.h, _p(x), _p(_d(xr)), nsteps, sim_dt, nsub, _p(X), _p(U), _p(it))
+        return X, U, it, bad
+
+
+def dt_raw_solve(P, A, q, l, u, st, flavour="f64"):
+    L = _dt_lib(flavour)
+    m, n = A.shape
+    x = np.zeros(n); y = np.zeros(m); info = np.zeros(6)
+    L.dto_raw_solve(n, m, _p(_d(P)), _p(_d(A)), _p(_d(q)), _p(_d(l)), _p(_d(u)), _p(_d(st)), _p(x), _p(y), _p(info))
+    return x, y, info
+
+
+class RefPlanarQP:
+    """The reference's generated planar dir-tran instance (planar/code), compiled in place."""
+
+    def __init__(self):
+        self.L = _private_copy(os.path.join(HERE, "_ref", "libref_planar_f32.so"))
+        nm = (C.c_int * 2)()
+        self.L.rp_dims(nm)
+        self.n, self.m = nm[0], nm[1]
+
+    def data(self):
+        n, m = self.n, self.m
+        P = np.zeros((n, n)); A = np.zeros((m, n)); q = np.zeros(n); l = np.zeros(m); u = np.zeros(m); rv = np.zeros(m); st = np.zeros(10)
+        self.L.rp_data(_p(P), _p(A), _p(q), _p(l), _p(u), _p(rv), _p(st))
+        return P, A, q, l, u, rv, st
+
+    def cold_start(self):
+        self.L.rp_cold_start()
+
+    def update(self, q, l, u):
+        return self.L.rp_update(_p(_d(q)), _p(_d(l)), _p(_d(u)))
+
+    def set_max_iter(self, it):
+        return self.L.rp_update_max_iter(int(it))
+
+    def solve(self):
+        x = np.zeros(self.n); y = np.zeros(self.m); info = np.zeros(4)
+        self.L.rp_solve(_p(x), _p(y), _p(info))
+        return x, y, info
+
+
+def have_ref_planar():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_planar_f32.so"))

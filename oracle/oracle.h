@@ -52,8 +52,10 @@ typedef double real;
 #define ST_UNSOLVED (-10)
 
 /* ---- generic OSQP 0.6.0-embedded restatement on dense storage ------------ */
+#ifndef OQ_NMAX /* the dir-tran oracle (dirtran_oracle.c) compiles the same code with larger caps */
 #define OQ_NMAX UM_NX
 #define OQ_MMAX UM_NC
+#endif
 #define OQ_KMAX (OQ_NMAX + OQ_MMAX)
 
 typedef struct {

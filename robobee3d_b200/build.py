@@ -6,12 +6,13 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "umpc_kernels.cu")
 SRC_CONV = os.path.join(HERE, "csrc", "umpc_conv.cu")  # converged mode: the same device code in double
+SRC_DT = os.path.join(HERE, "csrc", "dirtran.cu")      # planar dir-tran MPC (config 5)
 OUT = os.path.join(HERE, "libumpc_b200.so")
-DEPS = [SRC, SRC_CONV] + [os.path.join(HERE, "csrc", f) for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh",
-                                                                   "umpc_dev.cuh", "umpc_conv.h")] + [
-    os.path.join(HERE, "..", "include", "umpc_b200.h")]
+DEPS = [SRC, SRC_CONV, SRC_DT] + [os.path.join(HERE, "csrc", f) for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh",
+                                                                   "umpc_dev.cuh", "umpc_conv.h", "dirtran_core.cuh")] + [
+    os.path.join(HERE, "..", "include", "umpc_b200.h"), os.path.join(HERE, "..", "include", "dirtran_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
-              "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--threads", "2"]
+              "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--threads", "3"]
 
 
 def stale():
@@ -26,7 +27,7 @@ def build(force=False, verbose=False, defines=(), out=None):
     if out is None and not force and not stale():
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC, SRC_CONV]
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC, SRC_CONV, SRC_DT]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
     if out is None:

@@ -1,0 +1,413 @@
+// robobee3d_b200/csrc/dirtran_core.cuh -- per-environment algorithm of the batched planar dir-tran MPC (see dirtran.cu
+// for the design).  Plain functions on one environment's slab column so that the same source also compiles for the
+// host: tests/hostcheck builds it with g++ and checks it against the oracle on the CPU box (test infrastructure only; the
+// product launches it from dirtran.cu's kernels and has no CPU path).
+#pragma once
+#include <math.h>
+#include <stddef.h>
+#include "../../include/dirtran_b200.h"
+
+#ifdef __CUDACC__
+#define DT_FN __device__ __forceinline__
+#define DT_FN_NOINLINE __device__ __noinline__
+#define DT_HD __host__ __device__
+#define DT_SINCOS(a, s, c) sincos(a, s, c)
+#else
+#define DT_FN inline
+#define DT_FN_NOINLINE inline
+#define DT_HD
+#define DT_SINCOS(a, s, c) (*(s) = sin(a), *(c) = cos(a))
+#endif
+
+namespace dtcore {
+
+
+constexpr int NX = DT_NX, NU = DT_NU, NW = NX + NU;
+// header rows of an environment's slab column
+constexpr int R_Y = 0, R_CTRL = 6, R_RHO = 8, R_INFO = 9 /* iter,status,pri,dua,rho_updates */, R_LIN = 14 /* 12 */,
+              R_XR = 26, R_CNT = 32 /* iters, solves, unsolved */, R_HDR = 40;
+// rows of knot k (stride 128)
+constexpr int K_X = 0, K_ZI = 8, K_YI = 16, K_ZE = 24, K_YE = 30, K_SCR = 36, K_LD = 44, K_LO = 80, K_STRIDE = 128;
+constexpr int LANES = 32;
+
+constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_EQ_OVER_INEQ = 1e3;  // osqp constants.h
+constexpr int ST_SOLVED = 1, ST_SOLVED_INACCURATE = 2, ST_MAX_ITER = -2, ST_UNSOLVED = -10;
+
+struct DevPar {
+  int N, max_iter, check_termination, adaptive_rho_interval, nsub;
+  double dt, sim_dt, sigma, alpha, eps_abs, eps_rel, rho0, adaptive_rho_tol, g, ibmb_inv;
+  double wx[NX], wu[NU], lo[NW], hi[NW];
+  unsigned loose;  // bit j: inequality row j of a knot has no finite bound (rho_vec = RHO_MIN)
+};
+
+DT_HD constexpr int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+
+struct Env {
+  double* base;
+  DT_FN double& h(int r) const { return base[r * LANES]; }
+  DT_FN double* knot(int k) const { return base + (size_t)(R_HDR + k * K_STRIDE) * LANES; }
+};
+
+// the linearisation, FlappingModels.py:51-102: Ad = I + dt dfdy, Bd = dt dfdu
+struct Lin {
+  double dt, a32, a42, b30, b40, b50, b51;
+  // out = Ad x + Bd u
+  DT_FN void mul(const double (&w)[NW], double (&o)[NX]) const {
+    o[0] = w[0] + dt * w[3]; o[1] = w[1] + dt * w[4]; o[2] = w[2] + dt * w[5];
+    o[3] = w[3] + a32 * w[2] + b30 * w[6];
+    o[4] = w[4] + a42 * w[2] + b40 * w[6];
+    o[5] = w[5] + b50 * w[6] + b51 * w[7];
+  }
+  // o += [Ad Bd]' t
+  DT_FN void mulT_add(const double (&t)[NX], double (&o)[NW]) const {
+    o[0] += t[0]; o[1] += t[1]; o[2] += t[2] + a32 * t[3] + a42 * t[4];
+    o[3] += dt * t[0] + t[3]; o[4] += dt * t[1] + t[4]; o[5] += dt * t[2] + t[5];
+    o[6] += b30 * t[3] + b40 * t[4] + b50 * t[5];
+    o[7] += b51 * t[5];
+  }
+  // dense [Ad Bd], row-major 6x8 (factorisation only)
+  DT_FN void dense(double (&M)[NX][NW]) const {
+#pragma unroll
+    for (int i = 0; i < NX; ++i)
+#pragma unroll
+      for (int j = 0; j < NW; ++j) M[i][j] = (i == j) ? 1.0 : 0.0;
+    M[0][3] = dt; M[1][4] = dt; M[2][5] = dt;
+    M[3][2] = a32; M[4][2] = a42;
+    M[3][6] = b30; M[4][6] = b40; M[5][6] = b50; M[5][7] = b51;
+  }
+};
+
+DT_FN void dydt(const DevPar& P, const double (&y)[NX], double u0, double u1, double (&f)[NX]) {
+  double s, c;
+  DT_SINCOS(y[2], &s, &c);
+  const double thrust = P.g + u0;
+  f[0] = y[3]; f[1] = y[4]; f[2] = y[5];
+  f[3] = -thrust * s;
+  f[4] = -P.g + thrust * c;
+  f[5] = thrust * u1 * P.ibmb_inv;
+}
+
+// linearise at (y, u): fills lin and fd; stores both in the header rows
+DT_FN void linearise(const DevPar& P, const Env& e, const double (&y)[NX], double u0, double u1, Lin& L,
+                                          double (&fd)[NX]) {
+  double s, c;
+  DT_SINCOS(y[2], &s, &c);
+  const double thrust = P.g + u0;
+  const double d32 = -thrust * c, d42 = -thrust * s;               // dfdy[3][2], dfdy[4][2]
+  const double e30 = -s, e40 = c, e50 = u1 * P.ibmb_inv, e51 = thrust * P.ibmb_inv;  // dfdu
+  double f[NX];
+  f[0] = y[3]; f[1] = y[4]; f[2] = y[5];
+  f[3] = -thrust * s; f[4] = -P.g + thrust * c; f[5] = thrust * u1 * P.ibmb_inv;
+  // fd = dt (f - dfdy y - dfdu u), same order of subtraction as the row loops of the reference's matrix products
+  fd[0] = P.dt * (f[0] - y[3]); fd[1] = P.dt * (f[1] - y[4]); fd[2] = P.dt * (f[2] - y[5]);
+  fd[3] = P.dt * (f[3] - d32 * y[2] - e30 * u0);
+  fd[4] = P.dt * (f[4] - d42 * y[2] - e40 * u0);
+  fd[5] = P.dt * (f[5] - (e50 * u0 + e51 * u1));
+  L.dt = P.dt; L.a32 = P.dt * d32; L.a42 = P.dt * d42;
+  L.b30 = P.dt * e30; L.b40 = P.dt * e40; L.b50 = P.dt * e50; L.b51 = P.dt * e51;
+  e.h(R_LIN + 0) = L.a32; e.h(R_LIN + 1) = L.a42; e.h(R_LIN + 2) = L.b30; e.h(R_LIN + 3) = L.b40;
+  e.h(R_LIN + 4) = L.b50; e.h(R_LIN + 5) = L.b51;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) e.h(R_LIN + 6 + i) = fd[i];
+}
+
+DT_FN double rho_of_row(const DevPar& P, int j, double rho) { return ((P.loose >> j) & 1u) ? RHO_MIN : rho; }
+
+// Block Cholesky of H = P + sigma I + A' diag(rho_vec) A in knot order; writes LD (lower, packed, reciprocal diagonal)
+// and LO (the 6x8 coupling of knot k+1's state rows to knot k) of every knot.
+DT_FN_NOINLINE void factor(const DevPar& P, const Env& e, const Lin& L, double rho) {
+  const double rho_e = RHO_EQ_OVER_INEQ * rho;
+  double M[NX][NW];
+  L.dense(M);
+  double Hd[NW * (NW + 1) / 2];  // the diagonal block of a knot k < N
+#pragma unroll
+  for (int i = 0; i < NW; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      double g = 0.0;
+#pragma unroll
+      for (int r = 0; r < NX; ++r) g += M[r][i] * M[r][j];
+      if (i == j && i < NX) g += 1.0;  // the -I of the knot's own dynamics (or initial-state) row
+      g *= rho_e;
+      if (i == j) g += (i < NX ? P.wx[i] : P.wu[i - NX]) + P.sigma + rho_of_row(P, i, rho);
+      Hd[tri(i, j)] = g;
+    }
+  double S[NW * (NW + 1) / 2];
+#pragma unroll
+  for (int t = 0; t < NW * (NW + 1) / 2; ++t) S[t] = Hd[t];
+  for (int k = 0; k <= P.N; ++k) {
+    double* kb = e.knot(k);
+    if (k == P.N) {  // last knot: no input, no outgoing dynamics row
+#pragma unroll
+      for (int i = 0; i < NW; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+          if (i >= NX) S[tri(i, j)] = (i == j) ? 1.0 : 0.0;
+          else if (i == j) S[tri(i, j)] += (P.wx[i] + P.sigma + rho_of_row(P, i, rho) + rho_e) - Hd[tri(i, j)];
+          else S[tri(i, j)] -= Hd[tri(i, j)];
+        }
+    }
+    // in-place Cholesky, diagonal kept as its reciprocal
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      double d = S[tri(j, j)];
+#pragma unroll
+      for (int c = 0; c < j; ++c) d -= S[tri(j, c)] * S[tri(j, c)];
+      const double r = 1.0 / sqrt(d);
+      S[tri(j, j)] = r;
+#pragma unroll
+      for (int i = j + 1; i < NW; ++i) {
+        double v = S[tri(i, j)];
+#pragma unroll
+        for (int c = 0; c < j; ++c) v -= S[tri(i, c)] * S[tri(j, c)];
+        S[tri(i, j)] = v * r;
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < NW * (NW + 1) / 2; ++t) kb[(K_LD + t) * LANES] = S[t];
+    if (k == P.N) break;
+    // LO = H_{k+1,k} L^-T with H_{k+1,k} = -rho_e [Ad Bd]; next S = Hd - LO LO' on the state rows
+    double LO[NX][NW];
+#pragma unroll
+    for (int r = 0; r < NX; ++r) {
+#pragma unroll
+      for (int j = 0; j < NW; ++j) {
+        double v = -rho_e * M[r][j];
+#pragma unroll
+        for (int c = 0; c < j; ++c) v -= S[tri(j, c)] * LO[r][c];
+        LO[r][j] = v * S[tri(j, j)];
+      }
+#pragma unroll
+      for (int j = 0; j < NW; ++j) kb[(K_LO + r * NW + j) * LANES] = LO[r][j];
+    }
+#pragma unroll
+    for (int i = 0; i < NW; ++i)
+#pragma unroll
+      for (int j = 0; j <= i; ++j) {
+        double v = Hd[tri(i, j)];
+        if (i < NX) {
+#pragma unroll
+          for (int c = 0; c < NW; ++c) v -= LO[i][c] * LO[j][c];
+        }
+        S[tri(i, j)] = v;
+      }
+  }
+}
+
+// One ADMM iteration (osqp auxil.c update_xz_tilde / update_x / update_z / update_y in the reduced form).
+DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const double (&fd)[NX],
+                                               const double (&y0)[NX], const double (&q)[NX], double rho) {
+  const double rho_e = RHO_EQ_OVER_INEQ * rho, rho_e_inv = 1.0 / rho_e, alpha = P.alpha, oma = 1.0 - P.alpha;
+  double rin[NW], rin_inv[NW];
+#pragma unroll
+  for (int j = 0; j < NW; ++j) { rin[j] = rho_of_row(P, j, rho); rin_inv[j] = 1.0 / rin[j]; }
+  const int N = P.N;
+  // ---- forward sweep: rhs = sigma x - q + A'(rho z - y), forward substitution
+  double te[NX], c_prev[NW];
+  {
+    const double* kb = e.knot(0);
+#pragma unroll
+    for (int i = 0; i < NX; ++i) te[i] = rho_e * kb[(K_ZE + i) * LANES] - kb[(K_YE + i) * LANES];
+  }
+  for (int k = 0; k <= N; ++k) {
+    double* kb = e.knot(k);
+    const bool last = (k == N);
+    double b[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j)
+      b[j] = P.sigma * kb[(K_X + j) * LANES] + (rin[j] * kb[(K_ZI + j) * LANES] - kb[(K_YI + j) * LANES]);
+#pragma unroll
+    for (int i = 0; i < NX; ++i) b[i] -= q[i] + te[i];
+    if (!last) {
+      const double* kn = e.knot(k + 1);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) te[i] = rho_e * kn[(K_ZE + i) * LANES] - kn[(K_YE + i) * LANES];
+      L.mulT_add(te, b);
+    } else {
+      b[NX] = 0.0; b[NX + 1] = 0.0;
+    }
+    if (k > 0) {
+      const double* kp = e.knot(k - 1);
+#pragma unroll
+      for (int r = 0; r < NX; ++r) {
+        double v = b[r];
+#pragma unroll
+        for (int c = 0; c < NW; ++c) v -= kp[(K_LO + r * NW + c) * LANES] * c_prev[c];
+        b[r] = v;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      double v = b[j];
+#pragma unroll
+      for (int c = 0; c < j; ++c) v -= kb[(K_LD + tri(j, c)) * LANES] * c_prev[c];
+      c_prev[j] = v * kb[(K_LD + tri(j, j)) * LANES];
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) kb[(K_SCR + j) * LANES] = c_prev[j];
+  }
+  // ---- backward sweep: back substitution, z~ = A x~, x/z/y updates
+  double xn[NX];  // x~ of knot k+1 (state part)
+#pragma unroll
+  for (int i = 0; i < NX; ++i) xn[i] = 0.0;
+  for (int k = N; k >= 0; --k) {
+    double* kb = e.knot(k);
+    const bool last = (k == N);
+    double xt[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) xt[j] = kb[(K_SCR + j) * LANES];
+    if (!last) {
+#pragma unroll
+      for (int r = 0; r < NX; ++r)
+#pragma unroll
+        for (int c = 0; c < NW; ++c) xt[c] -= kb[(K_LO + r * NW + c) * LANES] * xn[r];
+    }
+#pragma unroll
+    for (int j = NW - 1; j >= 0; --j) {
+      double v = xt[j];
+#pragma unroll
+      for (int c = j + 1; c < NW; ++c) v -= kb[(K_LD + tri(c, j)) * LANES] * xt[c];
+      xt[j] = v * kb[(K_LD + tri(j, j)) * LANES];
+    }
+    if (!last) {
+      // dynamics rows of knot k+1: z~ = Ad x~_k + Bd u~_k - x~_{k+1}; l = u = -fd
+      double* kn = e.knot(k + 1);
+      double zt[NX];
+      L.mul(xt, zt);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) {
+        const double zp = kn[(K_ZE + i) * LANES], yp = kn[(K_YE + i) * LANES];
+        const double v = alpha * (zt[i] - xn[i]) + oma * zp;
+        const double zn = fmin(fmax(v + rho_e_inv * yp, -fd[i]), -fd[i]);
+        kn[(K_ZE + i) * LANES] = zn;
+        kn[(K_YE + i) * LANES] = yp + rho_e * (v - zn);
+      }
+    }
+    // bound rows of this knot (z~ = x~) and the x update
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      const double xp = kb[(K_X + j) * LANES], zp = kb[(K_ZI + j) * LANES], yp = kb[(K_YI + j) * LANES];
+      const double v = alpha * xt[j] + oma * zp;
+      double zn = fmin(fmax(v + rin_inv[j] * yp, P.lo[j]), P.hi[j]);
+      double xv = alpha * xt[j] + oma * xp;
+      double yn = yp + rin[j] * (v - zn);
+      if (last && j >= NX) { zn = 0.0; xv = 0.0; yn = 0.0; }
+      kb[(K_X + j) * LANES] = xv; kb[(K_ZI + j) * LANES] = zn; kb[(K_YI + j) * LANES] = yn;
+    }
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xn[i] = xt[i];
+  }
+  {  // initial-state rows: z~ = -x~_0, l = u = -y0
+    double* kb = e.knot(0);
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      const double zp = kb[(K_ZE + i) * LANES], yp = kb[(K_YE + i) * LANES];
+      const double v = alpha * (-xn[i]) + oma * zp;
+      const double zn = fmin(fmax(v + rho_e_inv * yp, -y0[i]), -y0[i]);
+      kb[(K_ZE + i) * LANES] = zn;
+      kb[(K_YE + i) * LANES] = yp + rho_e * (v - zn);
+    }
+  }
+}
+
+struct Resid { double pri, dua, nprim, ndual; };
+
+// osqp auxil.c compute_pri_res / compute_dua_res and the norms of compute_pri_tol / compute_dua_tol (scaling off)
+DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double (&q)[NX]) {
+  const int N = P.N;
+  double pri = 0.0, nz = 0.0, nAx = 0.0, dua = 0.0, nPx = 0.0, nAty = 0.0, nq = 0.0;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) nq = fmax(nq, fabs(q[i]));
+  double xn[NX], yen[NX], zen[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) { xn[i] = 0.0; yen[i] = 0.0; zen[i] = 0.0; }
+  for (int k = N; k >= 0; --k) {
+    const double* kb = e.knot(k);
+    const bool last = (k == N);
+    double x[NW], aty[NW], ye[NX], ze[NX];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      x[j] = kb[(K_X + j) * LANES];
+      const double zi = kb[(K_ZI + j) * LANES];
+      aty[j] = kb[(K_YI + j) * LANES];
+      if (!(last && j >= NX)) { pri = fmax(pri, fabs(x[j] - zi)); nz = fmax(nz, fabs(zi)); nAx = fmax(nAx, fabs(x[j])); }
+    }
+#pragma unroll
+    for (int i = 0; i < NX; ++i) { ye[i] = kb[(K_YE + i) * LANES]; ze[i] = kb[(K_ZE + i) * LANES]; aty[i] -= ye[i]; }
+    if (!last) {
+      double ax[NX];
+      L.mul(x, ax);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) {
+        const double a = ax[i] - xn[i];
+        pri = fmax(pri, fabs(a - zen[i])); nz = fmax(nz, fabs(zen[i])); nAx = fmax(nAx, fabs(a));
+      }
+      L.mulT_add(yen, aty);
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      if (last && j >= NX) continue;
+      const double px = (j < NX ? P.wx[j] : P.wu[j - NX]) * x[j];
+      const double qq = j < NX ? q[j] : 0.0;
+      dua = fmax(dua, fabs(px + qq + aty[j])); nPx = fmax(nPx, fabs(px)); nAty = fmax(nAty, fabs(aty[j]));
+    }
+#pragma unroll
+    for (int i = 0; i < NX; ++i) { xn[i] = x[i]; yen[i] = ye[i]; zen[i] = ze[i]; }
+  }
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {  // initial-state rows: Ax = -x_0
+    pri = fmax(pri, fabs(-xn[i] - zen[i])); nz = fmax(nz, fabs(zen[i])); nAx = fmax(nAx, fabs(xn[i]));
+  }
+  Resid r;
+  r.pri = pri; r.dua = dua; r.nprim = fmax(nz, nAx); r.ndual = fmax(nq, fmax(nAty, nPx));
+  return r;
+}
+
+// one LTVMPC.update for this thread's environment; returns u_0 in (u0, u1) and updates ctrl
+DT_FN void mpc_update(const DevPar& P, const Env& e, const double (&y)[NX], double& u0, double& u1) {
+  Lin L;
+  double fd[NX], q[NX];
+  linearise(P, e, y, u0, u1, L, fd);
+#pragma unroll
+  for (int i = 0; i < NX; ++i) q[i] = -P.wx[i] * e.h(R_XR + i);
+  double rho = e.h(R_RHO);
+  factor(P, e, L, rho);
+  int iter = 0, status = ST_UNSOLVED, rho_updates = 0;
+  bool checked = false;
+  Resid r;
+  r.pri = r.dua = r.nprim = r.ndual = 0.0;
+  for (iter = 1; iter <= P.max_iter; ++iter) {
+    admm_iteration(P, e, L, fd, y, q, rho);
+    checked = P.check_termination && (iter % P.check_termination == 0);
+    const bool adapt = P.adaptive_rho_interval && (iter % P.adaptive_rho_interval == 0);
+    if (checked || adapt) r = residuals(P, e, L, q);
+    if (checked && r.pri < P.eps_abs + P.eps_rel * r.nprim && r.dua < P.eps_abs + P.eps_rel * r.ndual) { status = ST_SOLVED; break; }
+    if (adapt) {  // osqp auxil.c compute_rho_estimate / adapt_rho
+      const double pn = r.pri / (r.nprim + 1e-10), dn = r.dua / (r.ndual + 1e-10);
+      double est = rho * sqrt(pn / (dn + 1e-10));
+      est = fmin(fmax(est, RHO_MIN), RHO_MAX);
+      if (est > rho * P.adaptive_rho_tol || est < rho / P.adaptive_rho_tol) {
+        rho = est;
+        ++rho_updates;
+        factor(P, e, L, rho);
+      }
+    }
+  }
+  if (status == ST_UNSOLVED) {
+    iter = P.max_iter;
+    if (!checked) r = residuals(P, e, L, q);
+    if (r.pri < P.eps_abs + P.eps_rel * r.nprim && r.dua < P.eps_abs + P.eps_rel * r.ndual) status = ST_SOLVED;
+    else if (r.pri < 10 * (P.eps_abs + P.eps_rel * r.nprim) && r.dua < 10 * (P.eps_abs + P.eps_rel * r.ndual)) status = ST_SOLVED_INACCURATE;
+    else status = ST_MAX_ITER;
+  }
+  e.h(R_RHO) = rho;
+  e.h(R_INFO + 0) = (double)iter; e.h(R_INFO + 1) = (double)status; e.h(R_INFO + 2) = r.pri; e.h(R_INFO + 3) = r.dua;
+  e.h(R_INFO + 4) = (double)rho_updates;
+  e.h(R_CNT + 0) += (double)iter; e.h(R_CNT + 1) += 1.0; e.h(R_CNT + 2) += (status == ST_SOLVED) ? 0.0 : 1.0;
+  const double* k0 = e.knot(0);
+  u0 = k0[(K_X + NX) * LANES]; u1 = k0[(K_X + NX + 1) * LANES];  // mpc.py:89
+  e.h(R_CTRL) = u0; e.h(R_CTRL + 1) = u1;
+}
+
+
+}  // namespace dtcore

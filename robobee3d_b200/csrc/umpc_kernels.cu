@@ -326,6 +326,7 @@ static int set_err(const char* what, cudaError_t e) {
   } while (0)
 
 extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
+void umpc_internal_set_error(const char* msg) { g_err = msg; }  // for the other translation units (dirtran.cu)
 
 struct UmpcBatch {
   int B = 0, Bp = 0, device = 0, tpb = 128;  // B: caller's env count, Bp: padded to whole warps (device stride)
