@@ -79,7 +79,8 @@ def test_hover_run_matches_golden():
     b.rollout(37)
     y, c = b.state()
     assert np.abs(y[0] - G["hover_X"][-1]).max() <= 2e-4
-    assert np.abs(c[0] - G["hover_U"][-1]).max() <= 2e-4
+    # the input at rest: two solves converged to eps = 1e-5 (relative to |u0| ~ 10 bounds) differ by O(TOL_U)
+    assert (np.abs(c[0] - G["hover_U"][-1]) <= TOL_U).all()
     b.close()
 
 
