@@ -68,15 +68,7 @@ __global__ void __launch_bounds__(128) dt_rollout_kernel(const __grid_constant__
 #pragma unroll
   for (int i = 0; i < NX; ++i) y[i] = e.h(R_Y + i);
   double u0 = e.h(R_CTRL), u1 = e.h(R_CTRL + 1);
-  for (int s = 0; s < nsteps; ++s) {
-    mpc_update(P, e, y, u0, u1);
-    for (int t = 0; t < P.nsub; ++t) {
-      double f[NX];
-      dydt(P, y, u0, u1, f);
-#pragma unroll
-      for (int i = 0; i < NX; ++i) y[i] += f[i] * P.sim_dt;
-    }
-  }
+  mpc_run<true>(P, e, y, u0, u1, nsteps);
 #pragma unroll
   for (int i = 0; i < NX; ++i) e.h(R_Y + i) = y[i];
 }

@@ -25,9 +25,9 @@ namespace dtcore {
 constexpr int NX = DT_NX, NU = DT_NU, NW = NX + NU;
 // header rows of an environment's slab column
 constexpr int R_Y = 0, R_CTRL = 6, R_RHO = 8, R_INFO = 9 /* iter,status,pri,dua,rho_updates */, R_LIN = 14 /* 12 */,
-              R_XR = 26, R_CNT = 32 /* iters, solves, unsolved */, R_HDR = 40;
+              R_XR = 26, R_CNT = 32 /* iters, solves, unsolved */, R_STEPS = 35 /* steps left in the running call */, R_HDR = 40;
 // rows of knot k (stride 128)
-constexpr int K_X = 0, K_ZI = 8, K_YI = 16, K_ZE = 24, K_YE = 30, K_SCR = 36, K_LD = 44, K_LO = 80, K_STRIDE = 128;
+constexpr int K_X = 0, K_ZI = 8, K_YI = 16, K_ZE = 24, K_YE = 30, K_SCR = 36, K_LD = 44, K_STRIDE = 80;
 constexpr int LANES = 32;
 
 constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_EQ_OVER_INEQ = 1e3;  // osqp constants.h
@@ -113,8 +113,10 @@ DT_FN void linearise(const DevPar& P, const Env& e, const double (&y)[NX], doubl
 
 DT_FN double rho_of_row(const DevPar& P, int j, double rho) { return ((P.loose >> j) & 1u) ? RHO_MIN : rho; }
 
-// Block Cholesky of H = P + sigma I + A' diag(rho_vec) A in knot order; writes LD (lower, packed, reciprocal diagonal)
-// and LO (the 6x8 coupling of knot k+1's state rows to knot k) of every knot.
+// Block Cholesky of H = P + sigma I + A' diag(rho_vec) A in knot order; writes LD_k = chol(S_k) (lower, packed, reciprocal
+// diagonal) of every knot, S_0 = H_00, S_{k+1} = H_{k+1,k+1} - LO_k LO_k'.  The coupling LO_k = H_{k+1,k} L_k^-T
+// (6x8, H_{k+1,k} = -rho_e [Ad Bd]) lives in registers only: the iteration applies H_{k+1,k} S_k^-1 as a sparse product
+// with [Ad Bd] around two triangular solves with LD_k, which it has loaded anyway (admm_iteration).
 DT_FN_NOINLINE void factor(const DevPar& P, const Env& e, const Lin& L, double rho) {
   const double rho_e = RHO_EQ_OVER_INEQ * rho;
   double M[NX][NW];
@@ -177,8 +179,6 @@ DT_FN_NOINLINE void factor(const DevPar& P, const Env& e, const Lin& L, double r
         for (int c = 0; c < j; ++c) v -= S[tri(j, c)] * LO[r][c];
         LO[r][j] = v * S[tri(j, j)];
       }
-#pragma unroll
-      for (int j = 0; j < NW; ++j) kb[(K_LO + r * NW + j) * LANES] = LO[r][j];
     }
 #pragma unroll
     for (int i = 0; i < NW; ++i)
@@ -194,7 +194,30 @@ DT_FN_NOINLINE void factor(const DevPar& P, const Env& e, const Lin& L, double r
   }
 }
 
+// forward then backward substitution with one knot's packed Cholesky factor: v <- S^-1 v
+DT_FN void chol_solve(const double (&Lk)[NW * (NW + 1) / 2], double (&v)[NW]) {
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    double a = v[j];
+#pragma unroll
+    for (int c = 0; c < j; ++c) a -= Lk[tri(j, c)] * v[c];
+    v[j] = a * Lk[tri(j, j)];
+  }
+#pragma unroll
+  for (int j = NW - 1; j >= 0; --j) {
+    double a = v[j];
+#pragma unroll
+    for (int c = j + 1; c < NW; ++c) a -= Lk[tri(c, j)] * v[c];
+    v[j] = a * Lk[tri(j, j)];
+  }
+}
+
 // One ADMM iteration (osqp auxil.c update_xz_tilde / update_x / update_z / update_y in the reduced form).
+// Block elimination of the tridiagonal H with t_k = S_k^-1 b~_k as the only stored intermediate:
+//   forward   b~_k = b_k + rho_e [Ad Bd] t_{k-1} (state rows),  t_k = S_k^-1 b~_k
+//   backward  x~_k = t_k + rho_e S_k^-1 [Ad Bd]' x~_{k+1}
+// Per knot and iteration: 36 factor words read per sweep, the 36 iterate words read twice and written once, t written
+// and read once (196 doubles).
 DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const double (&fd)[NX],
                                                const double (&y0)[NX], const double (&q)[NX], double rho) {
   const double rho_e = RHO_EQ_OVER_INEQ * rho, rho_e_inv = 1.0 / rho_e, alpha = P.alpha, oma = 1.0 - P.alpha;
@@ -202,8 +225,8 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
 #pragma unroll
   for (int j = 0; j < NW; ++j) { rin[j] = rho_of_row(P, j, rho); rin_inv[j] = 1.0 / rin[j]; }
   const int N = P.N;
-  // ---- forward sweep: rhs = sigma x - q + A'(rho z - y), forward substitution
-  double te[NX], c_prev[NW];
+  // ---- forward sweep: rhs = sigma x - q + A'(rho z - y), block forward elimination
+  double te[NX], t[NW];
   {
     const double* kb = e.knot(0);
 #pragma unroll
@@ -212,6 +235,9 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
   for (int k = 0; k <= N; ++k) {
     double* kb = e.knot(k);
     const bool last = (k == N);
+    double Lk[NW * (NW + 1) / 2];
+#pragma unroll
+    for (int i = 0; i < NW * (NW + 1) / 2; ++i) Lk[i] = kb[(K_LD + i) * LANES];
     double b[NW];
 #pragma unroll
     for (int j = 0; j < NW; ++j)
@@ -227,26 +253,16 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
       b[NX] = 0.0; b[NX + 1] = 0.0;
     }
     if (k > 0) {
-      const double* kp = e.knot(k - 1);
+      double mt[NX];
+      L.mul(t, mt);
 #pragma unroll
-      for (int r = 0; r < NX; ++r) {
-        double v = b[r];
-#pragma unroll
-        for (int c = 0; c < NW; ++c) v -= kp[(K_LO + r * NW + c) * LANES] * c_prev[c];
-        b[r] = v;
-      }
+      for (int r = 0; r < NX; ++r) b[r] += rho_e * mt[r];
     }
+    chol_solve(Lk, b);
 #pragma unroll
-    for (int j = 0; j < NW; ++j) {
-      double v = b[j];
-#pragma unroll
-      for (int c = 0; c < j; ++c) v -= kb[(K_LD + tri(j, c)) * LANES] * c_prev[c];
-      c_prev[j] = v * kb[(K_LD + tri(j, j)) * LANES];
-    }
-#pragma unroll
-    for (int j = 0; j < NW; ++j) kb[(K_SCR + j) * LANES] = c_prev[j];
+    for (int j = 0; j < NW; ++j) { t[j] = b[j]; kb[(K_SCR + j) * LANES] = b[j]; }
   }
-  // ---- backward sweep: back substitution, z~ = A x~, x/z/y updates
+  // ---- backward sweep: block back substitution, z~ = A x~, x/z/y updates
   double xn[NX];  // x~ of knot k+1 (state part)
 #pragma unroll
   for (int i = 0; i < NX; ++i) xn[i] = 0.0;
@@ -257,17 +273,18 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
 #pragma unroll
     for (int j = 0; j < NW; ++j) xt[j] = kb[(K_SCR + j) * LANES];
     if (!last) {
+      double Lk[NW * (NW + 1) / 2];
 #pragma unroll
-      for (int r = 0; r < NX; ++r)
+      for (int i = 0; i < NW * (NW + 1) / 2; ++i) Lk[i] = kb[(K_LD + i) * LANES];
+      double w[NW];
 #pragma unroll
-        for (int c = 0; c < NW; ++c) xt[c] -= kb[(K_LO + r * NW + c) * LANES] * xn[r];
-    }
+      for (int j = 0; j < NW; ++j) w[j] = 0.0;
+      L.mulT_add(xn, w);
 #pragma unroll
-    for (int j = NW - 1; j >= 0; --j) {
-      double v = xt[j];
+      for (int j = 0; j < NW; ++j) w[j] *= rho_e;
+      chol_solve(Lk, w);
 #pragma unroll
-      for (int c = j + 1; c < NW; ++c) v -= kb[(K_LD + tri(c, j)) * LANES] * xt[c];
-      xt[j] = v * kb[(K_LD + tri(j, j)) * LANES];
+      for (int j = 0; j < NW; ++j) xt[j] += w[j];
     }
     if (!last) {
       // dynamics rows of knot k+1: z~ = Ad x~_k + Bd u~_k - x~_{k+1}; l = u = -fd
@@ -363,50 +380,88 @@ DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double 
   return r;
 }
 
-// one LTVMPC.update for this thread's environment; returns u_0 in (u0, u1) and updates ctrl
-DT_FN void mpc_update(const DevPar& P, const Env& e, const double (&y)[NX], double& u0, double& u1) {
+DT_FN bool converged(const DevPar& P, const Resid& r, double f) {
+  return r.pri < f * (P.eps_abs + P.eps_rel * r.nprim) && r.dua < f * (P.eps_abs + P.eps_rel * r.ndual);
+}
+
+// nsteps x (one LTVMPC.update [+ the plant's Euler substeps when PLANT]) for this thread's environment, as ONE loop over
+// ADMM iterations: a lane that finishes a solve starts its next step in the same trip instead of idling until the
+// slowest lane of its warp is done.  Solves end and rho adapts only at trips that are multiples of check_termination /
+// adaptive_rho_interval, so the lanes of a warp keep taking the residual branch together however far apart their step
+// counters drift.  Returns the last u_0 in (u0, u1), the plant state in y.
+template <bool PLANT>
+DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, double& u1, int nsteps_uniform) {
+  if (nsteps_uniform <= 0) return;
+  // The per-lane step budget goes through the environment's header (volatile read-back).  Kept in a plain local
+  // initialised from the kernel parameter, nvcc 12.9 / ptxas put it in a UNIFORM register (UIADD3 UR5, UR5, -1;
+  // BRA.U in the SASS of dt_rollout_kernel) although it is decremented under a lane-dependent condition: the first
+  // lanes to finish a step then decremented it for the whole warp (measured: 37 of 96 solves done).  A loaded value
+  // is per-lane for the compiler; iter and rho_updates restart from a zero derived from it for the same reason.
+  e.h(R_STEPS) = (double)nsteps_uniform;
+  int nsteps = (int)*(const volatile double*)&e.h(R_STEPS);
+  const int lane_zero = nsteps - nsteps_uniform;
   Lin L;
   double fd[NX], q[NX];
-  linearise(P, e, y, u0, u1, L, fd);
 #pragma unroll
   for (int i = 0; i < NX; ++i) q[i] = -P.wx[i] * e.h(R_XR + i);
   double rho = e.h(R_RHO);
+  linearise(P, e, y, u0, u1, L, fd);
   factor(P, e, L, rho);
-  int iter = 0, status = ST_UNSOLVED, rho_updates = 0;
-  bool checked = false;
-  Resid r;
-  r.pri = r.dua = r.nprim = r.ndual = 0.0;
-  for (iter = 1; iter <= P.max_iter; ++iter) {
+  int iter = lane_zero, rho_updates = lane_zero;
+  while (true) {
+    ++iter;
     admm_iteration(P, e, L, fd, y, q, rho);
-    checked = P.check_termination && (iter % P.check_termination == 0);
+    const bool at_max = iter >= P.max_iter;
+    const bool checked = P.check_termination && (iter % P.check_termination == 0);
     const bool adapt = P.adaptive_rho_interval && (iter % P.adaptive_rho_interval == 0);
-    if (checked || adapt) r = residuals(P, e, L, q);
-    if (checked && r.pri < P.eps_abs + P.eps_rel * r.nprim && r.dua < P.eps_abs + P.eps_rel * r.ndual) { status = ST_SOLVED; break; }
-    if (adapt) {  // osqp auxil.c compute_rho_estimate / adapt_rho
+    if (!(checked || adapt || at_max)) continue;
+    const Resid r = residuals(P, e, L, q);
+    // order of osqp.c's loop: termination test, then the rho adaptation, then (out of iterations) the final tests
+    int status = (checked && converged(P, r, 1.0)) ? ST_SOLVED : ST_UNSOLVED;
+    bool refactor = false;
+    if (status == ST_UNSOLVED && adapt) {  // osqp auxil.c compute_rho_estimate / adapt_rho
       const double pn = r.pri / (r.nprim + 1e-10), dn = r.dua / (r.ndual + 1e-10);
       double est = rho * sqrt(pn / (dn + 1e-10));
       est = fmin(fmax(est, RHO_MIN), RHO_MAX);
       if (est > rho * P.adaptive_rho_tol || est < rho / P.adaptive_rho_tol) {
         rho = est;
         ++rho_updates;
-        factor(P, e, L, rho);
+        refactor = true;
       }
     }
-  }
-  if (status == ST_UNSOLVED) {
-    iter = P.max_iter;
-    if (!checked) r = residuals(P, e, L, q);
-    if (r.pri < P.eps_abs + P.eps_rel * r.nprim && r.dua < P.eps_abs + P.eps_rel * r.ndual) status = ST_SOLVED;
-    else if (r.pri < 10 * (P.eps_abs + P.eps_rel * r.nprim) && r.dua < 10 * (P.eps_abs + P.eps_rel * r.ndual)) status = ST_SOLVED_INACCURATE;
-    else status = ST_MAX_ITER;
+    if (status == ST_UNSOLVED && at_max)
+      status = converged(P, r, 1.0) ? ST_SOLVED : (converged(P, r, 10.0) ? ST_SOLVED_INACCURATE : ST_MAX_ITER);
+    if (status != ST_UNSOLVED) {  // this solve is over: record it, move the plant, open the next step's solve
+      e.h(R_INFO + 0) = (double)iter; e.h(R_INFO + 1) = (double)status; e.h(R_INFO + 2) = r.pri; e.h(R_INFO + 3) = r.dua;
+      e.h(R_INFO + 4) = (double)rho_updates;
+      e.h(R_CNT + 0) += (double)iter; e.h(R_CNT + 1) += 1.0; e.h(R_CNT + 2) += (status == ST_SOLVED) ? 0.0 : 1.0;
+      const double* k0 = e.knot(0);
+      u0 = k0[(K_X + NX) * LANES]; u1 = k0[(K_X + NX + 1) * LANES];  // mpc.py:89
+      if (PLANT) {
+        for (int t = 0; t < P.nsub; ++t) {
+          double f[NX];
+          dydt(P, y, u0, u1, f);
+#pragma unroll
+          for (int i = 0; i < NX; ++i) y[i] += f[i] * P.sim_dt;
+        }
+      }
+      if (--nsteps == 0) break;
+      linearise(P, e, y, u0, u1, L, fd);
+      iter = lane_zero; rho_updates = lane_zero;
+      refactor = true;
+    }
+    if (refactor) factor(P, e, L, rho);
   }
   e.h(R_RHO) = rho;
-  e.h(R_INFO + 0) = (double)iter; e.h(R_INFO + 1) = (double)status; e.h(R_INFO + 2) = r.pri; e.h(R_INFO + 3) = r.dua;
-  e.h(R_INFO + 4) = (double)rho_updates;
-  e.h(R_CNT + 0) += (double)iter; e.h(R_CNT + 1) += 1.0; e.h(R_CNT + 2) += (status == ST_SOLVED) ? 0.0 : 1.0;
-  const double* k0 = e.knot(0);
-  u0 = k0[(K_X + NX) * LANES]; u1 = k0[(K_X + NX + 1) * LANES];  // mpc.py:89
   e.h(R_CTRL) = u0; e.h(R_CTRL + 1) = u1;
+}
+
+// one LTVMPC.update for this thread's environment; returns u_0 in (u0, u1) and updates ctrl
+DT_FN void mpc_update(const DevPar& P, const Env& e, const double (&y)[NX], double& u0, double& u1) {
+  double yy[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) yy[i] = y[i];
+  mpc_run<false>(P, e, yy, u0, u1, 1);
 }
 
 

@@ -47,6 +47,7 @@ class HostCore:
         self.H.dthc_set.argtypes = [C.c_void_p, DP, DP]
         self.H.dthc_update.argtypes = [C.c_void_p, DP, DP, DP]
         self.H.dthc_plant.argtypes = [C.c_void_p, DP, DP]
+        self.H.dthc_rollout.argtypes = [C.c_void_p, DP, DP, C.c_int]
         self.H.dthc_solution.argtypes = [C.c_void_p, DP, DP]
         self.N = par.N
         self.n = (par.N + 1) * 6 + par.N * 2
@@ -78,6 +79,12 @@ class HostCore:
         x = np.ascontiguousarray(x, dtype=np.float64).copy()
         self.H.dthc_plant(self.h, self._p(x), self._p(np.ascontiguousarray(u, dtype=np.float64)))
         return x
+
+    def rollout(self, x, nsteps):
+        x = np.ascontiguousarray(x, dtype=np.float64).copy()
+        u = np.zeros(2)
+        self.H.dthc_rollout(self.h, self._p(x), self._p(u), int(nsteps))
+        return x, u
 
     def solution(self):
         x = np.zeros(self.n); y = np.zeros(self.m)

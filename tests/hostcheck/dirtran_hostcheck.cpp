@@ -58,6 +58,16 @@ void dthc_update(void* p, const double* x0, double* u, double* info) {
     info[4] = h->e.h(R_RHO); info[5] = h->e.h(R_INFO + 4);
   }
 }
+// nsteps of the fused loop (update + plant) exactly as dt_rollout_kernel runs it; x in/out, u = last input
+void dthc_rollout(void* p, double* x, double* u, int nsteps) {
+  HC* h = (HC*)p;
+  double y[NX];
+  for (int i = 0; i < NX; ++i) y[i] = x[i];
+  double u0 = h->e.h(R_CTRL), u1 = h->e.h(R_CTRL + 1);
+  mpc_run<true>(h->P, h->e, y, u0, u1, nsteps);
+  for (int i = 0; i < NX; ++i) x[i] = y[i];
+  u[0] = u0; u[1] = u1;
+}
 void dthc_plant(void* p, double* x, const double* u) {
   HC* h = (HC*)p;
   double y[NX];

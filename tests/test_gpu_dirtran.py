@@ -99,8 +99,26 @@ def test_rollout_equals_update_plus_host_plant():
     for s in range(4):
         u = b.update(y)
         y = np.stack([o.plant(y[e], u[e]) for e in range(B)])
-    assert np.abs(ca - u).max() <= 1e-9
-    assert np.abs(ya - y).max() <= 1e-9
+    # device plant (fused multiply-adds) against the oracle's plant, through 4 solves of ~100 iterations each
+    assert np.abs(ca - u).max() <= 1e-8
+    assert np.abs(ya - y).max() <= 1e-8
+    a.close(); b.close()
+
+
+def test_fused_rollout_is_bit_identical_to_single_steps():
+    """dtBatchRollout(k) runs the k steps of a lane as one loop over ADMM iterations (lanes of a warp drift apart in
+    step count); it must give exactly what k calls of dtBatchRollout(1) give, solve for solve"""
+    from robobee3d_b200.dirtran import BatchLTVMPC
+    B, N, k = 96, 10, 6
+    ys = dt_util.mild_states(B, seed=21)
+    a = BatchLTVMPC(B, N=N); a.set_state(y=ys, xr=XR_HOVER); a.rollout(k)
+    b = BatchLTVMPC(B, N=N); b.set_state(y=ys, xr=XR_HOVER)
+    for s in range(k):
+        b.rollout(1)
+    assert np.array_equal(a.state()[0], b.state()[0]) and np.array_equal(a.state()[1], b.state()[1])
+    ca, cb = a.counters(), b.counters()
+    assert ca == cb and ca["solves"] == B * k
+    assert np.array_equal(a.solution()[0], b.solution()[0])
     a.close(); b.close()
 
 
