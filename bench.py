@@ -137,6 +137,149 @@ def run_reference(args):
     return 0
 
 
+def _dt_mild_states(lo, hi, seed=1):
+    """config-5 initial conditions about the hover goal, keyed by the global env id (shard-invariant)"""
+    xr = np.array([-0.03, 0.02, 0, 0, 0, 0.0])
+    y = np.tile(xr, (hi - lo, 1))
+    r = np.random.default_rng(seed)
+    blk = r.uniform(-1.0, 1.0, (hi, 6))[lo:hi]
+    y += blk * np.array([0.01, 0.01, 0.05, 0.05, 0.05, 0.2])
+    return y, xr
+
+
+def _dt_cpu_worker(job):
+    ys, N, nsteps = job
+    from oracle import binding as OB
+    t0 = time.perf_counter()
+    its = 0.0
+    for y in ys:
+        o = OB.OracleDirTran(N=N)
+        X, U, it, bad = o.rollout(y, np.array([-0.03, 0.02, 0, 0, 0, 0.0]), nsteps)
+        its += float(it.sum())
+    return time.perf_counter() - t0, its
+
+
+def run_dirtran(args):
+    """BASELINE configs[4]: planar flapping dir-tran MPC (mpc_thrust_strokedev.py runSim(CTRL_MPC)), B envs x horizon N per
+    GPU.  A step = `--dt-steps` closed-loop MPC periods of every env in ONE launch of dt_rollout_kernel (update -> 60 Euler
+    substeps per period); value = env-steps/s = QP solves/s.  Extra measurement, not the driver's headline line."""
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from robobee3d_b200 import build as _build
+    from robobee3d_b200.dirtran import BatchLTVMPC
+    if rank == 0:
+        _build.build()
+    if world > 1:
+        dist.barrier()
+    nenv, N, S = args.envs, args.horizon, args.dt_steps
+    ys, xr = _dt_mild_states(rank * nenv, (rank + 1) * nenv)
+    b = BatchLTVMPC(nenv, N=N, device=local)
+    b.set_state(y=ys, xr=xr)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        b.rollout(S)
+    barrier()
+    c0 = b.counters()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dev_ms = 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        b.rollout(S)                       # synchronous; CUDA events on the library's stream bracket the launch
+        dev_ms += b.last_kernel_ms()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.finish() if rank == 0 else None
+    c1 = b.counters()
+    its = c1["iters"] - c0["iters"]
+    t = torch.tensor([dev_ms * 1e-3, wall], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([its, c1["unsolved"] - c0["unsolved"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    dev_s, wall = float(t[0]), float(t[1])
+    # e2e: LTVMPC.update through the C-ABI with host buffers (x0 in, u out), the call mpc_thrust_strokedev.py:171 makes
+    e2e = None
+    if not args.no_e2e:
+        yh, _ = b.state()
+        b.update(yh)
+        barrier()
+        t0 = time.perf_counter()
+        ne = 3
+        for _ in range(ne):
+            u = b.update(yh)
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        assert np.isfinite(u).all()
+        e2e = {"value": nenv * world * ne / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 48 * nenv, "d2h_bytes_per_step": 16 * nenv,
+               "call": "dtBatchUpdate (host x0[B][6] in, u[B][2] out; one LTVMPC.update per env at rest near the goal)"}
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        its_all = float(cnt[0])
+        bytes_per_it = (N + 1) * 108 * 8          # DESIGN.md 4.5: unique words per knot and iteration (factor 36 R, iterates 36 R + 36 W)
+        ach = (its / args.steps) * bytes_per_it / (dev_s / args.steps) * 1e-9   # this rank's launch
+        line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s)", "value": nenv * world * S * args.steps / dev_s,
+                "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[4]: planar mpc_osqp flapping MPC (PlanarThrustStrokeDev, LTVMPC N=%d, OSQP eps 1e-5, "
+                                       "check 25, adaptive rho 25), %d envs per GPU about the hover goal, %d MPC periods per launch" % (N, nenv, S),
+                           "envs_per_gpu": nenv, "horizon": N, "mpc_periods_per_launch": S,
+                           "l2_policy": "slab of %.2f GB per GPU streams through L2 every ADMM iteration" % ((40 + 80 * (N + 1)) * 8 * nenv / 1e9)},
+                "qp_iters_per_s": its_all / dev_s, "iters_per_solve": its_all / (nenv * world * S * args.steps), "unsolved": float(cnt[1]),
+                "wall_ms_per_step": 1e3 * wall / args.steps, "gpu_launches": args.steps, "clocks": clocks,
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                             "traffic": DT_TRAFFIC.get((nenv, N, S)), "kernel": "dt_rollout_kernel",
+                             "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
+                             "note": "algorithmic bytes = ADMM iterations of the launch x (N+1) knots x 864 B (unique words: 36 factor "
+                                     "words read, 36 iterate words read and written); the two sweeps ISSUE 196 words (1,568 B) per knot "
+                                     "and iteration, of which L2 serves a part: `traffic` is what reached DRAM"}}
+        if e2e:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu:
+            import multiprocessing as mp
+            cores = os.cpu_count() or 1
+            per, cs = 16, 20
+            jobs = [(ys[i * per:(i + 1) * per], N, cs) for i in range(cores)]
+            t0 = time.perf_counter()
+            with mp.get_context("spawn").Pool(cores) as pool:
+                res = pool.map(_dt_cpu_worker, jobs)
+            tmax = max(r[0] for r in res)
+            line["cpu_baseline"] = {"value": cores * per * cs / tmax, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": "%d of the %d envs x %d MPC periods, one process per host core (oracle port of "
+                                              "LTVMPC + OSQP, dense LDL')" % (cores * per, nenv, cs)}
+        print(json.dumps(line))
+    b.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of one dt_rollout_kernel launch from the ncu --set full captures under
+# profiles/ (key: envs, horizon, MPC periods per launch)
+DT_TRAFFIC = {(65536, 10, 10): 222.15e9}   # profiles/r01g_ncu_full_dt_rollout_kernel.txt: 156.89 GB read + 65.26 GB written
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -150,7 +293,9 @@ def main():
     ap.add_argument("--hl-interval", type=float, default=None,
                     help="MPC period in ms (controlTest's hlInterval; config 1 uses 5): a step then advances every env by one "
                          "MPC period (26 plant steps at 5 ms) in one launch.  Extra measurement; the headline line uses None")
-    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp"],
+    ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
+    ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     ap.add_argument("--converged", action="store_true",
@@ -160,6 +305,8 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "dirtran":
+        return run_dirtran(args)
 
     import torch
     import torch.distributed as dist

@@ -296,11 +296,26 @@ extern "C" int dtBatchUpdate(DtBatch* b, const double* x0, double* u) {
   return UMPC_OK;
 }
 
+// Launch shape of the rollout: threads per block and a dynamic shared-memory reservation whose only purpose is to cap
+// the resident threads per SM (the kernel uses no shared memory).  Fewer resident environments = a smaller working set
+// per ADMM iteration; once it fits the 126 MB L2 the iteration stops paying HBM for its second sweep.
+// Tuning knobs DT_TPB / DT_SMEM_KB override the per-horizon default.
+static void dt_launch_shape(const DtBatch* b, int* tpb, int* smem) {
+  *tpb = 128; *smem = 0;
+  const char* e = getenv("DT_TPB");
+  if (e && (atoi(e) == 32 || atoi(e) == 64 || atoi(e) == 128)) *tpb = atoi(e);
+  e = getenv("DT_SMEM_KB");
+  if (e && atoi(e) >= 0 && atoi(e) <= 220) *smem = atoi(e) * 1024;
+}
+
 extern "C" int dtBatchRollout(DtBatch* b, int nsteps) {
   if (!b || nsteps < 0) return UMPC_ERR_ARG;
   DCK(cudaSetDevice(b->device));
+  int tpb, smem;
+  dt_launch_shape(b, &tpb, &smem);
+  if (smem > 48 * 1024) DCK(cudaFuncSetAttribute(dt_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   DCK(cudaEventRecord(b->ev0, b->stream));
-  dt_rollout_kernel<<<(b->B + 127) / 128, 128, 0, b->stream>>>(b->dp, b->slab, b->rows, b->B, nsteps);
+  dt_rollout_kernel<<<(b->B + tpb - 1) / tpb, tpb, smem, b->stream>>>(b->dp, b->slab, b->rows, b->B, nsteps);
   DCK(cudaGetLastError());
   DCK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;
