@@ -137,6 +137,22 @@ def run_reference(args):
     return 0
 
 
+def _init_nccl(dist, torch, local):
+    """process group + communicator set-up with file descriptor 1 pointed at stderr: the box exports NCCL_DEBUG=VERSION
+    and NCCL writes its version banner to stdout, which belongs to the one JSON line"""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.barrier()
+        torch.cuda.synchronize()
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
+
+
 def _dt_mild_states(lo, hi, seed=1):
     """config-5 initial conditions about the hover goal, keyed by the global env id (shard-invariant)"""
     xr = np.array([-0.03, 0.02, 0, 0, 0, 0.0])
@@ -170,7 +186,7 @@ def run_dirtran(args):
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        _init_nccl(dist, torch, local)
     from robobee3d_b200 import build as _build
     from robobee3d_b200.dirtran import BatchLTVMPC
     if rank == 0:
@@ -317,7 +333,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        _init_nccl(dist, torch, local)
     from robobee3d_b200 import build as _build
     from robobee3d_b200.batch import BatchUMPC, gather_metrics, shard_range
     from robobee3d_b200 import flops as F
@@ -399,7 +415,8 @@ def main():
         assert torch.isfinite(hp).all()
         e2e = {"value": nenv * world * args.steps / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 27 * 4 * nenv,
                "d2h_bytes_per_step": 27 * 4 * nenv, "ms_per_step": 1e3 * float(te[0]) / args.steps,
-               "call": "umpcBatchEnvStep (pinned host buffers; umpcUpdate + clip + quadrotorNLDyn per env)"}
+               "call": "umpcBatchEnvStep (pinned host buffers read and written in place by one zero-copy kernel; umpcUpdate + clip + "
+                       "quadrotorNLDyn per env)"}
         b2.close()
 
     mean_iter = float(b.solve_info()["iter"].mean()) if args.converged else 50.0

@@ -199,6 +199,142 @@ umpc_update_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params
   SOLVER::template release<TPB>(&tmem_slot);
 }
 
+// ---- kernel 1b: the same env-step with its inputs and outputs in PINNED HOST memory (zero-copy) ----------------
+// The host-buffer entry points (umpcBatchUpdate / umpcBatchEnvStep) hand this kernel the caller's own [B][k] arrays,
+// mapped into the device address space: each CTA pulls its environments' slices over PCIe with coalesced 128-bit loads
+// into shared memory, solves, and pushes its results back with coalesced 128-bit stores.  No staging copies, no chunk
+// pipeline: transfer and compute overlap CTA by CTA (while one CTA waits for its inputs the others solve; result
+// stores are posted writes).  in: p0[3] R0[9] dq0[6] pdes[3] dpdes[3] sdes[3]; out: uquad[3] accdes[6] and, for the
+// env-step, p_next[3] R_next[9] dq_next[6].
+struct HostIO {
+  const float* in[6];
+  const float* aT0;  // [B] or null
+  float* out[5];     // out[2..4] null: update only
+  int nenv;          // environments the host arrays hold (the grid covers the padded slots as well)
+  unsigned* pulled;  // device counter (zero at launch): CTAs whose input pull has completed
+  int window;        // CTAs allowed to pull at the same time (0: no ordering)
+};
+
+// one array's slice, phase 1: every thread issues its (at most ceil(k/4)) 128-bit loads from host memory into registers
+template <int TPB, int K>
+__device__ __forceinline__ void hostio_load(float4 (&v)[(K + 3) / 4], const float* __restrict__ src, int nvalid_env) {
+  const int nv = nvalid_env * K;
+#pragma unroll
+  for (int j = 0; j < (K + 3) / 4; ++j) {
+    const int i = (threadIdx.x + j * TPB) * 4;
+    v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < TPB * K) {
+      if (i + 3 < nv) v[j] = *reinterpret_cast<const float4*>(src + i);
+      else if (i < nv) { v[j].x = src[i]; if (i + 1 < nv) v[j].y = src[i + 1]; if (i + 2 < nv) v[j].z = src[i + 2]; }
+    }
+  }
+}
+// phase 2: registers -> shared memory
+template <int TPB, int K>
+__device__ __forceinline__ void hostio_stash(float* __restrict__ dst, const float4 (&v)[(K + 3) / 4]) {
+#pragma unroll
+  for (int j = 0; j < (K + 3) / 4; ++j) {
+    const int i = (threadIdx.x + j * TPB) * 4;
+    if (i < TPB * K) *reinterpret_cast<float4*>(dst + i) = v[j];
+  }
+}
+template <int TPB>
+__device__ __forceinline__ void hostio_push(float* __restrict__ dst, const float* __restrict__ src, int k, int nvalid_env) {
+  const int n = TPB * k, nv = nvalid_env * k;
+  for (int i = threadIdx.x * 4; i < n; i += TPB * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(src + i);
+    if (i + 3 < nv) *reinterpret_cast<float4*>(dst + i) = v;
+    else if (i < nv) { dst[i] = v.x; if (i + 1 < nv) dst[i + 1] = v.y; if (i + 2 < nv) dst[i + 2] = v.z; }
+  }
+}
+
+template <int TPB, class SOLVER>
+__global__ void __launch_bounds__(TPB, SOLVER::kMinBlocks)
+umpc_hostio_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params> kp, const __grid_constant__ DevState s,
+                   const __grid_constant__ HostIO io, int want_qpdata) {
+  // slices of the CTA's TPB environments, [env][k] like the host arrays: p R dq pdes dpdes sdes | uq acc p' R' dq'
+  constexpr int OFF_IN[6] = {0, 3, 12, 18, 21, 24};
+  constexpr int OFF_OUT[5] = {0, 3, 9, 12, 21}, K_OUT[5] = {3, 6, 3, 9, 6};
+  __shared__ __align__(16) float sin_[27 * TPB];
+  __shared__ __align__(16) float sout_[27 * TPB];
+  __shared__ uint32_t tmem_slot;
+  const int cta0 = blockIdx.x * TPB, t = threadIdx.x, e = cta0 + t;
+  const int nvalid = min(max(io.nenv - cta0, 0), TPB);
+  const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);
+  // Ordered pulls: the link serves all outstanding requests round-robin, so CTAs that all pull at once all get their
+  // data at the same time (the whole first wave of 296 CTAs after ~90 us, SMs idle until then, and again for the second
+  // wave).  Letting only `window` CTAs pull at a time, in block order, hands the link's bandwidth to a few CTAs at a
+  // time: CTA i has its inputs after ~i x 0.3 us and solves while the later ones are still being served.  Blocks are
+  // dispatched in index order, so a CTA only ever waits for CTAs that are already resident (or done).
+  if (io.window) {
+    if (t == 0) {
+      // (the order is a performance hint only: give up after ~50 ms rather than ever hang on a scheduling surprise)
+      for (int spin = 0; spin < 250000 && (int)(*(volatile unsigned*)io.pulled) + io.window <= (int)blockIdx.x; ++spin) __nanosleep(200);
+    }
+    __syncthreads();
+  }
+  {  // all loads of the CTA's six slices in flight before the first is consumed: one PCIe round trip, not seven
+    float4 v0[1], v1[3], v2[2], v3[1], v4[1], v5[1];
+    hostio_load<TPB, 3>(v0, io.in[0] + (size_t)cta0 * 3, nvalid); hostio_load<TPB, 9>(v1, io.in[1] + (size_t)cta0 * 9, nvalid);
+    hostio_load<TPB, 6>(v2, io.in[2] + (size_t)cta0 * 6, nvalid); hostio_load<TPB, 3>(v3, io.in[3] + (size_t)cta0 * 3, nvalid);
+    hostio_load<TPB, 3>(v4, io.in[4] + (size_t)cta0 * 3, nvalid); hostio_load<TPB, 3>(v5, io.in[5] + (size_t)cta0 * 3, nvalid);
+    hostio_stash<TPB, 3>(sin_ + OFF_IN[0] * TPB, v0); hostio_stash<TPB, 9>(sin_ + OFF_IN[1] * TPB, v1);
+    hostio_stash<TPB, 6>(sin_ + OFF_IN[2] * TPB, v2); hostio_stash<TPB, 3>(sin_ + OFF_IN[3] * TPB, v3);
+    hostio_stash<TPB, 3>(sin_ + OFF_IN[4] * TPB, v4); hostio_stash<TPB, 3>(sin_ + OFF_IN[5] * TPB, v5);
+  }
+  const float aT0 = (io.aT0 && t < nvalid) ? io.aT0[e] : -1.0f;
+  __syncthreads();
+  if (io.window && t == 0) atomicAdd(io.pulled, 1u);
+  {
+  const volatile float* sp = sin_ + OFF_IN[0] * TPB + t * 3; const volatile float* sR = sin_ + OFF_IN[1] * TPB + t * 9;
+  const volatile float* sdq = sin_ + OFF_IN[2] * TPB + t * 6;
+  float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    p[i] = sp[i]; pd[i] = sin_[OFF_IN[3] * TPB + t * 3 + i];
+    dpd[i] = sin_[OFF_IN[4] * TPB + t * 3 + i]; sd[i] = sin_[OFF_IN[5] * TPB + t * 3 + i];
+  }
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] = sR[i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) dq[i] = sdq[i];
+  float* const eb = env_base(s, e);
+  SOLVER sol;
+  sol.init(scratch_base, s, e);
+  if (want_qpdata) sol.qpdata(kp.mpc, s, e, p, R, dq, pd, dpd, sd, aT0);
+  float uq[3], acc[6];
+  sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pd, dpd, sd, aT0);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { sout_[OFF_OUT[0] * TPB + t * 3 + i] = uq[i]; eb[ROWF(ROW_UQ + i)] = uq[i]; }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { sout_[OFF_OUT[1] * TPB + t * 6 + i] = acc[i]; eb[ROWF(ROW_ACC + i)] = acc[i]; }
+  if (io.out[2]) {
+    // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
+    // (inputs re-read from shared memory: they were not kept in registers over the solve)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) p[i] = sp[i];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = sR[i];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dq[i] = sdq[i];
+    uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
+    uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
+    sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) sout_[OFF_OUT[2] * TPB + t * 3 + i] = p[i];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sout_[OFF_OUT[3] * TPB + t * 9 + i] = R[i];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) sout_[OFF_OUT[4] * TPB + t * 6 + i] = dq[i];
+  }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int a = 0; a < 5; ++a)
+    if (io.out[a]) hostio_push<TPB>(io.out[a] + (size_t)cta0 * K_OUT[a], sout_ + OFF_OUT[a] * TPB, K_OUT[a], nvalid);
+  SOLVER::template release<TPB>(&tmem_slot);
+}
+
 // ---- kernel 2: fused closed loop (uprightmpc2.py:87-159) -------------------------------------
 // Per plant step: task -> [umpcUpdate when the host-computed schedule fires] -> [WL stage] ->
 // torque clip -> rigid-body step -> metric sums.  Plant state stays in registers for the

@@ -333,6 +333,7 @@ struct UmpcBatch {
   cudaStream_t stream = nullptr;
   cudaStream_t side[3] = {nullptr, nullptr, nullptr};  // chunk pipeline of the host-buffer calls
   cudaEvent_t side_ev = nullptr, join_ev[3] = {nullptr, nullptr, nullptr};
+  unsigned* d_pulled = nullptr;         // zero-copy host-buffer calls: ordered-pull counter
   cudaGraphExec_t g_exec = nullptr;     // captured chunk pipeline of the host-buffer calls + what it was captured for
   std::vector<const void*> g_key;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
@@ -511,6 +512,7 @@ extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
   cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
   if (b->g_exec) cudaGraphExecDestroy(b->g_exec);
+  if (b->d_pulled) cudaFree(b->d_pulled);
   for (int i = 0; i < 3; ++i) { if (b->side[i]) cudaStreamDestroy(b->side[i]); if (b->join_ev[i]) cudaEventDestroy(b->join_ev[i]); }
   if (b->side_ev) cudaEventDestroy(b->side_ev);
   cudaStreamDestroy(b->stream);
@@ -636,9 +638,52 @@ static int run_chunked(UmpcBatch* b, HostArr* in, int nin, HostArr* out, int nou
   static int nchunks_env = -1, no_graph = -1;
   if (nchunks_env < 0) { const char* ev = getenv("UMPC_E2E_CHUNKS"); nchunks_env = ev ? atoi(ev) : 0; if (nchunks_env < 0) nchunks_env = 0; }
   if (no_graph < 0) { const char* ev = getenv("UMPC_NO_GRAPH"); no_graph = (ev && atoi(ev)) ? 1 : 0; }
-  bool pinned = !no_graph;
+  bool pinned = true;
   for (int a = 0; a < nin && pinned; ++a) if (in[a].h_in) pinned = host_pinned(in[a].h_in);
   for (int a = 0; a < nout && pinned; ++a) pinned = host_pinned(out[a].h_out);
+  // Zero-copy path (default for pinned buffers; UMPC_E2E_ZEROCOPY=0 falls back to the copy pipeline below): ONE launch of
+  // umpc_hostio_kernel on the caller's own arrays.  Needs the default launch shape (128 threads, TMEM scratch, shared
+  // weights, float32 path) and 16-byte aligned arrays.
+  const char* zc_ev = getenv("UMPC_E2E_ZEROCOPY");  // read per call: the tests switch paths inside one process
+  const int zc_env = (zc_ev && !atoi(zc_ev)) ? 0 : 1;
+  if (pinned && zc_env && b->tpb == 128 && !b->s.wts && !b->conv && nin == 7 && (nout == 2 || nout == 5)) {
+    HostIO io;
+    memset(&io, 0, sizeof io);
+    bool ok = true;
+    for (int a = 0; a < 6 && ok; ++a) {
+      void* d = nullptr;
+      ok = cudaHostGetDevicePointer(&d, (void*)in[a].h_in, 0) == cudaSuccess && ((uintptr_t)d & 15) == 0;
+      io.in[a] = (const float*)d;
+    }
+    if (ok && in[6].h_in) {
+      void* d = nullptr;
+      ok = cudaHostGetDevicePointer(&d, (void*)in[6].h_in, 0) == cudaSuccess;
+      io.aT0 = (const float*)d;
+    }
+    for (int a = 0; a < nout && ok; ++a) {
+      void* d = nullptr;
+      ok = cudaHostGetDevicePointer(&d, (void*)out[a].h_out, 0) == cudaSuccess && ((uintptr_t)d & 15) == 0;
+      io.out[a] = (float*)d;
+    }
+    if (!ok) cudaGetLastError();
+    else {
+      io.nenv = b->B;
+      const char* wv = getenv("UMPC_E2E_WINDOW");   // tuning knob; 0 = unordered pulls
+      io.window = wv ? atoi(wv) : 32;
+      if (io.window < 0) io.window = 0;
+      if (!b->d_pulled) CK(cudaMalloc(&b->d_pulled, sizeof(unsigned)));
+      io.pulled = b->d_pulled;
+      CK(cudaMemsetAsync(b->d_pulled, 0, sizeof(unsigned), b->stream));
+      CK(cudaEventRecord(b->ev0, b->stream));
+      umpc_hostio_kernel<128, SolverF32<128, TmemStore>><<<b->Bp / 128, 128, 0, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
+      CK(cudaGetLastError());
+      CK(cudaEventRecord(b->ev1, b->stream));
+      b->timed = true;
+      CK(cudaStreamSynchronize(b->stream));
+      return UMPC_OK;
+    }
+  }
+  if (no_graph) pinned = false;
   if (!pinned) {
     int rc = issue_chunks(b, in, nin, out, nout, duq, dacc, din, daT, dpn, dRn, ddqn, nchunks_env ? nchunks_env : 2);
     if (rc) return rc;

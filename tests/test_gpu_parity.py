@@ -137,13 +137,16 @@ def test_dropin_single_controller_matches_golden(cuda_required, gold):
             assert up.info()["iter"] == 50
 
 
-def test_host_buffer_calls_pinned_graph_path_equals_pageable_path(cuda_required):
-    """umpcBatchUpdate / umpcBatchEnvStep with PINNED host buffers replay a captured CUDA graph of the chunk pipeline;
-    with pageable numpy buffers they issue the copies directly.  Same kernels, same results -- bit for bit -- over
-    several calls (the graph is replayed), after a change of buffers (re-capture), and for a ragged batch size."""
+@pytest.mark.parametrize("zerocopy", ["1", "0"])
+def test_host_buffer_calls_pinned_paths_equal_pageable_path(cuda_required, zerocopy, monkeypatch):
+    """umpcBatchUpdate / umpcBatchEnvStep with PINNED host buffers run ONE zero-copy kernel on the caller's arrays
+    (umpc_hostio_kernel; default) or, with UMPC_E2E_ZEROCOPY=0, replay a captured CUDA graph of the chunk pipeline;
+    with pageable numpy buffers they issue the copies directly.  Same solver code, same results -- bit for bit -- over
+    several calls (in-place state buffers, graph replay), after a change of buffers, and for ragged batch sizes."""
     import torch
     from robobee3d_b200.batch import BatchUMPC
-    for B in (20000, 4097):
+    monkeypatch.setenv("UMPC_E2E_ZEROCOPY", zerocopy)
+    for B in (20000, 4097, 130):
         p, R, dq = util.config2_states(B, seed=5)
         Rc = np.ascontiguousarray(R.transpose(0, 2, 1).reshape(B, 9), np.float32)
         f = lambda a: np.ascontiguousarray(a, np.float32)

@@ -161,3 +161,14 @@ def test_converged_formulation_on_host_matches_oracle_f64():
                 xr = conv["x"][e]
                 assert int(g["info"][0]) == int(conv["iter"][e])
                 assert np.abs(g["x"] - xr).max() <= 10 * 1e-4 + 1e-4 * np.abs(xr).max()
+
+
+def test_dirtran_bench_shards_reproduce_the_same_envs():
+    """bench.py --workload dirtran: a rank's initial conditions are keyed by the global env id, so N ranks of B envs hold
+    exactly the envs one rank of N*B would"""
+    import bench
+    whole, xr = bench._dt_mild_states(0, 96)
+    for lo, hi in ((0, 32), (32, 64), (64, 96)):
+        part, xr2 = bench._dt_mild_states(lo, hi)
+        assert np.array_equal(part, whole[lo:hi]) and np.array_equal(xr, xr2)
+    assert np.abs(whole - xr).max() <= 0.2 and np.abs(whole - xr).max() > 0.05
