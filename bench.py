@@ -153,6 +153,19 @@ def _init_nccl(dist, torch, local):
         os.close(saved)
 
 
+def _bind_to_gpu_numa_node(local):
+    """pin this rank to the CPU cores next to its GPU (NVML's affinity mask) BEFORE it allocates pinned host buffers, so
+    that first touch puts them on the GPU's own NUMA node: the zero-copy e2e leg of 8 ranks then does not cross sockets"""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return sorted(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def _dt_mild_states(lo, hi, seed=1):
     """config-5 initial conditions about the hover goal, keyed by the global env id (shard-invariant)"""
     xr = np.array([-0.03, 0.02, 0, 0, 0, 0.0])
@@ -252,7 +265,7 @@ def run_dirtran(args):
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         its_all = float(cnt[0])
-        bytes_per_it = (N + 1) * 108 * 8          # unique words per knot and iteration (factor 36 R, iterates 36 R + 36 W)
+        bytes_per_it = (N + 1) * 96 * 8           # unique words per knot and iteration (factor 36 R, iterates 30 R + 30 W)
         ach = (its / args.steps) * bytes_per_it / (dev_s / args.steps) * 1e-9   # this rank's launch
         line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s)", "value": nenv * world * S * args.steps / dev_s,
                 "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
@@ -260,14 +273,14 @@ def run_dirtran(args):
                 "config": {"workload": "BASELINE configs[4]: planar mpc_osqp flapping MPC (PlanarThrustStrokeDev, LTVMPC N=%d, OSQP eps 1e-5, "
                                        "check 25, adaptive rho 25), %d envs per GPU about the hover goal, %d MPC periods per launch" % (N, nenv, S),
                            "envs_per_gpu": nenv, "horizon": N, "mpc_periods_per_launch": S,
-                           "l2_policy": "slab of %.2f GB per GPU streams through L2 every ADMM iteration" % ((40 + 80 * (N + 1)) * 8 * nenv / 1e9)},
+                           "l2_policy": "slab of %.2f GB per GPU streams through L2 every ADMM iteration" % ((44 + 74 * (N + 1)) * 8 * nenv / 1e9)},
                 "qp_iters_per_s": its_all / dev_s, "iters_per_solve": its_all / (nenv * world * S * args.steps), "unsolved": float(cnt[1]),
                 "wall_ms_per_step": 1e3 * wall / args.steps, "gpu_launches": args.steps, "clocks": clocks,
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                              "traffic": DT_TRAFFIC.get((nenv, N, S)), "kernel": "dt_rollout_kernel",
                              "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
-                             "note": "algorithmic bytes = ADMM iterations of the launch x (N+1) knots x 864 B (unique words: 36 factor "
-                                     "words read, 36 iterate words read and written); the two sweeps ISSUE 196 words (1,568 B) per knot "
+                             "note": "algorithmic bytes = ADMM iterations of the launch x (N+1) knots x 768 B (unique words: 36 factor "
+                                     "words read, 30 iterate words read and written); the two sweeps ISSUE 178 words (1,424 B) per knot "
                                      "and iteration, of which L2 serves a part: `traffic` is what reached DRAM"}}
         if e2e:
             line["e2e"] = e2e
@@ -293,7 +306,7 @@ def run_dirtran(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one dt_rollout_kernel launch from the ncu --set full captures under
 # profiles/ (key: envs, horizon, MPC periods per launch)
-DT_TRAFFIC = {(65536, 10, 10): 222.15e9}   # profiles/r01g_ncu_full_dt_rollout_kernel.txt: 156.89 GB read + 65.26 GB written
+DT_TRAFFIC = {(65536, 10, 10): 195.81e9}   # profiles/r01i_ncu_full_dt_rollout_kernel.txt: 139.16 GB read + 56.65 GB written
 
 
 def main():
@@ -333,6 +346,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        _bind_to_gpu_numa_node(local)
         _init_nccl(dist, torch, local)
     from robobee3d_b200 import build as _build
     from robobee3d_b200.batch import BatchUMPC, gather_metrics, shard_range

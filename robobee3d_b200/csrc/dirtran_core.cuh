@@ -25,9 +25,12 @@ namespace dtcore {
 constexpr int NX = DT_NX, NU = DT_NU, NW = NX + NU;
 // header rows of an environment's slab column
 constexpr int R_Y = 0, R_CTRL = 6, R_RHO = 8, R_INFO = 9 /* iter,status,pri,dua,rho_updates */, R_LIN = 14 /* 12 */,
-              R_XR = 26, R_CNT = 32 /* iters, solves, unsolved */, R_STEPS = 35 /* steps left in the running call */, R_HDR = 40;
+              R_XR = 26, R_CNT = 32 /* iters, solves, unsolved */, R_STEPS = 35 /* steps left in the running call */,
+              R_Y0 = 36 /* 6: initial state of the last solve */, R_HDR = 44;
 // rows of knot k (stride 128)
-constexpr int K_X = 0, K_ZI = 8, K_YI = 16, K_ZE = 24, K_YE = 30, K_SCR = 36, K_LD = 44, K_STRIDE = 80;
+// (z of the equality rows is not stored: after an iteration it IS the bound, -fd for the dynamics rows of every knot and
+// -y0 for the initial-state rows; until the first iteration of a solve it is the previous solve's bound -- header rows)
+constexpr int K_X = 0, K_ZI = 8, K_YI = 16, K_YE = 24, K_SCR = 30, K_LD = 38, K_STRIDE = 74;
 constexpr int LANES = 32;
 
 constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_EQ_OVER_INEQ = 1e3;  // osqp constants.h
@@ -218,9 +221,11 @@ DT_FN void chol_solve(const double (&Lk)[NW * (NW + 1) / 2], double (&v)[NW]) {
 //   backward  x~_k = t_k + rho_e S_k^-1 [Ad Bd]' x~_{k+1}
 // Per knot and iteration: 36 factor words read per sweep, the 36 iterate words read twice and written once, t written
 // and read once (196 doubles).
+// zd / z0: z of the dynamics / initial-state rows as OSQP holds it on entry (see K_* above).
 DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const double (&fd)[NX],
-                                               const double (&y0)[NX], const double (&q)[NX], double rho) {
-  const double rho_e = RHO_EQ_OVER_INEQ * rho, rho_e_inv = 1.0 / rho_e, alpha = P.alpha, oma = 1.0 - P.alpha;
+                                               const double (&y0)[NX], const double (&q)[NX], double rho,
+                                               const double (&zd)[NX], const double (&z0)[NX]) {
+  const double rho_e = RHO_EQ_OVER_INEQ * rho, alpha = P.alpha, oma = 1.0 - P.alpha;
   double rin[NW], rin_inv[NW];
 #pragma unroll
   for (int j = 0; j < NW; ++j) { rin[j] = rho_of_row(P, j, rho); rin_inv[j] = 1.0 / rin[j]; }
@@ -230,7 +235,7 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
   {
     const double* kb = e.knot(0);
 #pragma unroll
-    for (int i = 0; i < NX; ++i) te[i] = rho_e * kb[(K_ZE + i) * LANES] - kb[(K_YE + i) * LANES];
+    for (int i = 0; i < NX; ++i) te[i] = rho_e * z0[i] - kb[(K_YE + i) * LANES];
   }
   for (int k = 0; k <= N; ++k) {
     double* kb = e.knot(k);
@@ -247,7 +252,7 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
     if (!last) {
       const double* kn = e.knot(k + 1);
 #pragma unroll
-      for (int i = 0; i < NX; ++i) te[i] = rho_e * kn[(K_ZE + i) * LANES] - kn[(K_YE + i) * LANES];
+      for (int i = 0; i < NX; ++i) te[i] = rho_e * zd[i] - kn[(K_YE + i) * LANES];
       L.mulT_add(te, b);
     } else {
       b[NX] = 0.0; b[NX + 1] = 0.0;
@@ -293,10 +298,9 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
       L.mul(xt, zt);
 #pragma unroll
       for (int i = 0; i < NX; ++i) {
-        const double zp = kn[(K_ZE + i) * LANES], yp = kn[(K_YE + i) * LANES];
+        const double zp = zd[i], yp = kn[(K_YE + i) * LANES];
         const double v = alpha * (zt[i] - xn[i]) + oma * zp;
-        const double zn = fmin(fmax(v + rho_e_inv * yp, -fd[i]), -fd[i]);
-        kn[(K_ZE + i) * LANES] = zn;
+        const double zn = -fd[i];  // = min(max(v + y/rho, l), u) with l = u = -fd
         kn[(K_YE + i) * LANES] = yp + rho_e * (v - zn);
       }
     }
@@ -318,10 +322,9 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
     double* kb = e.knot(0);
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
-      const double zp = kb[(K_ZE + i) * LANES], yp = kb[(K_YE + i) * LANES];
+      const double zp = z0[i], yp = kb[(K_YE + i) * LANES];
       const double v = alpha * (-xn[i]) + oma * zp;
-      const double zn = fmin(fmax(v + rho_e_inv * yp, -y0[i]), -y0[i]);
-      kb[(K_ZE + i) * LANES] = zn;
+      const double zn = -y0[i];
       kb[(K_YE + i) * LANES] = yp + rho_e * (v - zn);
     }
   }
@@ -330,7 +333,8 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
 struct Resid { double pri, dua, nprim, ndual; };
 
 // osqp auxil.c compute_pri_res / compute_dua_res and the norms of compute_pri_tol / compute_dua_tol (scaling off)
-DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double (&q)[NX]) {
+DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double (&q)[NX], const double (&zd)[NX],
+                      const double (&z0)[NX]) {
   const int N = P.N;
   double pri = 0.0, nz = 0.0, nAx = 0.0, dua = 0.0, nPx = 0.0, nAty = 0.0, nq = 0.0;
 #pragma unroll
@@ -350,7 +354,7 @@ DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double 
       if (!(last && j >= NX)) { pri = fmax(pri, fabs(x[j] - zi)); nz = fmax(nz, fabs(zi)); nAx = fmax(nAx, fabs(x[j])); }
     }
 #pragma unroll
-    for (int i = 0; i < NX; ++i) { ye[i] = kb[(K_YE + i) * LANES]; ze[i] = kb[(K_ZE + i) * LANES]; aty[i] -= ye[i]; }
+    for (int i = 0; i < NX; ++i) { ye[i] = kb[(K_YE + i) * LANES]; ze[i] = (k == 0) ? z0[i] : zd[i]; aty[i] -= ye[i]; }
     if (!last) {
       double ax[NX];
       L.mul(x, ax);
@@ -405,17 +409,23 @@ DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, d
 #pragma unroll
   for (int i = 0; i < NX; ++i) q[i] = -P.wx[i] * e.h(R_XR + i);
   double rho = e.h(R_RHO);
+  // z of the equality rows as the warm start holds it: the bounds of the previous solve (0 for a fresh controller)
+  double zd[NX], z0[NX], y0[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) { zd[i] = 0.0 - e.h(R_LIN + 6 + i); z0[i] = 0.0 - e.h(R_Y0 + i); y0[i] = y[i]; }
   linearise(P, e, y, u0, u1, L, fd);
   factor(P, e, L, rho);
   int iter = lane_zero, rho_updates = lane_zero;
   while (true) {
     ++iter;
-    admm_iteration(P, e, L, fd, y, q, rho);
+    admm_iteration(P, e, L, fd, y0, q, rho, zd, z0);
+#pragma unroll
+    for (int i = 0; i < NX; ++i) { zd[i] = -fd[i]; z0[i] = -y0[i]; }
     const bool at_max = iter >= P.max_iter;
     const bool checked = P.check_termination && (iter % P.check_termination == 0);
     const bool adapt = P.adaptive_rho_interval && (iter % P.adaptive_rho_interval == 0);
     if (!(checked || adapt || at_max)) continue;
-    const Resid r = residuals(P, e, L, q);
+    const Resid r = residuals(P, e, L, q, zd, z0);
     // order of osqp.c's loop: termination test, then the rho adaptation, then (out of iterations) the final tests
     int status = (checked && converged(P, r, 1.0)) ? ST_SOLVED : ST_UNSOLVED;
     bool refactor = false;
@@ -446,6 +456,8 @@ DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, d
         }
       }
       if (--nsteps == 0) break;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) y0[i] = y[i];
       linearise(P, e, y, u0, u1, L, fd);
       iter = lane_zero; rho_updates = lane_zero;
       refactor = true;
@@ -454,6 +466,8 @@ DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, d
   }
   e.h(R_RHO) = rho;
   e.h(R_CTRL) = u0; e.h(R_CTRL + 1) = u1;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) e.h(R_Y0 + i) = y0[i];
 }
 
 // one LTVMPC.update for this thread's environment; returns u_0 in (u0, u1) and updates ctrl

@@ -21,7 +21,7 @@ ap.add_argument("--max-gb", type=float, default=60.0)
 a = ap.parse_args()
 for N in [int(x) for x in a.N.split(",")]:
     for B in [int(x) for x in a.B.split(",")]:
-        rows = 40 + 80 * (N + 1)
+        rows = 44 + 74 * (N + 1)
         gb = rows * 8 * B / 1e9
         if gb > a.max_gb:
             print(json.dumps({"N": N, "B": B, "skipped": "slab %.1f GB" % gb})); continue
@@ -34,8 +34,8 @@ for N in [int(x) for x in a.N.split(",")]:
         ms = b.last_kernel_ms()
         c1 = b.counters()
         its = c1["iters"] - c0["iters"]
-        # bytes per knot and iteration of the two sweeps: 152 doubles read + 44 written
-        traffic = its * (N + 1) * 196 * 8
+        # bytes per knot and iteration of the two sweeps: 140 doubles read + 38 written
+        traffic = its * (N + 1) * 178 * 8
         print(json.dumps({"N": N, "B": B, "steps": a.steps, "ms": round(ms, 3), "env_steps_per_s": B * a.steps / ms * 1e3,
                           "qp_iters_per_s": its / ms * 1e3, "iters_per_solve": its / (B * a.steps),
                           "unsolved": c1["unsolved"] - c0["unsolved"], "model_GBps": traffic / ms / 1e6,
