@@ -265,7 +265,7 @@ def run_dirtran(args):
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         its_all = float(cnt[0])
-        bytes_per_it = (N + 1) * 96 * 8           # unique words per knot and iteration (factor 36 R, iterates 30 R + 30 W)
+        bytes_per_it = (N + 1) * 76 * 8           # unique words per knot and iteration (factor 36 R, iterates 20 R + 20 W)
         ach = (its / args.steps) * bytes_per_it / (dev_s / args.steps) * 1e-9   # this rank's launch
         line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s)", "value": nenv * world * S * args.steps / dev_s,
                 "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
@@ -279,8 +279,9 @@ def run_dirtran(args):
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                              "traffic": DT_TRAFFIC.get((nenv, N, S)), "kernel": "dt_rollout_kernel",
                              "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
-                             "note": "algorithmic bytes = ADMM iterations of the launch x (N+1) knots x 768 B (unique words: 36 factor "
-                                     "words read, 30 iterate words read and written); the two sweeps ISSUE 178 words (1,424 B) per knot "
+                             "note": "algorithmic bytes = ADMM iterations of the launch x (N+1) knots x 608 B (unique words: 36 factor "
+                                     "words read, 20 iterate words read and written -- x 8, z/y of the 3 finitely bounded rows, y of the "
+                                     "6 dynamics rows); the two sweeps ISSUE 148 words (1,184 B) per knot "
                                      "and iteration, of which L2 serves a part: `traffic` is what reached DRAM"}}
         if e2e:
             line["e2e"] = e2e
@@ -306,7 +307,7 @@ def run_dirtran(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one dt_rollout_kernel launch from the ncu --set full captures under
 # profiles/ (key: envs, horizon, MPC periods per launch)
-DT_TRAFFIC = {(65536, 10, 10): 195.81e9}   # profiles/r01i_ncu_full_dt_rollout_kernel.txt: 139.16 GB read + 56.65 GB written
+DT_TRAFFIC = {(65536, 10, 10): 152.38e9}   # profiles/r01j_ncu_full_dt_rollout_kernel.txt: 110.69 GB read + 41.68 GB written
 
 
 def main():

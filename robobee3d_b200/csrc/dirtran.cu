@@ -45,6 +45,7 @@ __device__ __forceinline__ Env env_of(double* slab, int rows, int e) {
 }
 
 // kernel 1: one LTVMPC.update per environment from caller-supplied states (x0 [B][6] in, u [B][2] out)
+template <bool PF>
 __global__ void __launch_bounds__(128) dt_update_kernel(const __grid_constant__ DevPar P, double* __restrict__ slab, int rows, int nenv,
                                                         const double* __restrict__ x0, double* __restrict__ uout) {
   const int id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -54,11 +55,12 @@ __global__ void __launch_bounds__(128) dt_update_kernel(const __grid_constant__ 
 #pragma unroll
   for (int i = 0; i < NX; ++i) { y[i] = x0[(size_t)id * NX + i]; e.h(R_Y + i) = y[i]; }
   double u0 = e.h(R_CTRL), u1 = e.h(R_CTRL + 1);
-  mpc_update(P, e, y, u0, u1);
+  mpc_update<PF>(P, e, y, u0, u1);
   uout[(size_t)id * NU] = u0; uout[(size_t)id * NU + 1] = u1;
 }
 
 // kernel 2: nsteps of the closed loop (mpc_thrust_strokedev.py:146-199) without leaving the device
+template <bool PF>
 __global__ void __launch_bounds__(128) dt_rollout_kernel(const __grid_constant__ DevPar P, double* __restrict__ slab, int rows, int nenv,
                                                          int nsteps) {
   const int id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(128) dt_rollout_kernel(const __grid_constant__
 #pragma unroll
   for (int i = 0; i < NX; ++i) y[i] = e.h(R_Y + i);
   double u0 = e.h(R_CTRL), u1 = e.h(R_CTRL + 1);
-  mpc_run<true>(P, e, y, u0, u1, nsteps);
+  mpc_run<true, PF>(P, e, y, u0, u1, nsteps);
 #pragma unroll
   for (int i = 0; i < NX; ++i) e.h(R_Y + i) = y[i];
 }
@@ -141,6 +143,8 @@ struct DtBatch {
   size_t big_doubles = 0;
   double* d_cnt = nullptr;
 };
+
+static bool dt_prefetch(const DtBatch* b);
 
 static int dt_err(const char* what, cudaError_t e) {
   char buf[256];
@@ -287,7 +291,8 @@ extern "C" int dtBatchUpdate(DtBatch* b, const double* x0, double* u) {
   double* d_u = b->d_io + (size_t)NX * b->Bp;
   DCK(cudaMemcpyAsync(d_x0, x0, (size_t)b->B * NX * sizeof(double), cudaMemcpyHostToDevice, b->stream));
   DCK(cudaEventRecord(b->ev0, b->stream));
-  dt_update_kernel<<<(b->B + 127) / 128, 128, 0, b->stream>>>(b->dp, b->slab, b->rows, b->B, d_x0, d_u);
+  if (dt_prefetch(b)) dt_update_kernel<true><<<(b->B + 127) / 128, 128, 0, b->stream>>>(b->dp, b->slab, b->rows, b->B, d_x0, d_u);
+  else dt_update_kernel<false><<<(b->B + 127) / 128, 128, 0, b->stream>>>(b->dp, b->slab, b->rows, b->B, d_x0, d_u);
   DCK(cudaGetLastError());
   DCK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;
@@ -300,6 +305,12 @@ extern "C" int dtBatchUpdate(DtBatch* b, const double* x0, double* u) {
 // the resident threads per SM (the kernel uses no shared memory).  Fewer resident environments = a smaller working set
 // per ADMM iteration; once it fits the 126 MB L2 the iteration stops paying HBM for its second sweep.
 // Tuning knobs DT_TPB / DT_SMEM_KB override the per-horizon default.
+// next-knot L2 prefetch (dirtran_core.cuh prefetch_knot): on for horizons above 5 (measured: N = 3, 5 lose, N >= 10 gain 13 %); DT_PREFETCH=0/1 overrides
+static bool dt_prefetch(const DtBatch* b) {
+  const char* e = getenv("DT_PREFETCH");
+  return e ? atoi(e) != 0 : b->par.N > 5;
+}
+
 static void dt_launch_shape(const DtBatch* b, int* tpb, int* smem) {
   *tpb = 128; *smem = 0;
   const char* e = getenv("DT_TPB");
@@ -313,9 +324,12 @@ extern "C" int dtBatchRollout(DtBatch* b, int nsteps) {
   DCK(cudaSetDevice(b->device));
   int tpb, smem;
   dt_launch_shape(b, &tpb, &smem);
-  if (smem > 48 * 1024) DCK(cudaFuncSetAttribute(dt_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const bool pf = dt_prefetch(b);
+  if (smem > 48 * 1024)
+    DCK(cudaFuncSetAttribute(pf ? dt_rollout_kernel<true> : dt_rollout_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   DCK(cudaEventRecord(b->ev0, b->stream));
-  dt_rollout_kernel<<<(b->B + tpb - 1) / tpb, tpb, smem, b->stream>>>(b->dp, b->slab, b->rows, b->B, nsteps);
+  if (pf) dt_rollout_kernel<true><<<(b->B + tpb - 1) / tpb, tpb, smem, b->stream>>>(b->dp, b->slab, b->rows, b->B, nsteps);
+  else dt_rollout_kernel<false><<<(b->B + tpb - 1) / tpb, tpb, smem, b->stream>>>(b->dp, b->slab, b->rows, b->B, nsteps);
   DCK(cudaGetLastError());
   DCK(cudaEventRecord(b->ev1, b->stream));
   b->timed = true;

@@ -12,11 +12,13 @@
 #define DT_FN_NOINLINE __device__ __noinline__
 #define DT_HD __host__ __device__
 #define DT_SINCOS(a, s, c) sincos(a, s, c)
+#define DT_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #else
 #define DT_FN inline
 #define DT_FN_NOINLINE inline
 #define DT_HD
 #define DT_SINCOS(a, s, c) (*(s) = sin(a), *(c) = cos(a))
+#define DT_PREFETCH_L2(p) ((void)(p))
 #endif
 
 namespace dtcore {
@@ -114,7 +116,8 @@ DT_FN void linearise(const DevPar& P, const Env& e, const double (&y)[NX], doubl
   for (int i = 0; i < NX; ++i) e.h(R_LIN + 6 + i) = fd[i];
 }
 
-DT_FN double rho_of_row(const DevPar& P, int j, double rho) { return ((P.loose >> j) & 1u) ? RHO_MIN : rho; }
+DT_FN bool is_loose(const DevPar& P, int j) { return (P.loose >> j) & 1u; }
+DT_FN double rho_of_row(const DevPar& P, int j, double rho) { return is_loose(P, j) ? RHO_MIN : rho; }
 
 // Block Cholesky of H = P + sigma I + A' diag(rho_vec) A in knot order; writes LD_k = chol(S_k) (lower, packed, reciprocal
 // diagonal) of every knot, S_0 = H_00, S_{k+1} = H_{k+1,k+1} - LO_k LO_k'.  The coupling LO_k = H_{k+1,k} L_k^-T
@@ -197,6 +200,19 @@ DT_FN_NOINLINE void factor(const DevPar& P, const Env& e, const Lin& L, double r
   }
 }
 
+// The sweeps are latency-bound once their bytes are down (two warps per scheduler at 255 registers, each knot = loads then
+// a dependent chain of ~300 DFMA): while knot k is being solved, the rows knot k +- 1 will read are requested into L2.
+// One prefetch instruction of a warp covers one 256-byte row.  Compile-time switch (PF): horizons whose resident working
+// set mostly sits in L2 (N = 3, 5) lose 7-15 % to the extra requests, N >= 10 gains 13 % (profiles/r01j_dt_prefetch.txt).
+DT_FN void prefetch_knot(const DevPar& P, const double* kb, bool scratch) {
+#pragma unroll
+  for (int r = 0; r < K_STRIDE; ++r) {
+    if (r >= K_SCR && r < K_LD && !scratch) continue;
+    if (r >= K_ZI && r < K_YE && is_loose(P, (r - K_ZI) % NW)) continue;
+    DT_PREFETCH_L2(kb + r * LANES);
+  }
+}
+
 // forward then backward substitution with one knot's packed Cholesky factor: v <- S^-1 v
 DT_FN void chol_solve(const double (&Lk)[NW * (NW + 1) / 2], double (&v)[NW]) {
 #pragma unroll
@@ -222,6 +238,7 @@ DT_FN void chol_solve(const double (&Lk)[NW * (NW + 1) / 2], double (&v)[NW]) {
 // Per knot and iteration: 36 factor words read per sweep, the 36 iterate words read twice and written once, t written
 // and read once (196 doubles).
 // zd / z0: z of the dynamics / initial-state rows as OSQP holds it on entry (see K_* above).
+template <bool PF>
 DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const double (&fd)[NX],
                                                const double (&y0)[NX], const double (&q)[NX], double rho,
                                                const double (&zd)[NX], const double (&z0)[NX]) {
@@ -240,13 +257,18 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
   for (int k = 0; k <= N; ++k) {
     double* kb = e.knot(k);
     const bool last = (k == N);
+    if (PF && !last) prefetch_knot(P, e.knot(k + 1), false);
     double Lk[NW * (NW + 1) / 2];
 #pragma unroll
     for (int i = 0; i < NW * (NW + 1) / 2; ++i) Lk[i] = kb[(K_LD + i) * LANES];
     double b[NW];
 #pragma unroll
-    for (int j = 0; j < NW; ++j)
-      b[j] = P.sigma * kb[(K_X + j) * LANES] + (rin[j] * kb[(K_ZI + j) * LANES] - kb[(K_YI + j) * LANES]);
+    for (int j = 0; j < NW; ++j) {
+      const double xj = kb[(K_X + j) * LANES];
+      // a bound row without finite bounds ("loose"): z = x and y = 0 exactly, in OSQP's arithmetic too, so neither is stored
+      const double zj = is_loose(P, j) ? xj : kb[(K_ZI + j) * LANES], yj = is_loose(P, j) ? 0.0 : kb[(K_YI + j) * LANES];
+      b[j] = P.sigma * xj + (rin[j] * zj - yj);
+    }
 #pragma unroll
     for (int i = 0; i < NX; ++i) b[i] -= q[i] + te[i];
     if (!last) {
@@ -274,6 +296,7 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
   for (int k = N; k >= 0; --k) {
     double* kb = e.knot(k);
     const bool last = (k == N);
+    if (PF && k > 0) prefetch_knot(P, e.knot(k - 1), true);
     double xt[NW];
 #pragma unroll
     for (int j = 0; j < NW; ++j) xt[j] = kb[(K_SCR + j) * LANES];
@@ -307,13 +330,16 @@ DT_FN void admm_iteration(const DevPar& P, const Env& e, const Lin& L, const dou
     // bound rows of this knot (z~ = x~) and the x update
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
-      const double xp = kb[(K_X + j) * LANES], zp = kb[(K_ZI + j) * LANES], yp = kb[(K_YI + j) * LANES];
+      const bool lj = is_loose(P, j);
+      const double xp = kb[(K_X + j) * LANES];
+      const double zp = lj ? xp : kb[(K_ZI + j) * LANES], yp = lj ? 0.0 : kb[(K_YI + j) * LANES];
       const double v = alpha * xt[j] + oma * zp;
       double zn = fmin(fmax(v + rin_inv[j] * yp, P.lo[j]), P.hi[j]);
       double xv = alpha * xt[j] + oma * xp;
       double yn = yp + rin[j] * (v - zn);
       if (last && j >= NX) { zn = 0.0; xv = 0.0; yn = 0.0; }
-      kb[(K_X + j) * LANES] = xv; kb[(K_ZI + j) * LANES] = zn; kb[(K_YI + j) * LANES] = yn;
+      kb[(K_X + j) * LANES] = xv;
+      if (!lj) { kb[(K_ZI + j) * LANES] = zn; kb[(K_YI + j) * LANES] = yn; }
     }
 #pragma unroll
     for (int i = 0; i < NX; ++i) xn[i] = xt[i];
@@ -349,8 +375,8 @@ DT_FN Resid residuals(const DevPar& P, const Env& e, const Lin& L, const double 
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
       x[j] = kb[(K_X + j) * LANES];
-      const double zi = kb[(K_ZI + j) * LANES];
-      aty[j] = kb[(K_YI + j) * LANES];
+      const double zi = is_loose(P, j) ? x[j] : kb[(K_ZI + j) * LANES];
+      aty[j] = is_loose(P, j) ? 0.0 : kb[(K_YI + j) * LANES];
       if (!(last && j >= NX)) { pri = fmax(pri, fabs(x[j] - zi)); nz = fmax(nz, fabs(zi)); nAx = fmax(nAx, fabs(x[j])); }
     }
 #pragma unroll
@@ -393,7 +419,7 @@ DT_FN bool converged(const DevPar& P, const Resid& r, double f) {
 // slowest lane of its warp is done.  Solves end and rho adapts only at trips that are multiples of check_termination /
 // adaptive_rho_interval, so the lanes of a warp keep taking the residual branch together however far apart their step
 // counters drift.  Returns the last u_0 in (u0, u1), the plant state in y.
-template <bool PLANT>
+template <bool PLANT, bool PF = false>
 DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, double& u1, int nsteps_uniform) {
   if (nsteps_uniform <= 0) return;
   // The per-lane step budget goes through the environment's header (volatile read-back).  Kept in a plain local
@@ -418,7 +444,7 @@ DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, d
   int iter = lane_zero, rho_updates = lane_zero;
   while (true) {
     ++iter;
-    admm_iteration(P, e, L, fd, y0, q, rho, zd, z0);
+    admm_iteration<PF>(P, e, L, fd, y0, q, rho, zd, z0);
 #pragma unroll
     for (int i = 0; i < NX; ++i) { zd[i] = -fd[i]; z0[i] = -y0[i]; }
     const bool at_max = iter >= P.max_iter;
@@ -471,11 +497,12 @@ DT_FN void mpc_run(const DevPar& P, const Env& e, double (&y)[NX], double& u0, d
 }
 
 // one LTVMPC.update for this thread's environment; returns u_0 in (u0, u1) and updates ctrl
+template <bool PF = false>
 DT_FN void mpc_update(const DevPar& P, const Env& e, const double (&y)[NX], double& u0, double& u1) {
   double yy[NX];
 #pragma unroll
   for (int i = 0; i < NX; ++i) yy[i] = y[i];
-  mpc_run<false>(P, e, yy, u0, u1, 1);
+  mpc_run<false, PF>(P, e, yy, u0, u1, 1);
 }
 
 
