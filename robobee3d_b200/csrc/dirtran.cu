@@ -36,6 +36,10 @@ void umpc_internal_set_error(const char* msg);  // umpc_kernels.cu (thread-local
 
 using namespace dtcore;
 
+#ifndef DT_ROLLOUT_MIN_BLOCKS
+#define DT_ROLLOUT_MIN_BLOCKS 2   // 255 registers; 3 (168 registers, ~1 KB of spills per thread) measured 1.5x slower: profiles/r01j_dt_min_blocks3.txt
+#endif
+
 namespace {
 
 __device__ __forceinline__ Env env_of(double* slab, int rows, int e) {
@@ -61,7 +65,7 @@ __global__ void __launch_bounds__(128) dt_update_kernel(const __grid_constant__ 
 
 // kernel 2: nsteps of the closed loop (mpc_thrust_strokedev.py:146-199) without leaving the device
 template <bool PF>
-__global__ void __launch_bounds__(128) dt_rollout_kernel(const __grid_constant__ DevPar P, double* __restrict__ slab, int rows, int nenv,
+__global__ void __launch_bounds__(128, DT_ROLLOUT_MIN_BLOCKS) dt_rollout_kernel(const __grid_constant__ DevPar P, double* __restrict__ slab, int rows, int nenv,
                                                          int nsteps) {
   const int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= nenv) return;
