@@ -108,6 +108,22 @@ void wlControllerUpdateW(float *u, float *w0, const float *u0init, const float *
 /* forget the global WLQP state (tests; the reference needs a fresh process for that) */
 void wlControllerReset(void);
 
+/* The WLQP object itself (wlcontroller/c/wlqp.h:21-31), same struct fields and order.  The reference's wlqpUpdate
+ * calls the application's wrenchMap / wrenchJacMap (wlqp.h:18-19); host callbacks cannot run on the device, so the
+ * quadratic wrench model popts[90] is installed with wlqpSetWrenchModel (or by the first wlControllerUpdate). */
+typedef struct {
+  float umin[NDELU], umax[NDELU], U0[NDELU];
+  float w0[6];
+  float Q[6 * 6];
+} WLQP_t;
+void wlqpInit(WLQP_t *wlqp, float controlRate);
+void wlqpUpdate(WLQP_t *wlqp, float *u, const float *u0, const float *h0, const float *pdotdes);
+void wlqpSetWrenchModel(const float popts[/* 90 */]);
+/* scalar quadratic model (uprightmpc2/funapprox.h:31-35 == wlcontroller/c/funapprox.h:31-35); F and Df evaluate on the device */
+void funApproxInit(FunApprox_t *fa, const float popts[/* 15 */]);
+float funApproxF(const FunApprox_t *fa, const float *xi);
+void funApproxDf(float *Df, const FunApprox_t *fa, const float *xi);
+
 /* ---- (2) batched API -------------------------------------------------------------------- */
 #define UMPC_OK 0
 #define UMPC_ERR_CUDA 100   /* no device / CUDA runtime error: message via umpcLastError() */
@@ -159,9 +175,15 @@ int umpcBatchUpdate(UmpcBatch *b, float *uquad, float *accdes, const float *p0, 
 int umpcBatchEnvStep(UmpcBatch *b, float *uquad, float *accdes, float *p_next, float *R_next, float *dq_next,
                      const float *p0, const float *R0, const float *dq0, const float *pdes, const float *dpdes,
                      const float *sdes, const float *actualT0);
-/* same with DEVICE pointers in the same [B][k] layout, asynchronous on the batch's stream */
+/* same with DEVICE pointers in the same [B][k] layout (arrays of exactly B rows: padded lanes never touch them),
+ * asynchronous on the batch's PRIVATE stream: the caller orders it against its own work (umpcBatchSync, or the
+ * "stream" handle of umpcBatchDevPtr) */
 int umpcBatchUpdateDev(UmpcBatch *b, float *uquad, float *accdes, const float *p0, const float *R0, const float *dq0,
                        const float *pdes, const float *dpdes, const float *sdes, const float *actualT0);
+/* same, ordered against `caller_stream` (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream): the update
+ * starts after everything already queued there and later work there sees its outputs; no host synchronisation */
+int umpcBatchUpdateDevOn(UmpcBatch *b, void *caller_stream, float *uquad, float *accdes, const float *p0, const float *R0,
+                         const float *dq0, const float *pdes, const float *dpdes, const float *sdes, const float *actualT0);
 /* per-environment solver diagnostics of the last update: host arrays, any may be NULL.
  * info[B][4] = iter, status_val, pri_res, dua_res; x[B][45], y[B][39] = OSQP solution;
  * xs[B][45], zs[B][39], ys[B][39] = scaled warm-start iterates; D[B][45], E[B][39] */

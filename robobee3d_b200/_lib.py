@@ -51,12 +51,18 @@ class WLCon_t(C.Structure):
                 ("Qw", C.c_float * 36), ("fa", FunApprox_t * 6)]
 
 
+class WLQP_t(C.Structure):  # wlcontroller/c/wlqp.h:21-25
+    _fields_ = [("umin", C.c_float * 4), ("umax", C.c_float * 4), ("U0", C.c_float * 4), ("w0", C.c_float * 6),
+                ("Q", C.c_float * 36)]
+
+
 # every symbol include/umpc_b200.h declares (tests check the .so exports all of them)
 EXPORTS = [
     "umpcInit", "umpcUpdate", "umpcS", "umpcGetInfo", "umpcGetSolution", "umpcFree",
     "wlConInit", "wlConUpdate", "wlconS", "wlControllerUpdate", "wlControllerUpdateW", "wlControllerReset",
+    "wlqpInit", "wlqpUpdate", "wlqpSetWrenchModel", "funApproxInit", "funApproxF", "funApproxDf",
     "umpcBatchDefaults", "umpcLastError", "umpcBatchCreate", "umpcBatchDestroy", "umpcBatchSize", "umpcBatchReset",
-    "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
+    "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchUpdateDevOn", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
     "umpcBatchGetState", "umpcBatchRollout", "umpcBatchGetMetrics", "umpcBatchReduceMetrics", "umpcBatchSetLog",
     "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchSetWeights", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch",
     "umpcMeasureFp32Peak",
@@ -83,6 +89,7 @@ def load():
     vp = C.c_void_p
     L.umpcBatchUpdate.argtypes = [vp] + [vp] * 9
     L.umpcBatchUpdateDev.argtypes = [vp] + [vp] * 9
+    L.umpcBatchUpdateDevOn.argtypes = [vp, vp] + [vp] * 9
     L.umpcBatchEnvStep.argtypes = [vp] + [vp] * 12
     L.umpcBatchGetSolve.argtypes = [vp] + [vp] * 8
     L.umpcBatchGetQPData.argtypes = [vp, vp]
@@ -128,6 +135,18 @@ def load():
     L.wlControllerUpdateW.argtypes = [FP] * 6 + [f]
     L.wlControllerUpdateW.restype = None
     L.wlControllerReset.restype = None
+    L.wlqpInit.argtypes = [C.POINTER(WLQP_t), f]
+    L.wlqpInit.restype = None
+    L.wlqpUpdate.argtypes = [C.POINTER(WLQP_t)] + [FP] * 4
+    L.wlqpUpdate.restype = None
+    L.wlqpSetWrenchModel.argtypes = [FP]
+    L.wlqpSetWrenchModel.restype = None
+    L.funApproxInit.argtypes = [C.POINTER(FunApprox_t), FP]
+    L.funApproxInit.restype = None
+    L.funApproxF.argtypes = [C.POINTER(FunApprox_t), FP]
+    L.funApproxF.restype = f
+    L.funApproxDf.argtypes = [FP, C.POINTER(FunApprox_t), FP]
+    L.funApproxDf.restype = None
     _lib = L
     return L
 

@@ -132,11 +132,22 @@ class BatchUMPC:
         _lib.check(self.lib.umpcBatchEnvStep(self.h, ptr(uquad), ptr(accdes), ptr(p), ptr(Rc), ptr(dq), ptr(p), ptr(Rc), ptr(dq),
                                              ptr(pdes), ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchEnvStep")
 
-    def update_dev(self, uquad, accdes, p0, R0c, dq0, pdes, dpdes, sdes, actualT0=None):
-        """torch CUDA tensors (float32, contiguous, [B,k]); asynchronous on the batch's stream."""
+    def update_dev(self, uquad, accdes, p0, R0c, dq0, pdes, dpdes, sdes, actualT0=None, stream="current"):
+        """torch CUDA tensors (float32, contiguous, [B,k] -- exactly B rows, no padding needed).  Ordering contract:
+        the launch goes to the batch's private stream, hand-shaken with `stream` by events (no host sync): it starts after
+        everything already queued on `stream`, and work queued on `stream` afterwards sees its outputs.
+        stream="current" (default): torch.cuda.current_stream() of the batch's device; an int / cudaStream_t handle:
+        that stream; None: no hand-shake (the caller synchronises, e.g. with sync())."""
         ptr = lambda a: None if a is None else C.c_void_p(a.data_ptr())
-        _lib.check(self.lib.umpcBatchUpdateDev(self.h, ptr(uquad), ptr(accdes), ptr(p0), ptr(R0c), ptr(dq0), ptr(pdes),
-                                               ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchUpdateDev")
+        if isinstance(stream, str) and stream == "current":
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        if stream is None:
+            _lib.check(self.lib.umpcBatchUpdateDev(self.h, ptr(uquad), ptr(accdes), ptr(p0), ptr(R0c), ptr(dq0), ptr(pdes),
+                                                   ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchUpdateDev")
+        else:
+            _lib.check(self.lib.umpcBatchUpdateDevOn(self.h, C.c_void_p(int(stream)), ptr(uquad), ptr(accdes), ptr(p0), ptr(R0c),
+                                                     ptr(dq0), ptr(pdes), ptr(dpdes), ptr(sdes), ptr(actualT0)), "umpcBatchUpdateDevOn")
 
     def solve_info(self, full=False):
         B = self.B

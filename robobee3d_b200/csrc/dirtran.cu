@@ -12,13 +12,16 @@
 //  * x = (y_0..y_N, u_0..u_{N-1}) is re-ordered by knot, w_k = (y_k, u_k): the reduced ADMM system
 //    H = P + sigma I + A' diag(rho) A is then block tridiagonal with 8x8 blocks (A = [dynamics; I], so the inequality
 //    rows only add to H's diagonal and z~ = A x~ needs no second solve).  A block Cholesky of H replaces OSQP's sparse
-//    LDL' of the 3n+.. KKT matrix: (N+1) 8x8 factors + N 6x8 couplings, no fill, no pivoting, no index arrays.
+//    LDL' of the (n+m)^2 KKT matrix: (N+1) 8x8 factors, no fill, no pivoting, no index arrays.  The couplings
+//    H_{k+1,k} S_k^-1 are NOT stored: they are applied as the sparse product with [Ad Bd] (7 entries, registers).
 //  * One ADMM iteration = one forward sweep over the knots (right-hand side + forward substitution) and one backward
 //    sweep (back substitution + z~ = A x~ + the x/z/y updates), each knot's data touched once per sweep.
 //  * All per-environment data (iterates, factor, linearisation) is a tiled struct of arrays double[B/32][rows][32] in HBM:
 //    lane = environment, so every access of a warp is one 256-byte line.  The iteration is HBM/L2-bandwidth bound
-//    (~2.3 KB per knot and iteration against ~0.9 kflop): that is the roofline bench.py reports for it.
-//  * Environments converge independently (own iteration count, own rho); a warp runs until its slowest lane is done.
+//    (608 B of unique data per knot and iteration against ~0.8 kflop): the roofline bench.py reports for it.
+//  * Environments converge independently (own iteration count, own rho).  The rollout is ONE loop over ADMM iterations
+//    (mpc_run): a lane that finishes a solve moves its plant and starts its next MPC period in the same trip instead
+//    of idling until the slowest lane of its warp is done.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -193,6 +196,9 @@ extern "C" int dtBatchReset(DtBatch* b) {
   return dt_fill(b, R_RHO, b->par.rho);
 }
 
+static int dt_create_alloc(DtBatch* b);
+extern "C" int dtBatchDestroy(DtBatch* b);
+
 extern "C" int dtBatchCreate(DtBatch** out, int nenv, int device, const DtParams* par) {
   if (!out || nenv <= 0 || !par) { umpc_internal_set_error("dtBatchCreate: bad argument"); return UMPC_ERR_ARG; }
   *out = nullptr;
@@ -229,6 +235,13 @@ extern "C" int dtBatchCreate(DtBatch** out, int nenv, int device, const DtParams
     if (lo < -OSQP_INFTY * MIN_SCALING && hi > OSQP_INFTY * MIN_SCALING) d.loose |= 1u << j;  // auxil.c set_rho_vec
     if (j < NX) d.wx[j] = par->wx[j]; else d.wu[j - NX] = par->wu[j - NX];
   }
+  const int rc = dt_create_alloc(b);
+  if (rc != UMPC_OK) { dtBatchDestroy(b); return rc; }  // a failed create leaves nothing allocated
+  *out = b;
+  return UMPC_OK;
+}
+
+static int dt_create_alloc(DtBatch* b) {
   DCK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   DCK(cudaEventCreate(&b->ev0));
   DCK(cudaEventCreate(&b->ev1));
@@ -239,17 +252,18 @@ extern "C" int dtBatchCreate(DtBatch** out, int nenv, int device, const DtParams
   int rc = dtBatchReset(b);
   if (rc != UMPC_OK) return rc;
   DCK(cudaStreamSynchronize(b->stream));
-  *out = b;
   return UMPC_OK;
 }
 
 extern "C" int dtBatchDestroy(DtBatch* b) {
   if (!b) return UMPC_OK;
   cudaSetDevice(b->device);
-  cudaStreamSynchronize(b->stream);
+  if (b->stream) cudaStreamSynchronize(b->stream);
   cudaFree(b->slab); cudaFree(b->d_io); cudaFree(b->d_big); cudaFree(b->d_cnt);
-  cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
-  cudaStreamDestroy(b->stream);
+  if (b->ev0) cudaEventDestroy(b->ev0);
+  if (b->ev1) cudaEventDestroy(b->ev1);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  cudaGetLastError();
   delete b;
   return UMPC_OK;
 }

@@ -24,8 +24,8 @@ enum {
   ROW_D = ROW_YS + 39, ROW_E = ROW_D + 45, ROW_SOLX = ROW_E + 39, ROW_SOLY = ROW_SOLX + 45,             //  warm start, scaling,
   ROW_INFO = ROW_SOLY + 39,                                                                              //  solution, info
   ROW_TASK = ROW_INFO + 4, ROW_TP = ROW_TASK + 1, ROW_PINIT = ROW_TP + 4, ROW_AT0 = ROW_PINIT + 3,      // task / loop
-  ROW_METRICS = ROW_AT0 + 1,
-  ROW_WLU0 = ROW_METRICS + 5, ROW_WLQP = ROW_WLU0 + 4,                                                   // WL stage (25 = WlqpState)
+  ROW_METRICS = ROW_AT0 + 1,  // err, eff (float sums), nsolve, nstep (int32 bit patterns), pert_done, Kahan terms of err, eff
+  ROW_WLU0 = ROW_METRICS + 7, ROW_WLQP = ROW_WLU0 + 4,                                                   // WL stage (25 = WlqpState)
   UMPC_ROWS = ROW_WLQP + 25
 };
 #define ROWF(r) ((r) * 32)  // float offset of row r inside a tile
@@ -152,48 +152,54 @@ umpc_update_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params
   const int e = env0 + blockIdx.x * blockDim.x + threadIdx.x;  // env0: first env of this launch (chunked host-buffer calls)
   __shared__ uint32_t tmem_slot;
   const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);  // every warp of the CTA takes part
-  // No bounds test: B and every launch's env range are multiples of 256, so all threads of the grid own an env slot.
-  // (A thread-dependent branch around the body would also keep ptxas from using the uniform datapath inside it.)
+  // No bounds BRANCH: B and every launch's env range are multiples of 256, so all threads of the grid own an env slot
+  // in the slab (a thread-dependent branch around the body would also keep ptxas from using the uniform datapath
+  // inside it).  The caller's [B][k] arrays, however, hold only the nreal environments it asked for: padded lanes read
+  // the LAST real env's inputs (in bounds, discarded) and their output stores are predicated off.
+  const bool real = e < s.nreal;
+  const size_t ei = (size_t)(real ? e : s.nreal - 1);
   {
   float p[3], R[9], dq[6], pd[3], dpd[3], sd[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    p[i] = p0[(size_t)e * 3 + i]; pd[i] = pdes[(size_t)e * 3 + i];
-    dpd[i] = dpdes[(size_t)e * 3 + i]; sd[i] = sdes[(size_t)e * 3 + i];
+    p[i] = p0[ei * 3 + i]; pd[i] = pdes[ei * 3 + i];
+    dpd[i] = dpdes[ei * 3 + i]; sd[i] = sdes[ei * 3 + i];
   }
 #pragma unroll
-  for (int i = 0; i < 9; ++i) R[i] = R0[(size_t)e * 9 + i];
+  for (int i = 0; i < 9; ++i) R[i] = R0[ei * 9 + i];
 #pragma unroll
-  for (int i = 0; i < 6; ++i) dq[i] = dq0[(size_t)e * 6 + i];
-  const float aT0 = actualT0 ? actualT0[e] : -1.0f;
+  for (int i = 0; i < 6; ++i) dq[i] = dq0[ei * 6 + i];
+  const float aT0 = actualT0 ? actualT0[ei] : -1.0f;
   float* const eb = env_base(s, e);
   SOLVER sol;
   sol.init(scratch_base, s, e);
-  if (want_qpdata) sol.qpdata(kp.mpc, s, e, p, R, dq, pd, dpd, sd, aT0);
+  if (want_qpdata && real) sol.qpdata(kp.mpc, s, e, p, R, dq, pd, dpd, sd, aT0);
   float uq[3], acc[6];
   sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pd, dpd, sd, aT0);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { uquad[(size_t)e * 3 + i] = uq[i]; eb[ROWF(ROW_UQ + i)] = uq[i]; }
+  for (int i = 0; i < 3; ++i) { if (real) uquad[ei * 3 + i] = uq[i]; eb[ROWF(ROW_UQ + i)] = uq[i]; }
 #pragma unroll
-  for (int i = 0; i < 6; ++i) { accdes[(size_t)e * 6 + i] = acc[i]; eb[ROWF(ROW_ACC + i)] = acc[i]; }
+  for (int i = 0; i < 6; ++i) { if (real) accdes[ei * 6 + i] = acc[i]; eb[ROWF(ROW_ACC + i)] = acc[i]; }
   if (p_next) {
     // the two lines of controlTest that follow mdl.update (uprightmpc2.py:148-151): clip, plant step
     // (inputs re-read: they were not kept in registers over the solve)
 #pragma unroll
-    for (int i = 0; i < 3; ++i) p[i] = *(volatile const float*)(p0 + (size_t)e * 3 + i);
+    for (int i = 0; i < 3; ++i) p[i] = *(volatile const float*)(p0 + ei * 3 + i);
 #pragma unroll
-    for (int i = 0; i < 9; ++i) R[i] = *(volatile const float*)(R0 + (size_t)e * 9 + i);
+    for (int i = 0; i < 9; ++i) R[i] = *(volatile const float*)(R0 + ei * 9 + i);
 #pragma unroll
-    for (int i = 0; i < 6; ++i) dq[i] = *(volatile const float*)(dq0 + (size_t)e * 6 + i);
+    for (int i = 0; i < 6; ++i) dq[i] = *(volatile const float*)(dq0 + ei * 6 + i);
     uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
     uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
     sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
+    if (real) {
 #pragma unroll
-    for (int i = 0; i < 3; ++i) p_next[(size_t)e * 3 + i] = p[i];
+      for (int i = 0; i < 3; ++i) p_next[ei * 3 + i] = p[i];
 #pragma unroll
-    for (int i = 0; i < 9; ++i) R_next[(size_t)e * 9 + i] = R[i];
+      for (int i = 0; i < 9; ++i) R_next[ei * 9 + i] = R[i];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) dq_next[(size_t)e * 6 + i] = dq[i];
+      for (int i = 0; i < 6; ++i) dq_next[ei * 6 + i] = dq[i];
+    }
   }
   }
   SOLVER::template release<TPB>(&tmem_slot);
@@ -357,7 +363,11 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
 #pragma unroll
   for (int i = 0; i < 6; ++i) dq[i] = eb[ROWF(ROW_DQ + i)];
   const int task = ((const int*)eb)[ROWF(ROW_TASK)];
-  float err = eb[ROWF(ROW_METRICS + 0)], eff = eb[ROWF(ROW_METRICS + 1)], nsolve = eb[ROWF(ROW_METRICS + 2)], nstep = eb[ROWF(ROW_METRICS + 3)];
+  // logMetric sums (uprightmpc2.py:161-175): float32 with Kahan compensation (a 5,000-step flight adds 5,000 terms of
+  // very different size), solve / step counters as integers
+  float err = eb[ROWF(ROW_METRICS + 0)], eff = eb[ROWF(ROW_METRICS + 1)];
+  float cerr = eb[ROWF(ROW_METRICS + 5)], ceff = eb[ROWF(ROW_METRICS + 6)];
+  int nsolve = ((const int*)eb)[ROWF(ROW_METRICS + 2)], nstep = ((const int*)eb)[ROWF(ROW_METRICS + 3)];
   float pert_done = eb[ROWF(ROW_METRICS + 4)];
   SOLVER sol;
   sol.init(scratch_base, s, e);
@@ -387,7 +397,8 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
       for (int i = 0; i < 9; ++i) eb[ROWF(ROW_R + i)] = R[i];
 #pragma unroll
       for (int i = 0; i < 6; ++i) eb[ROWF(ROW_DQ + i)] = dq[i];
-      eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 2)] = nsolve; eb[ROWF(ROW_METRICS + 3)] = nstep;
+      eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 5)] = cerr; eb[ROWF(ROW_METRICS + 6)] = ceff;
+      ((int*)eb)[ROWF(ROW_METRICS + 2)] = nsolve; ((int*)eb)[ROWF(ROW_METRICS + 3)] = nstep;
       sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0);
 #pragma unroll
       for (int i = 0; i < 6; ++i) eb[ROWF(ROW_ACC + i)] = acc[i];
@@ -398,16 +409,21 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
 #pragma unroll
       for (int i = 0; i < 6; ++i) dq[i] = *(volatile float*)(eb + ROWF(ROW_DQ + i));
       err = *(volatile float*)(eb + ROWF(ROW_METRICS + 0)); eff = *(volatile float*)(eb + ROWF(ROW_METRICS + 1));
-      nsolve = *(volatile float*)(eb + ROWF(ROW_METRICS + 2)); nstep = *(volatile float*)(eb + ROWF(ROW_METRICS + 3));
+      cerr = *(volatile float*)(eb + ROWF(ROW_METRICS + 5)); ceff = *(volatile float*)(eb + ROWF(ROW_METRICS + 6));
+      nsolve = *(volatile int*)((int*)eb + ROWF(ROW_METRICS + 2)); nstep = *(volatile int*)((int*)eb + ROWF(ROW_METRICS + 3));
       if (kp.sim.wl_mode) wl_stage(kp.sim, wlp, eb, R, acc);
-      nsolve += 1.0f;
+      nsolve += 1;
     }
     uq[1] = sim_clip(uq[1], -kp.sim.taulim, kp.sim.taulim);
     uq[2] = sim_clip(uq[2], -kp.sim.taulim, kp.sim.taulim);
     sim_dyn_step(p, R, dq, uq, kp.sim.dtsim, kp.sim.Ib, kp.sim.g);
-    err += p[0] * p[0] + p[1] * p[1] + p[2] * p[2];
-    eff += uq[1] * uq[1] + uq[2] * uq[2];
-    nstep += 1.0f;
+    {
+      const float ye = (p[0] * p[0] + p[1] * p[1] + p[2] * p[2]) - cerr, te = __fadd_rn(err, ye);
+      cerr = __fsub_rn(__fsub_rn(te, err), ye); err = te;
+      const float yf = (uq[1] * uq[1] + uq[2] * uq[2]) - ceff, tf = __fadd_rn(eff, yf);
+      ceff = __fsub_rn(__fsub_rn(tf, eff), yf); eff = tf;
+    }
+    nstep += 1;
     if (e == lg.env && step0 + k < lg.cap) {
       float* y = lg.y + (size_t)(step0 + k) * 12;
       float* u = lg.u + (size_t)(step0 + k) * 3;
@@ -423,7 +439,8 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   for (int i = 0; i < 9; ++i) eb[ROWF(ROW_R + i)] = R[i];
 #pragma unroll
   for (int i = 0; i < 6; ++i) eb[ROWF(ROW_DQ + i)] = dq[i];
-  eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 2)] = nsolve; eb[ROWF(ROW_METRICS + 3)] = nstep;
+  eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 5)] = cerr; eb[ROWF(ROW_METRICS + 6)] = ceff;
+  ((int*)eb)[ROWF(ROW_METRICS + 2)] = nsolve; ((int*)eb)[ROWF(ROW_METRICS + 3)] = nstep;
   eb[ROWF(ROW_METRICS + 4)] = pert_done;
   }
   SOLVER::template release<TPB>(&tmem_slot);

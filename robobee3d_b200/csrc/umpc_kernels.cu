@@ -258,12 +258,12 @@ __global__ void reduce_metrics_kernel(const __grid_constant__ DevState s, double
   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < s.nreal; e += gridDim.x * blockDim.x) {
     const float* eb = env_base(s, e);
     const float err = eb[ROWF(ROW_METRICS + 0)], eff = eb[ROWF(ROW_METRICS + 1)];
-    const float ns = eb[ROWF(ROW_METRICS + 3)];
+    const int ns = ((const int*)eb)[ROWF(ROW_METRICS + 3)];
     bool bad = !(isfinite(err) && isfinite(eff));
 #pragma unroll
     for (int i = 0; i < 3; ++i) bad = bad || !isfinite(eb[ROWF(ROW_P + i)]);
     if (!bad) { a[0] += err; a[1] += eff; a[5] = fmax(a[5], ns > 0 ? (double)err / ns : 0.0); }
-    a[2] += eb[ROWF(ROW_METRICS + 2)]; a[3] += ns; a[4] += bad ? 1.0 : 0.0;
+    a[2] += ((const int*)eb)[ROWF(ROW_METRICS + 2)]; a[3] += ns; a[4] += bad ? 1.0 : 0.0;
   }
 #pragma unroll
   for (int k = 0; k < 6; ++k)
@@ -337,6 +337,7 @@ struct UmpcBatch {
   cudaGraphExec_t g_exec = nullptr;     // captured chunk pipeline of the host-buffer calls + what it was captured for
   std::vector<const void*> g_key;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
+  cudaEvent_t x_ev0 = nullptr, x_ev1 = nullptr;  // hand-shake with a caller's stream (umpcBatchUpdateDevOn)
   bool timed = false;
   UmpcBatchParams bp;
   KernelParams kp;
@@ -357,6 +358,9 @@ struct UmpcBatch {
   double* d_sums = nullptr;
   LogBuf lg{-1, 0, nullptr, nullptr};
   bool have_qpdata = false;
+  // batch-of-1 drop-in (umpcUpdate): one pinned, device-mapped block -- in[28] | out[9] | qp[216][256] -- that the update
+  // kernel reads and writes directly (no staging copies); s.qpdata points into it
+  float *h_single = nullptr, *d_single = nullptr;
 };
 
 extern "C" void umpcBatchDefaults(UmpcBatchParams* p) {
@@ -451,6 +455,9 @@ extern "C" int umpcBatchReset(UmpcBatch* b) {
   return reset_state(b);
 }
 
+static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par);
+extern "C" void umpcBatchDestroy(UmpcBatch* b);
+
 extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const UmpcBatchParams* par) {
   if (!out || nenv <= 0 || !par) { g_err = "umpcBatchCreate: bad argument"; return UMPC_ERR_ARG; }
   *out = nullptr;
@@ -463,6 +470,13 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
   CK(cudaSetDevice(device));
   UmpcBatch* b = new UmpcBatch();
   b->B = nenv; b->Bp = (nenv + 255) & ~255; b->device = device; b->bp = *par;  // Bp: whole CTAs of the largest launch shape
+  const int rc = batch_create_body(b, nenv, par);
+  if (rc) { umpcBatchDestroy(b); return rc; }   // a failed create leaves nothing allocated
+  *out = b;
+  return UMPC_OK;
+}
+
+static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par) {
   fill_kernel_params(b);
   CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&b->ev0));
@@ -496,26 +510,28 @@ extern "C" int umpcBatchCreate(UmpcBatch** out, int nenv, int device, const Umpc
     const int v = atoi(t);
     if (v == 32 || v == 64 || v == 128 || v == 256) b->tpb = v;
   }
-  int rc = reset_state(b);
-  if (rc) return rc;
-  *out = b;
-  return UMPC_OK;
+  return reset_state(b);
 }
 
 extern "C" void umpcBatchDestroy(UmpcBatch* b) {
   if (!b) return;
   cudaSetDevice(b->device);
-  cudaStreamSynchronize(b->stream);
+  if (b->stream) cudaStreamSynchronize(b->stream);
   umpc_conv_destroy(b->conv);
   cudaFree(b->s.wts);
   cudaFree(b->slab); cudaFree(b->d_in); cudaFree(b->d_out); cudaFree(b->d_sums); cudaFree(b->d_next);
-  cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->s.qpdata); cudaFree(b->lg.y); cudaFree(b->lg.u);
-  cudaEventDestroy(b->ev0); cudaEventDestroy(b->ev1);
+  cudaFree(b->d_fire); cudaFree(b->d_t); cudaFree(b->lg.y); cudaFree(b->lg.u);
+  if (b->h_single) cudaFreeHost(b->h_single); else cudaFree(b->s.qpdata);
+  if (b->ev0) cudaEventDestroy(b->ev0);
+  if (b->ev1) cudaEventDestroy(b->ev1);
+  if (b->x_ev0) { cudaEventDestroy(b->x_ev0); cudaEventDestroy(b->x_ev1); }
+  if (b->tev0) { cudaEventDestroy(b->tev0); cudaEventDestroy(b->tev1); }
   if (b->g_exec) cudaGraphExecDestroy(b->g_exec);
   if (b->d_pulled) cudaFree(b->d_pulled);
   for (int i = 0; i < 3; ++i) { if (b->side[i]) cudaStreamDestroy(b->side[i]); if (b->join_ev[i]) cudaEventDestroy(b->join_ev[i]); }
   if (b->side_ev) cudaEventDestroy(b->side_ev);
-  cudaStreamDestroy(b->stream);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  cudaGetLastError();
   delete b;
 }
 
@@ -723,6 +739,28 @@ extern "C" int umpcBatchUpdateDev(UmpcBatch* b, float* uquad, float* accdes, con
   return launch_update(b, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0);
 }
 
+// The same launch ORDERED AGAINST THE CALLER'S STREAM (e.g. torch.cuda.current_stream().cuda_stream): the batch's
+// private stream first waits for everything queued on `caller_stream` (so inputs written by preceding work there are
+// complete), and `caller_stream` then waits for the update (so later work there sees the outputs).  No host sync.
+extern "C" int umpcBatchUpdateDevOn(UmpcBatch* b, void* caller_stream, float* uquad, float* accdes, const float* p0,
+                                    const float* R0, const float* dq0, const float* pdes, const float* dpdes,
+                                    const float* sdes, const float* actualT0) {
+  if (!b) return UMPC_ERR_ARG;
+  CK(cudaSetDevice(b->device));
+  cudaStream_t cs = (cudaStream_t)caller_stream;
+  if (!b->x_ev0) {
+    CK(cudaEventCreateWithFlags(&b->x_ev0, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&b->x_ev1, cudaEventDisableTiming));
+  }
+  CK(cudaEventRecord(b->x_ev0, cs));
+  CK(cudaStreamWaitEvent(b->stream, b->x_ev0, 0));
+  int rc = launch_update(b, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, actualT0);
+  if (rc) return rc;
+  CK(cudaEventRecord(b->x_ev1, b->stream));
+  CK(cudaStreamWaitEvent(cs, b->x_ev1, 0));
+  return UMPC_OK;
+}
+
 extern "C" int umpcBatchUpdate(UmpcBatch* b, float* uquad, float* accdes, const float* p0, const float* R0,
                                const float* dq0, const float* pdes, const float* dpdes, const float* sdes,
                                const float* actualT0) {
@@ -840,7 +878,7 @@ extern "C" int umpcBatchSetState(UmpcBatch* b, const float* p, const float* R, c
   if (tp) { if ((rc = put_rows(b, b->s.tp, 4, tp))) return rc; }
   else if ((rc = fill_rows(b, ROW_TP, 4, 0.0f))) return rc;
   if ((rc = fill_rows(b, ROW_UQ, 3, 0.0f))) return rc;
-  if ((rc = fill_rows(b, ROW_METRICS, 5, 0.0f))) return rc;
+  if ((rc = fill_rows(b, ROW_METRICS, 7, 0.0f))) return rc;
   CK(cudaStreamSynchronize(b->stream));
   b->step = 0; b->thl = 0.0;
   return UMPC_OK;
@@ -936,7 +974,12 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
 extern "C" int umpcBatchGetMetrics(UmpcBatch* b, float* metrics) {
   if (!b || !metrics) return UMPC_ERR_ARG;
   CK(cudaSetDevice(b->device));
-  return get_rows(b, b->s.metrics, 4, metrics);
+  int rc = get_rows(b, b->s.metrics, 4, metrics);
+  if (rc) return rc;
+  // the solve / step counters are int32 on the device (exact beyond 2^24 steps); this call reports them as floats
+  for (int e = 0; e < b->B; ++e)
+    for (int k = 2; k < 4; ++k) { int v; memcpy(&v, &metrics[(size_t)e * 4 + k], 4); metrics[(size_t)e * 4 + k] = (float)v; }
+  return UMPC_OK;
 }
 
 extern "C" int umpcBatchReduceMetrics(UmpcBatch* b, double* sums8) {
@@ -1105,8 +1148,18 @@ extern "C" void umpcInit(UprightMPC_t* up, float dt, float g, float TtoWmax, flo
     fprintf(stderr, "umpcInit (libumpc_b200): %s\n", umpcLastError());
     return;
   }
-  std::vector<float> scratch(216);
-  umpcBatchGetQPData(b, scratch.data());  // switches the QP-data output on
+  // pinned + mapped I/O block: the update kernel reads the 28 inputs from it and writes uquad/accdes and the public QP
+  // vectors (UprightMPC_t.l/u/q/Px_data/Ax_data, uprightmpc2.h:36-40) straight into it
+  const size_t nfl = 28 + 9 + (size_t)216 * b->Bp;
+  if (cudaHostAlloc(&b->h_single, nfl * sizeof(float), cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer((void**)&b->d_single, b->h_single, 0) != cudaSuccess) {
+    fprintf(stderr, "umpcInit (libumpc_b200): pinned I/O block: %s\n", cudaGetErrorString(cudaGetLastError()));
+    umpcBatchDestroy(b);
+    return;
+  }
+  memset(b->h_single, 0, nfl * sizeof(float));
+  b->s.qpdata = b->d_single + 37;
+  b->have_qpdata = true;
   std::lock_guard<std::mutex> lk(g_mu);
   g_single[up] = b;
 }
@@ -1121,15 +1174,37 @@ extern "C" int umpcUpdate(UprightMPC_t* up, float uquad[3], float accdes[6], con
     for (int i = 0; i < 6; ++i) accdes[i] = nanf("");
     return UMPC_ERR_CUDA;
   }
-  // T0 is a public field the caller may have edited between calls (uprightmpc2.h:42)
-  if (cudaMemcpy(b->s.T0, &up->T0, sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) return UMPC_ERR_CUDA;
-  int rc = umpcBatchUpdate(b, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, &actualT0);
+  if (cudaSetDevice(b->device) != cudaSuccess) return UMPC_ERR_CUDA;
+  // The reference re-reads the public fields of *up on every call (updateObjective / umpcUpdateConstraint,
+  // uprightmpc2.c:126-207): a caller may edit weights, dt, Tmax or T0 between calls.
+  UmpcParams& m = b->kp.mpc;
+  m.dt = up->dt; m.g = up->g; m.Tmax = up->Tmax;
+  for (int i = 0; i < 6; ++i) { m.Qyr[i] = up->Qyr[i]; m.Qyf[i] = up->Qyf[i]; m.Qdyr[i] = up->Qdyr[i]; m.Qdyf[i] = up->Qdyf[i]; }
+  for (int i = 0; i < 3; ++i) m.R[i] = up->R[i];
+  m.Ibi[0] = up->e3hIbi[1]; m.Ibi[1] = -up->e3hIbi[3];   // e3h * diag(1/Ib), column-major (uprightmpc2.c:48-55)
+  float* hin = b->h_single;
+  memcpy(hin, p0, 12); memcpy(hin + 3, R0, 36); memcpy(hin + 12, dq0, 24); memcpy(hin + 18, pdes, 12);
+  memcpy(hin + 21, dpdes, 12); memcpy(hin + 24, sdes, 12);
+  // T0: `if (actualT0 >= 0) T0 = actualT0` (uprightmpc2.c:215-216); otherwise the struct's own T0 (a public field the
+  // caller may have edited, uprightmpc2.h:42) -- both reach the kernel through its actualT0 input
+  hin[27] = actualT0 >= 0.0f ? actualT0 : up->T0;
+  if (!(hin[27] >= 0.0f)) {  // negative / NaN T0 cannot travel that way: write the slab row instead
+    if (cudaMemcpy(b->s.T0, &up->T0, sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) return UMPC_ERR_CUDA;
+    hin[27] = -1.0f;
+  }
+  const float* d = b->d_single;
+  float* dout = b->d_single + 28;
+  int rc = launch_update(b, dout, dout + 3, d, d + 3, d + 12, d + 18, d + 21, d + 24, d + 27, nullptr, nullptr, nullptr, 0, 128);
+  if (!rc && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = set_err("umpcUpdate", cudaGetLastError());
   if (rc) { fprintf(stderr, "umpcUpdate (libumpc_b200): %s\n", umpcLastError()); return rc; }
-  float qp[216];
-  umpcBatchGetQPData(b, qp);
-  memcpy(up->l, qp, sizeof(up->l)); memcpy(up->u, qp + 39, sizeof(up->u)); memcpy(up->q, qp + 78, sizeof(up->q));
-  memcpy(up->Px_data, qp + 123, sizeof(up->Px_data)); memcpy(up->Ax_data, qp + 168, sizeof(up->Ax_data));
-  cudaMemcpy(&up->T0, b->s.T0, sizeof(float), cudaMemcpyDeviceToHost);
+  const float* ho = b->h_single + 28;
+  memcpy(uquad, ho, 12); memcpy(accdes, ho + 3, 24);
+  const float* qp = b->h_single + 37;  // [216][Bp] rows, env 0
+  const size_t P = b->Bp;
+  for (int i = 0; i < 39; ++i) { up->l[i] = qp[(size_t)i * P]; up->u[i] = qp[(size_t)(39 + i) * P]; }
+  for (int i = 0; i < 45; ++i) { up->q[i] = qp[(size_t)(78 + i) * P]; up->Px_data[i] = qp[(size_t)(123 + i) * P]; }
+  for (int i = 0; i < 48; ++i) up->Ax_data[i] = qp[(size_t)(168 + i) * P];
+  up->T0 = uquad[0];  // T0 += dT; uquad[0] = T0 (uprightmpc2.c:253-257)
   return 0;
 }
 
@@ -1261,6 +1336,7 @@ static float g_u0[4] = {-1.0f, 0.0f, 0.0f, 0.0f};
 static WlqpState g_wlqp_state;
 static WlParams g_wlqp_par;
 static int g_wlqp_check = 25;
+static int g_wlqp_have_model = 0;
 
 extern "C" void wlControllerReset(void) { g_u0[0] = -1.0f; g_u0[1] = g_u0[2] = g_u0[3] = 0.0f; }
 extern "C" void wlControllerSetCheckTermination(int k) { g_wlqp_check = k; }
@@ -1277,6 +1353,7 @@ extern "C" void wlControllerUpdateW(float* u, float* w0, const float* u0init, co
     tmp.bp.wlqpCheckTermination = g_wlqp_check;
     fill_kernel_params(&tmp);
     g_wlqp_par = tmp.wlp;
+    g_wlqp_have_model = 1;
     wlqp_state_init(g_wlqp_state);
     for (int i = 0; i < 4; ++i) g_u0[i] = u0init[i];
   }
@@ -1292,4 +1369,85 @@ extern "C" void wlControllerUpdateW(float* u, float* w0, const float* u0init, co
 extern "C" void wlControllerUpdate(float* u, const float* u0init, const float* h0, const float* pdotdes, const float* popts,
                                    float controlRate) {
   wlControllerUpdateW(u, nullptr, u0init, h0, pdotdes, popts, controlRate);
+}
+
+// ---- wlqpInit / wlqpUpdate (wlcontroller/c/wlqp.h:21-31) and funApproxInit/F/Df (uprightmpc2/funapprox.h:31-35) ----
+// A C caller that links the reference's WLQP object directly binds these.  The reference's wlqpUpdate calls the
+// application-provided wrenchMap / wrenchJacMap (wlqp.h:18-19; wlcontroller.c defines them from its global fa[]):
+// host callbacks cannot run on the device, so the quadratic wrench model (popts[90]) is the one installed by
+// wlqpSetWrenchModel, or by the first wlControllerUpdate of the process (wlcontroller.c:21-33).  The OSQP warm start
+// is process-global like the reference's generated workspace (wlqp/workspace.c).
+extern "C" void wlqpSetWrenchModel(const float popts[90]) {
+  memcpy(g_wlqp_par.popts, popts, sizeof(g_wlqp_par.popts));
+  g_wlqp_have_model = 1;
+}
+
+extern "C" void wlqpInit(WLQP_t* wlqp, float controlRate) {
+  memset(wlqp, 0, sizeof(*wlqp));
+  for (int i = 0; i < 6; ++i) wlqp->Q[i + 6 * i] = i < 3 ? 1.0f : 0.1f;   // wlqp.c:19-24
+  const float umin[4] = {90.0f, -0.5f, -0.2f, -0.1f}, umax[4] = {240.0f, 0.5f, 0.2f, 0.1f};
+  const float dumax[4] = {5.0e3f, 10.0f, 10.0f, 10.0f};                  // wlqp.c:27-41
+  for (int i = 0; i < 4; ++i) { wlqp->umin[i] = umin[i]; wlqp->umax[i] = umax[i]; wlqp->U0[i] = dumax[i] / controlRate; }
+  wlqp_state_init(g_wlqp_state);  // osqp_set_default_settings + max_iter 40 on the global workspace (wlqp.c:43-46)
+}
+
+extern "C" void wlqpUpdate(WLQP_t* wlqp, float* u, const float* u0, const float* h0, const float* pdotdes) {
+  WlParams wp = g_wlqp_par;  // popts of the installed wrench model
+  for (int i = 0; i < 4; ++i) { wp.umin[i] = wlqp->umin[i]; wp.umax[i] = wlqp->umax[i]; wp.dumax[i] = wlqp->U0[i]; }
+  for (int i = 0; i < 6; ++i) wp.Qw[i] = wlqp->Q[i + 6 * i];
+  wp.rho = 0.1f; wp.sigma = 1e-6f; wp.alpha = 1.6f; wp.eps_abs = 1e-3f; wp.eps_rel = 1e-3f;
+  wp.max_iter = 40; wp.check_termination = g_wlqp_check; wp.scaling_iters = 10;
+  float uu[4] = {u0[0], u0[1], u0[2], u0[3]};
+  if (!g_wlqp_have_model || wl_single(wp, 2, uu, &g_wlqp_state, h0, pdotdes, wlqp->w0) != UMPC_OK) {
+    if (!g_wlqp_have_model) fprintf(stderr, "wlqpUpdate (libumpc_b200): no wrench model -- call wlqpSetWrenchModel(popts) first\n");
+    for (int i = 0; i < 4; ++i) u[i] = nanf("");
+    return;
+  }
+  for (int i = 0; i < 4; ++i) u[i] = uu[i];
+}
+
+extern "C" void funApproxInit(FunApprox_t* fa, const float popts[/* 15 */]) {
+  fa->k = NDELU; fa->a0 = popts[0];
+  for (int r = 0; r < NDELU; ++r) fa->a1[r] = popts[1 + r];
+  int kk = 1 + NDELU;
+  for (int r = 0; r < NDELU; ++r)
+    for (int c = r; c < NDELU; ++c) fa->A2[r + NDELU * c] = fa->A2[c + NDELU * r] = popts[kk++];
+}
+
+// one quadratic model evaluated on the device (the library has no host arithmetic path): out5 = f, df[4]
+__global__ void funapprox_kernel(FunApprox_t fa, const float* __restrict__ xi, float* __restrict__ out5) {
+  if (threadIdx.x || blockIdx.x) return;
+  float x[4], Ax[4], f = fa.a0, quad = 0.0f;
+  for (int i = 0; i < 4; ++i) x[i] = xi[i];
+  for (int r = 0; r < 4; ++r) {
+    float acc = 0.0f;
+    for (int c = 0; c < 4; ++c) acc += fa.A2[r + 4 * c] * x[c];
+    Ax[r] = acc;
+    f += x[r] * fa.a1[r];
+  }
+  for (int r = 0; r < 4; ++r) { quad += x[r] * Ax[r]; out5[1 + r] = fa.a1[r] + Ax[r]; }
+  out5[0] = f + 0.5f * quad;
+}
+
+static int funapprox_eval(const FunApprox_t* fa, const float* xi, float out5[5]) {
+  static float* d = nullptr;  // 4 in + 5 out
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!d) CK(cudaMalloc(&d, 9 * sizeof(float)));
+  CK(cudaMemcpy(d, xi, 4 * sizeof(float), cudaMemcpyHostToDevice));
+  funapprox_kernel<<<1, 32>>>(*fa, d, d + 4);
+  CK(cudaGetLastError());
+  CK(cudaMemcpy(out5, d + 4, 5 * sizeof(float), cudaMemcpyDeviceToHost));
+  return UMPC_OK;
+}
+
+extern "C" float funApproxF(const FunApprox_t* fa, const float* xi) {
+  float o[5];
+  if (funapprox_eval(fa, xi, o) != UMPC_OK) { fprintf(stderr, "funApproxF (libumpc_b200): %s\n", umpcLastError()); return nanf(""); }
+  return o[0];
+}
+
+extern "C" void funApproxDf(float* Df, const FunApprox_t* fa, const float* xi) {
+  float o[5];
+  if (funapprox_eval(fa, xi, o) != UMPC_OK) { fprintf(stderr, "funApproxDf (libumpc_b200): %s\n", umpcLastError()); for (int i = 0; i < 4; ++i) Df[i] = nanf(""); return; }
+  for (int i = 0; i < 4; ++i) Df[i] = o[1 + i];
 }
