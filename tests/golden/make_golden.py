@@ -9,6 +9,7 @@ Outputs (small, committed):
     umpc_conv.npz    the same QPs solved by the reference's vendored OSQP built in float64 and run to
                      convergence with the Python path's settings (flavour B, libref_umpc_f64.so)
     rollout_c1.npz   config 1: controlTest hover flight, reference C controller + double plant
+    cascade_wlqp.npz config 4 with the true WLQP: reference umpcUpdate -> reference wlControllerUpdate -> actualT0 feedback
     wl_seq.npz       WLCon (uprightmpc2/funapprox.c) and true WLQP (wlcontroller/c) on the scripted demand of
                      template/wlcontroller/testwlqppy.py:15-40, plus the cascade of config 4
 The GPU box has no /root/reference: tests only read these files.
@@ -156,6 +157,56 @@ def wl_seq(c):
     np.savez_compressed(os.path.join(HERE, "wl_seq.npz"), **res)
 
 
+def cascade_wlqp(c):
+    """config 4 with the TRUE WLQP: the loop of robobee_test_controllers.py:162-171 --
+    umpcUpdate (reference C, libref_umpc_f32.so) -> h0 = [R'(0,0,mb g);0], pdotdes = M0 accdes -> wlControllerUpdate
+    (reference C, libref_wlqp_f32.so: wlcontroller/c + its own OSQP workspace) -> actualT0 = w0[2]/mb fed back,
+    w0 = wlqp.w0 = w(u0 before the step) (wlqp.c:87) -- around the double plant of the oracle (quadrotorNLDyn).
+    The two reference libraries each carry their own global `workspace`, so the loop runs here in Python."""
+    import ctypes as C
+    mb, g, Ib = 100.0, 9.81e-3, np.array([3333.0, 3333.0, 1000.0])
+    res = {}
+    for name, hl, tend, task, tp in (("hover", 1.0, 200.0, B.TASK_HELIX, (0.0, 0.0, 0.1, 0.0)),
+                                     ("helix", 5.0, 300.0, B.TASK_HELIX, (50.0, 1.0, 0.1, 1.0))):
+        ref = B.RefUMPC()
+        wl = B.RefWLQP(c["popts_waypoint"])
+        w0v = (C.c_float * 58).in_dll(wl.lib, "wlqp")      # WLQP_t: umin[4] umax[4] U0[4] w0[6] Q[36] (wlqp.h:21-25)
+        orc = C.CDLL(os.path.join(ROOT, "oracle", "liboracle_f64.so"))
+        orc.orc_dyn_step.argtypes = [B.DP, B.DP, B.DP, B.DP, C.c_double, B.DP, C.c_double]
+        orc.orc_task_q.argtypes = [C.c_int, C.c_double, B.DP, B.DP, C.c_int, B.DP, B.DP, B.DP]
+        p, R, dq = B.control_test_ic()
+        p = p.copy(); Rc = np.ascontiguousarray(R.T).ravel().copy(); dq = dq.copy()   # column-major R
+        pinit = p.copy()
+        nt = int(np.ceil(tend / 0.2))
+        uq = np.zeros(3); aT0 = -1.0; thl = 0.0; nsolve = 0
+        Y = np.zeros((nt, 12)); U = np.zeros((nt, 3)); U4 = []
+        err = eff = 0.0
+        tpa = np.asarray(tp, float)
+        for ti in range(nt):
+            t = ti * 0.2
+            if t - thl > hl:
+                pdes, dpdes, sdes = np.zeros(3), np.zeros(3), np.zeros(3)
+                orc.orc_task_q(int(task), t, B._p(pinit), B._p(tpa), 0, B._p(pdes), B._p(dpdes), B._p(sdes))
+                Rm = Rc.reshape(3, 3).T
+                uqn, acc = ref.update(p, Rm, dq, pdes, dpdes, sdes, aT0)
+                h0 = np.r_[Rm.T @ np.array([0, 0, mb * g]), 0, 0, 0]
+                pdd = np.r_[mb * acc[:3], Ib * acc[3:]]
+                u4 = wl.update(h0, pdd)
+                aT0 = float(w0v[14]) / mb                                  # w0[2] / mb
+                U4.append(np.r_[u4, [w0v[12 + i] for i in range(6)]])
+                uq = uqn.copy(); thl = t; nsolve += 1
+            uq[1:] = np.clip(uq[1:], -100.0, 100.0)
+            orc.orc_dyn_step(B._p(p), B._p(Rc), B._p(dq), B._p(uq), 0.2, B._p(Ib), g)
+            Y[ti, :3] = p; Y[ti, 3:6] = Rc[6:9]; Y[ti, 6:] = dq; U[ti] = uq
+            err += p @ p; eff += uq[1] ** 2 + uq[2] ** 2
+        res[name + "_y"] = Y[::10].astype(np.float32)
+        res[name + "_u"] = U[::10].astype(np.float32)
+        res[name + "_u4w0"] = np.array(U4, np.float32)
+        res[name + "_metrics"] = np.array([err / nt, eff / nt, nsolve])
+        res[name + "_cfg"] = np.array([hl, tend, task] + list(tp))
+    np.savez_compressed(os.path.join(HERE, "cascade_wlqp.npz"), **res)
+
+
 if __name__ == "__main__":
     B.build(ref=True)
     assert B.have_ref(), "oracle/_ref not built (needs /root/reference)"
@@ -163,5 +214,6 @@ if __name__ == "__main__":
     umpc_seq()
     rollout_c1()
     wl_seq(c)
+    cascade_wlqp(c)
     for f in sorted(os.listdir(HERE)):
         print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -172,3 +172,112 @@ def test_host_buffer_calls_pinned_paths_equal_pageable_path(cuda_required, zeroc
             bd.update_raw(np_p, np_R, np_dq, z3, z3, e3, a_np, np_uq, np_acc)
             assert np.array_equal(uq2.numpy(), np_uq) and np.array_equal(acc2.numpy(), np_acc)
         bg.close(); bd.close()
+
+
+@pytest.mark.parametrize("B", [130, 4097])
+def test_update_dev_ragged_batch_stays_in_bounds(cuda_required, B):
+    """umpcBatchUpdateDev on device arrays of EXACTLY B rows (B not a multiple of 256): the padded lanes of the launch
+    must neither read nor write past them.  The arrays sit inside guard-filled allocations; results equal update()."""
+    import torch
+    from robobee3d_b200.batch import BatchUMPC
+    p, R, dq = util.config2_states(B, seed=21)
+    Rc = np.ascontiguousarray(R.transpose(0, 2, 1).reshape(B, 9), np.float32)
+    z3 = np.zeros((B, 3), np.float32); e3 = np.tile(np.float32([0, 0, 1.0]), (B, 1))
+    aT0 = np.full(B, 9.81e-3, np.float32)
+    G = 1024  # guard elements on both sides
+    def guarded(a, fill):
+        a = np.ascontiguousarray(a, np.float32)
+        t = torch.full((a.size + 2 * G,), fill, dtype=torch.float32, device="cuda")
+        t[G:G + a.size] = torch.from_numpy(a.ravel()).cuda()
+        return t, t[G:G + a.size].view(*a.shape)
+    ins = [guarded(a, 7.5e8) for a in (p, Rc, dq, z3, z3, e3, aT0)]
+    outs = [guarded(np.zeros((B, k), np.float32), -3.25) for k in (3, 6)]
+    b1, b2 = BatchUMPC(B), BatchUMPC(B)
+    for call in range(2):
+        # ordered against torch's current stream: inputs written just above by torch ops, outputs read right after
+        b1.update_dev(outs[0][1], outs[1][1], *[v for _, v in ins])
+        uq_d, acc_d = outs[0][1].cpu().numpy(), outs[1][1].cpu().numpy()
+        uq, acc = b2.update(p, R, dq, z3, z3, e3, aT0)
+        assert np.array_equal(uq_d, uq) and np.array_equal(acc_d, acc), (B, call)
+        for full, view in outs:
+            f = full.cpu().numpy()
+            assert (f[:G] == -3.25).all() and (f[G + view.numel():] == -3.25).all(), "write past the caller's array"
+    b1.close(); b2.close()
+
+
+def test_wlqp_and_funapprox_exports(cuda_required):
+    """wlqpInit / wlqpUpdate (wlcontroller/c/wlqp.h:29-31) and funApproxInit/F/Df (funapprox.h:31-35) as a C caller
+    binds them: same results as wlControllerUpdate on the scripted demand, F/Df equal to the closed form."""
+    import ctypes as C
+    from robobee3d_b200 import _lib
+    L = _lib.load()
+    c = util.load_constants()
+    g = np.load(os.path.join(GOLDEN, "wl_seq.npz"))
+    FP = C.POINTER(C.c_float)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    fp = lambda a: a.ctypes.data_as(FP)
+    po = f32(c["popts_waypoint"])
+    # FunApprox
+    rng = np.random.default_rng(0)
+    for i in range(6):
+        fa = _lib.FunApprox_t()
+        L.funApproxInit(C.byref(fa), fp(po[15 * i:15 * i + 15].copy()))
+        a0, a1 = po[15 * i], po[15 * i + 1:15 * i + 5]
+        A2 = np.zeros((4, 4)); A2[np.triu_indices(4)] = po[15 * i + 5:15 * i + 15]; A2 = A2 + A2.T - np.diag(np.diag(A2))
+        assert np.allclose(np.array(fa.A2).reshape(4, 4), A2.astype(np.float32))
+        x = f32(rng.uniform(-1, 1, 4) * [100, 0.5, 0.2, 0.1] + [140, 0, 0, 0])
+        fv = L.funApproxF(C.byref(fa), fp(x))
+        df = np.zeros(4, np.float32)
+        L.funApproxDf(fp(df), C.byref(fa), fp(x))
+        ref_f = a0 + a1 @ x + 0.5 * x @ A2 @ x
+        assert abs(fv - ref_f) <= 1e-5 * max(1.0, abs(ref_f))
+        assert np.abs(df - (a1 + A2 @ x)).max() <= 1e-5 * max(1.0, np.abs(a1 + A2 @ x).max())
+    # WLQP object: u0 carried by the caller (wlControllerUpdate does exactly that, wlcontroller.c:35-45)
+    L.wlqpSetWrenchModel(fp(po))
+    q = _lib.WLQP_t()
+    L.wlqpInit(C.byref(q), C.c_float(1000.0))
+    assert abs(q.U0[0] - 5.0) < 1e-6 and q.Q[0] == 1.0 and abs(q.Q[35] - 0.1) < 1e-7 and q.umin[0] == 90.0
+    u0 = f32(c["wl_defaults"]["u0"]); h0 = f32(g["h0"])
+    n = 120
+    scale = np.abs(g["popts_waypoint_qp_u"][:n]).max(axis=0)
+    for i in range(1, n + 1):
+        u = np.zeros(4, np.float32)
+        L.wlqpUpdate(C.byref(q), fp(u), fp(u0), fp(h0), fp(f32(g["pdotdes"][i])))
+        assert (np.abs(u - g["popts_waypoint_qp_u"][i - 1]) / scale).max() < 2e-3, i
+        u0 = u.copy()
+    assert np.isfinite(np.array(q.w0)).all() and abs(q.w0[2]) > 0
+
+
+def test_dropin_rereads_public_fields(cuda_required, gold):
+    """the reference re-reads UprightMPC_t's weights / dt / Tmax / T0 on every umpcUpdate (uprightmpc2.c:126-207):
+    editing them between calls must act like a controller built with the new values."""
+    import ctypes as C
+    from robobee3d_b200 import _lib
+    L = _lib.load()
+    d = util.load_constants()["umpc_defaults"]
+    FP = C.POINTER(C.c_float)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    fp = lambda a: a.ctypes.data_as(FP)
+    def mk(wpr):
+        up = _lib.UprightMPC_t()
+        L.umpcInit(C.byref(up), d["dt"], d["g"], d["TtoWmax"], d["ws"], d["wds"], wpr, d["wpf"], d["wvr"], d["wvf"],
+                   d["wthrust"], d["wmom"], fp(f32(d["Ib"])), d["maxIter"])
+        return up
+    def call(up, e, T0=None):
+        if T0 is not None:
+            up.T0 = T0
+        uq, acc = np.zeros(3, np.float32), np.zeros(6, np.float32)
+        L.umpcUpdate(C.byref(up), fp(uq), fp(acc), fp(f32(gold["p"][e, 0])), fp(f32(gold["R"][e, 0].T)), fp(f32(gold["dq"][e, 0])),
+                     fp(f32(gold["pdes"][e, 0])), fp(f32(gold["dpdes"][e, 0])), fp(f32(gold["sdes"][e, 0])), C.c_float(-1.0))
+        return uq, acc
+    a, bq = mk(d["wpr"]), mk(3.0)
+    for i in range(3):
+        a.Qyr[i] = 3.0          # edit the running controller's position weight
+    ua, _ = call(a, 1, T0=9.81e-3)
+    ub, _ = call(bq, 1, T0=9.81e-3)
+    assert np.array_equal(ua, ub)
+    assert a.Px_data[0] == 3.0 and abs(a.T0 - ua[0]) == 0.0
+    u0, _ = call(mk(d["wpr"]), 1, T0=9.81e-3)
+    assert not np.array_equal(u0, ua)
+    for up in (a, bq):
+        L.umpcFree(C.byref(up))

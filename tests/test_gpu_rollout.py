@@ -185,3 +185,58 @@ def test_rollout_matches_reference_python_loop(cuda_required, name):
         m = b.metrics()
         assert abs(m["err"][5] / gm[0] - 1) < 2e-2 and abs(m["eff"][5] / gm[1] - 1) < 5e-2
     b.close()
+
+
+@pytest.mark.parametrize("name", ["hover", "helix"])
+def test_cascade_true_wlqp_matches_reference(cuda_required, name):
+    """config 4 with the TRUE WLQP fused into the rollout kernel (wlMode=2): umpcUpdate -> wlqpUpdate (4x4 OSQP, 40
+    iterations, termination test every 25 like the C build) -> actualT0 feedback, against the reference's own
+    umpcUpdate + wlControllerUpdate loop (tests/golden/cascade_wlqp.npz, make_golden.py::cascade_wlqp)."""
+    from robobee3d_b200.batch import BatchUMPC
+    c = util.load_constants()
+    g = np.load(os.path.join(GOLDEN, "cascade_wlqp.npz"))
+    hl, tend, task = g[name + "_cfg"][:3]
+    tp = g[name + "_cfg"][3:]
+    nt = int(np.ceil(tend / 0.2))
+    b = BatchUMPC(32, hlInterval=float(hl), wlMode=2, wl_popts=c["popts_waypoint"], wlqpCheckTermination=25)
+    p, R, dq = _ic(32)
+    b.set_state(p, R, dq, task=int(task), tp=tp)
+    b.set_log(2, nt)
+    for n in (3, nt - 3):   # the WL state (u0, OSQP warm start) must carry over launches
+        b.rollout(n)
+    y, u = b.get_log(nt)
+    gy = g[name + "_y"]
+    tol_p = max(TOL_TRAJ_P, 2e-3 * np.abs(gy[:, :3]).max())
+    assert np.abs(y[::10, :3] - gy[:, :3]).max() <= tol_p
+    assert np.abs(y[::10, 3:6] - gy[:, 3:6]).max() <= 2 * TOL_TRAJ_S
+    gm = g[name + "_metrics"]
+    m = b.metrics()
+    assert m["nsolve"][2] == int(gm[2]) and m["nstep"][2] == nt
+    assert abs(m["err"][2] / gm[0] - 1) < 2e-2 and abs(m["eff"][2] / gm[1] - 1) < 5e-2
+    b.close()
+
+
+def test_monte_carlo_sample_matches_oracle(cuda_required):
+    """config 3 at its size (65,536 perturbed flights, MPC every step): 64 envs spread over the batch are compared with
+    the CPU oracle (restated controller + plant) over the 50 steps -- not only finiteness."""
+    from oracle import binding as OB
+    from robobee3d_b200.batch import BatchUMPC
+    B, nt = 65536, 50
+    p, R, dq = util.config3_ics(B, seed=0)
+    b = BatchUMPC(B)
+    b.set_state(p, R, dq, task=0, tp=(0.0, 0.0, 0.1, 0.0))
+    b.rollout(nt)
+    pf, Rf, dqf, uq = b.state()
+    m = b.metrics()
+    cfg = OB.rollout_cfg(tend=nt * 0.2, hlInterval=None)
+    worst_p = worst_s = 0.0
+    for e in np.linspace(0, B - 1, 64).astype(int):
+        o = OB.OracleUMPC("f32")
+        r = OB.rollout(o.lib, o.par, o.st, (p[e], R[e], dq[e]), cfg)
+        fin = r["final"]
+        worst_p = max(worst_p, np.abs(pf[e] - fin[:3]).max())
+        worst_s = max(worst_s, np.abs(Rf[e][:, 2] - fin[3 + 6:3 + 9]).max())
+        assert np.abs(dqf[e] - fin[12:]).max() <= 5e-3 * max(1.0, np.abs(fin[12:]).max()), e
+        assert abs(m["err"][e] / r["err"] - 1) < 1e-3 and m["nsolve"][e] == r["nsolve"]
+    assert worst_p <= TOL_TRAJ_P and worst_s <= TOL_TRAJ_S, (worst_p, worst_s)
+    b.close()

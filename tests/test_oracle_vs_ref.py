@@ -164,3 +164,24 @@ def test_golden_fixtures_reproduce_from_reference(gold):
             x, y, _ = r.solution()
             assert np.array_equal(x.astype(np.float32), gold["x"][e, c])
             assert np.array_equal(uq.astype(np.float32), gold["uquad"][e, c])
+
+
+def test_oracle_cascade_true_wlqp_matches_reference_golden():
+    """config 4 with the TRUE WLQP (wlMode 2): restated umpcUpdate -> restated wlqpUpdate -> actualT0 feedback against
+    the reference's umpcUpdate -> wlControllerUpdate loop (tests/golden/make_golden.py::cascade_wlqp)."""
+    c = util.load_constants()
+    g = np.load(os.path.join(GOLDEN, "cascade_wlqp.npz"))
+    for name in ("hover", "helix"):
+        hl, tend, task = g[name + "_cfg"][:3]
+        tp = g[name + "_cfg"][3:]
+        o = OB.OracleUMPC("f32")
+        wl = OB.OracleWL(c["popts_waypoint"])
+        cfg = OB.rollout_cfg(tend=float(tend), hlInterval=float(hl))
+        r = OB.rollout(o.lib, o.par, o.st, OB.control_test_ic(), cfg, task=int(task), tp=tp, wl=wl.wl, wlmode=2)
+        gy = g[name + "_y"]
+        tol_p = max(util.TOL_TRAJ_P, 2e-3 * np.abs(gy[:, :3]).max())
+        assert np.abs(r["y"][::10, :3] - gy[:, :3]).max() <= tol_p, name
+        assert np.abs(r["y"][::10, 3:6] - gy[:, 3:6]).max() <= 2 * util.TOL_TRAJ_S, name
+        gm = g[name + "_metrics"]
+        assert r["nsolve"] == int(gm[2])
+        assert abs(r["err"] / gm[0] - 1) < 2e-2 and abs(r["eff"] / gm[1] - 1) < 5e-2, (name, r["err"], r["eff"], gm)
