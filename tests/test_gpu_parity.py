@@ -281,3 +281,26 @@ def test_dropin_rereads_public_fields(cuda_required, gold):
     assert not np.array_equal(u0, ua)
     for up in (a, bq):
         L.umpcFree(C.byref(up))
+
+
+def test_c_program_links_and_runs(cuda_required, tmp_path, gold):
+    """tests/cabi/link_check.c (plain C, links libumpc_b200.so through include/umpc_b200.h) runs three umpcUpdate calls;
+    its outputs equal the ctypes drop-in on the same inputs."""
+    import subprocess
+    from robobee3d_b200 import uprightmpc2py
+    root = util.ROOT
+    libdir = os.path.join(root, "robobee3d_b200")
+    exe = str(tmp_path / "link_check")
+    subprocess.run(["gcc", "-O1", "-I" + os.path.join(root, "include"), os.path.join(root, "tests", "cabi", "link_check.c"),
+                    "-L" + libdir, "-lumpc_b200", "-Wl,-rpath," + libdir, "-o", exe], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = [l.split() for l in r.stdout.splitlines() if l.startswith("umpcUpdate")]
+    assert len(lines) == 3
+    d = util.load_constants()["umpc_defaults"]
+    up = uprightmpc2py.UprightMPC2C(d["dt"], d["g"], d["TtoWmax"], d["ws"], d["wds"], d["wpr"], d["wpf"], d["wvr"], d["wvf"],
+                                    d["wthrust"], d["wmom"], d["Ib"], d["maxIter"])
+    for k, l in enumerate(lines):
+        uq, acc = up.update([1.0, -2.0, 3.0], np.eye(3), [0.1, 0, 0, 0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 1.0], 9.81e-3 if k == 0 else -1.0)
+        got = np.array([float(v) for v in l[5:8]])
+        assert np.array_equal(got.astype(np.float32), uq.astype(np.float32)), (k, got, uq)

@@ -172,3 +172,42 @@ def test_dirtran_bench_shards_reproduce_the_same_envs():
         part, xr2 = bench._dt_mild_states(lo, hi)
         assert np.array_equal(part, whole[lo:hi]) and np.array_equal(xr, xr2)
     assert np.abs(whole - xr).max() <= 0.2 and np.abs(whole - xr).max() > 0.05
+
+
+def _cc(args, out):
+    import subprocess
+    subprocess.run(["gcc", "-O1"] + args + ["-o", out], check=True)
+    return out
+
+
+def test_abi_layout_equals_reference_headers(tmp_path):
+    """Compiler-checked boundary: tests/cabi/abi_probe.c compiled against the REFERENCE's own headers
+    (template/uprightmpc2/{uprightmpc2,funapprox}.h, template/wlcontroller/c/{wlqp,funapprox}.h) and against
+    include/umpc_b200.h must print the same sizeof/offsetof tables.  Where /root/reference is absent (GPU box) the
+    reference-side tables are the committed tests/golden/abi_layout_ref_*.txt, generated by this same probe."""
+    import subprocess
+    src = os.path.join(ROOT, "tests", "cabi", "abi_probe.c")
+    ours = _cc(["-I" + os.path.join(ROOT, "include"), src], str(tmp_path / "ours"))
+    run = lambda exe, w: subprocess.run([exe, w], capture_output=True, text=True, check=True).stdout
+    refs = {}
+    for tag, define, inc in (("umpc", "PROBE_REF_UMPC", "/root/reference/template/uprightmpc2"),
+                             ("wlqp", "PROBE_REF_WLQP", "/root/reference/template/wlcontroller/c")):
+        gold = open(os.path.join(ROOT, "tests", "golden", "abi_layout_ref_%s.txt" % tag)).read()
+        if os.path.isdir(inc):
+            exe = _cc(["-D" + define, "-I" + inc, src], str(tmp_path / ("ref_" + tag)))
+            live = run(exe, "a")
+            assert live == gold, "committed reference layout table is stale"
+        refs[tag] = gold
+    assert run(ours, "u") + run(ours, "f") == refs["umpc"]
+    assert run(ours, "w") + run(ours, "f") == refs["wlqp"]
+    assert "UprightMPC_t sizeof 1308" in refs["umpc"]
+
+
+def test_c_program_links_against_the_library(tmp_path):
+    """a plain C translation unit including include/umpc_b200.h links libumpc_b200.so (no ctypes in between)"""
+    import subprocess
+    libdir = os.path.join(ROOT, "robobee3d_b200")
+    exe = _cc(["-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cabi", "link_check.c"), "-L" + libdir,
+               "-lumpc_b200", "-Wl,-rpath," + libdir], str(tmp_path / "link_check"))
+    out = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
+    assert "libumpc_b200.so" in out
