@@ -57,6 +57,7 @@ struct GlobStore64 {
     for (int i = 0; i < UMPC_GEN_CHUNK; ++i) v[i] = __ldcg(w + ROWD(c * UMPC_GEN_CHUNK + i));
   }
   __device__ __forceinline__ void wait(double (&)[UMPC_GEN_CHUNK]) const {}
+  __device__ __forceinline__ void waitc(int, double (&)[UMPC_GEN_CHUNK]) const {}
   __device__ __forceinline__ void setW(int e, double v) { __stcg(w + ROWD(e), v); }
   __device__ __forceinline__ void setChunk(int c, const double (&v)[UMPC_GEN_CHUNK]) {
 #pragma unroll
@@ -98,6 +99,7 @@ struct SolverF64 {
   typedef umpc64::UmpcParams Params;
   static constexpr int kMinBlocks = 1;
   GlobStore64 st;
+  bool info_wanted = true;  // (converged mode always evaluates its residuals: they are the termination test)
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t*) { return 0u; }
   template <int TPB>

@@ -59,6 +59,7 @@ typedef UMPC_REAL ureal;
 #define UMPC_ST_MAX_ITER (-2)
 #define UMPC_ST_NON_CVX (-7)
 #define UMPC_ST_UNSOLVED (-10)
+#define UMPC_ST_NOT_EVALUATED 0   // ours: update ran with want_info = false (no residuals, no status)
 
 // Controller parameters (what umpcInit derives, uprightmpc2.c:19-63,116-117) plus the
 // OSQP settings baked into the generated workspace (uprightmpc2/workspace.c:561).
@@ -287,7 +288,10 @@ UMPC_HD ureal umpc_ref(const ureal (&yd)[6], const ureal (&dyd)[6], int j) {
 template <bool CONV, class ST, class IO>
 UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], ureal accdes[6], const ureal p0[3],
                          const ureal R0[9], const ureal dq0[6], const ureal pdes[3], const ureal dpdes[3],
-                         const ureal sdes[3], ureal actualT0, ureal& T0, UmpcInfo& info) {
+                         const ureal sdes[3], ureal actualT0, ureal& T0, UmpcInfo& info, bool want_info = true) {
+  // want_info = false (C path only): the caller will not read solve info / solution of this update (the reference never acts
+  // on it either: check_termination = 0, uprightmpc2.c:116-117) -- the residual norms, status and the solx/soly rows are
+  // skipped; the divergence guard (NaN solution + cold start, auxil.c:538-561) then tests the iterates themselves.
   const ureal dt = par.dt;
   if (actualT0 >= 0.0f) T0 = actualT0;
   io.prefetch_warm_start();  // xs/zs/ys are needed only after Ruiz + factor: start pulling them into L2 now
@@ -500,7 +504,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
       ureal wd[UMPC_GEN_CHUNK];
       st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
-      st.wait(wd);
+      st.waitc(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
 #pragma unroll
       for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
         ureal s2[2];
@@ -529,7 +533,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     for (int gq = 0; gq < (UMPC_GEN_NWORDS - UMPC_GEN_OFF_SG) / UMPC_GEN_CHUNK; ++gq) {
       ureal wd[UMPC_GEN_CHUNK];
       st.issue(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
-      st.wait(wd);
+      st.waitc(UMPC_GEN_OFF_SG / UMPC_GEN_CHUNK + gq, wd);
 #pragma unroll
       for (int u = 0; u < UMPC_GEN_CHUNK; ++u) {
         ureal s2[2];
@@ -619,8 +623,9 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     // un-scaled norms for the termination test; scaled ones (E, D weighted) for the rho estimate (auxil.c:13-75
     // works on the scaled residual vectors left in z_prev / x_prev)
     const bool adapt = rho_every > 0;
+    const bool full = CONV || want_info;
     ureal pri = 0.0f, nz = 0.0f, nAx = 0.0f, pri_s = 0.0f, pn_s = 0.0f;
-    {
+    if (full) {
       ureal Ax[UMPC_NC];
       umpc_gen_Ax(Ax, xf, a);
 #pragma unroll
@@ -635,7 +640,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       }
     }
     ureal dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f, dua_s = 0.0f, dn_s = 0.0f;
-    {
+    if (full) {
       ureal Aty[UMPC_NX];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
@@ -661,6 +666,19 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     bool check = last;
     if constexpr (CONV) check = last || (chk_every > 0 && iter_done % chk_every == 0);
     int status;
+    if (!full) {
+      // no residuals: an iterate that left the float range (or is NaN) is what drives a residual past OSQP_INFTY
+      ureal mx = 0.0f;
+#pragma unroll
+      for (int j = 0; j < UMPC_NX; ++j) mx = umpc_fmax(mx, umpc_fabs(xf[j]));
+#pragma unroll
+      for (int i = 0; i < UMPC_NC; ++i) mx = umpc_fmax(mx, umpc_fabs(ys[i]));
+      ureal sm = 0.0f;  // fmax drops NaNs: a sum keeps them
+#pragma unroll
+      for (int k = 0; k < 3; ++k) sm += xf[36 + k] + xf[18 + k] + xf[21 + k];
+      status = (mx > 1e30f || sm != sm) ? UMPC_ST_NON_CVX : UMPC_ST_NOT_EVALUATED;
+      pri = umpc_nan(); dua = umpc_nan();
+    } else
     if (pri > 1e30f || dua > 1e30f) status = UMPC_ST_NON_CVX;  // OSQP_INFTY (auxil.c:706-716)
     else if (!check) status = UMPC_ST_UNSOLVED;
     else if (pri < ep && dua < ed) status = UMPC_ST_SOLVED;
@@ -674,13 +692,13 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       const bool bad = status == UMPC_ST_NON_CVX;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        io.st_solx(j, xf[j]);
+        if (full) io.st_solx(j, xf[j]);
         io.st_xs(j, xf[j] * UMPC_RCP(Dl[j]));
       }
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) {
         const ureal e = El[i];
-        io.st_soly(i, ys[i] * cinv);
+        if (full) io.st_soly(i, ys[i] * cinv);
         io.st_zs(i, zs[i] * e);
         io.st_ys(i, ys[i] * UMPC_RCP(e));
       }

@@ -63,6 +63,7 @@ struct SmemStore {
     asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
                  "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]));
   }
+  __device__ __forceinline__ void waitc(int, float (&v)[UMPC_GEN_CHUNK]) const { wait(v); }
   __device__ __forceinline__ void setW(int e, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(e >> 2) * gstride + (uint32_t)(e & 3) * 4u), "f"(v) : "memory");
   }
@@ -98,6 +99,7 @@ struct TmemStore {
                    "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15])
                  :: "memory");
   }
+  __device__ __forceinline__ void waitc(int, float (&v)[UMPC_GEN_CHUNK]) const { wait(v); }
   __device__ __forceinline__ void setW(int e, float v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tbase + (uint32_t)e), "f"(v) : "memory");
   }
@@ -118,6 +120,80 @@ struct TmemStore {
 #else
   __device__ __forceinline__ void sync() const {}
 #endif
+  __device__ __forceinline__ float Vf(int i) const { return vf[ROWF(i)]; }
+  __device__ __forceinline__ void setVf(int i, float v) { vf[ROWF(i)] = v; }
+};
+
+
+// (3) HybridStore: the round-1 profile put the ADMM loop at 0.66 IPC per scheduler with ONE or TWO warps on it -- the
+//     loop is bound by the TMEM read path (31 x 2 KB per warp and pass = ~184 B/clk/SM, tests/microbench/tmem_bw.cu
+//     measures ~190), not by issue.  Shared memory is a second, independent pipe (128 B/clk/SM): the chunks whose bit
+//     is set in MASK live there ([chunk slot][group of 4 words][thread][4]: a chunk = four conflict-free LDS.128),
+//     the others in TMEM, so both pipes stream the factor at the same time.  MASK = 0 is the pure-TMEM store.
+__host__ __device__ constexpr int umpc_popc(unsigned v) { int n = 0; while (v) { n += v & 1u; v >>= 1; } return n; }
+#ifndef UMPC_SMEM_MASK
+#define UMPC_SMEM_MASK 0x0000u
+#endif
+template <int TPB, unsigned MASK>
+struct HybridStore {
+  static constexpr bool kTmem = true;
+  static constexpr unsigned kMask = MASK;
+  static constexpr int kSmemChunks = umpc_popc(MASK);
+  static constexpr size_t kSmemBytes = (size_t)kSmemChunks * UMPC_GEN_CHUNK * 4 * TPB;
+  static constexpr uint32_t gstride = TPB * 16u;
+  uint32_t tbase, sbase;
+  float* vf;
+  __device__ __forceinline__ void init(uint32_t tbase_, float* vf_);
+  __device__ __forceinline__ void begin_iteration(int) {}
+  static __host__ __device__ constexpr bool in_smem(int c) { return (MASK >> c) & 1u; }
+  static __host__ __device__ constexpr int slot(int c) { return umpc_popc(MASK & ((1u << c) - 1u)); }
+  __device__ __forceinline__ void issue(int c, float (&v)[UMPC_GEN_CHUNK]) const {
+    if (in_smem(c)) {
+#pragma unroll
+      for (int g = 0; g < UMPC_GEN_CHUNK / 4; ++g)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[4 * g]), "=f"(v[4 * g + 1]), "=f"(v[4 * g + 2]), "=f"(v[4 * g + 3])
+                     : "r"(sbase + (uint32_t)(slot(c) * (UMPC_GEN_CHUNK / 4) + g) * gstride));
+    } else {
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]),
+            "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+          : "r"(tbase + (uint32_t)c * UMPC_GEN_CHUNK));
+    }
+  }
+  __device__ __forceinline__ void waitc(int c, float (&v)[UMPC_GEN_CHUNK]) const {
+    if (in_smem(c))
+      asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
+                   "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]));
+    else
+      asm volatile("tcgen05.wait::ld.sync.aligned;"
+                   : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
+                     "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15])
+                   :: "memory");
+  }
+  __device__ __forceinline__ void setW(int e, float v) {
+    const int c = e / UMPC_GEN_CHUNK, r = e % UMPC_GEN_CHUNK;
+    if (in_smem(c))
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)(slot(c) * (UMPC_GEN_CHUNK / 4) + r / 4) * gstride + (uint32_t)(r & 3) * 4u), "f"(v) : "memory");
+    else
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tbase + (uint32_t)e), "f"(v) : "memory");
+  }
+  __device__ __forceinline__ void setChunk(int c, const float (&v)[UMPC_GEN_CHUNK]) {
+    if (in_smem(c)) {
+#pragma unroll
+      for (int g = 0; g < UMPC_GEN_CHUNK / 4; ++g)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sbase + (uint32_t)(slot(c) * (UMPC_GEN_CHUNK / 4) + g) * gstride),
+                     "f"(v[4 * g]), "f"(v[4 * g + 1]), "f"(v[4 * g + 2]), "f"(v[4 * g + 3]) : "memory");
+    } else {
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+          ::"r"(tbase + (uint32_t)c * UMPC_GEN_CHUNK), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]),
+          "f"(v[7]), "f"(v[8]), "f"(v[9]), "f"(v[10]), "f"(v[11]), "f"(v[12]), "f"(v[13]), "f"(v[14]), "f"(v[15]) : "memory");
+    }
+  }
+  __device__ __forceinline__ void end_writes() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ void sync() const {}
   __device__ __forceinline__ float Vf(int i) const { return vf[ROWF(i)]; }
   __device__ __forceinline__ void setVf(int i, float v) { vf[ROWF(i)] = v; }
 };
@@ -168,6 +244,9 @@ struct GlobIO {
   __device__ __forceinline__ void st_soly(int i, float v) { eb[ROWF(ROW_SOLY + i)] = v; }
 };
 
+#ifndef UMPC_DEFAULT_STAGGER_NS
+#define UMPC_DEFAULT_STAGGER_NS 0
+#endif
 #ifndef UMPC_DEFAULT_TPB
 #define UMPC_DEFAULT_TPB 128  // TMEM scratch, two 4-warp CTAs per SM
 #endif
@@ -175,6 +254,13 @@ struct GlobIO {
 typedef KernelParamsT<UmpcParams> KernelParams;
 
 extern __shared__ float g_smem[];
+template <int TPB, unsigned MASK>
+__device__ __forceinline__ void HybridStore<TPB, MASK>::init(uint32_t tbase_, float* vf_) {
+  tbase = tbase_; vf = vf_;
+  sbase = (uint32_t)__cvta_generic_to_shared(g_smem) + threadIdx.x * 16u;
+}
+// default scratch store of the TMEM launch shapes
+template <int TPB> using DefStore = HybridStore<TPB, UMPC_SMEM_MASK>;
 
 // The C path's SOLVER policy (umpc_dev.cuh): float32, scratch store ST, exactly max_iter iterations.
 // PERENV: cost weights per environment (DevState::wts) instead of the batch-wide ones; a separate instantiation so
@@ -185,6 +271,7 @@ struct SolverF32 {
   static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
   ST st;
   float* eb;
+  bool info_wanted = true;  // false: skip residuals / status / solution rows of the next update (rollout steps nobody reads)
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) {
     if (ST::kTmem) return tmem_acquire<TPB>(slot);
@@ -215,9 +302,9 @@ struct SolverF32 {
     if constexpr (PERENV) {
       Params pe = par;
       load_env_weights(pe, s, e);
-      umpc_update<false>(pe, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+      umpc_update<false>(pe, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info, info_wanted);
     } else {
-      umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
+      umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info, info_wanted);
     }
     eb[ROWF(ROW_T0)] = T0;
     store_info(eb, info.iter, info.status, info.pri_res, info.dua_res);
@@ -329,6 +416,8 @@ extern "C" const char* umpcLastError(void) { return g_err.c_str(); }
 void umpc_internal_set_error(const char* msg) { g_err = msg; }  // for the other translation units (dirtran.cu)
 
 struct UmpcBatch {
+  int nsm = 148;           // SMs of the device
+  bool tpb_user = false;   // launch shape chosen through umpcBatchSetLaunch / UMPC_TPB
   int B = 0, Bp = 0, device = 0, tpb = 128;  // B: caller's env count, Bp: padded to whole warps (device stride)
   cudaStream_t stream = nullptr;
   cudaStream_t side[3] = {nullptr, nullptr, nullptr};  // chunk pipeline of the host-buffer calls
@@ -401,6 +490,11 @@ static void fill_kernel_params(UmpcBatch* b) {
   sm.dtsim = (float)p.dtsim; sm.hl_interval = (float)p.hlInterval; sm.taulim = p.taulim; sm.tpert = p.tpert;
   for (int i = 0; i < 3; ++i) sm.Ib[i] = p.Ib[i];
   sm.g = p.g; sm.mb = p.mb; sm.wl_mode = p.wlMode; sm.int_pos = p.intInitialPos;
+  sm.info_every_step = 0;
+  if (const char* ev = getenv("UMPC_INFO_EVERY_STEP")) sm.info_every_step = atoi(ev);
+  // start delay of the second warp per scheduler in multi-step rollouts (umpc_dev.cuh); tuning knob, microseconds
+  sm.stagger_ns = UMPC_DEFAULT_STAGGER_NS;
+  if (const char* ev = getenv("UMPC_STAGGER_US")) sm.stagger_ns = atoi(ev) * 1000;
   WlParams& w = b->wlp;
   memset(&w, 0, sizeof(w));
   memcpy(w.popts, p.wl_popts, sizeof(w.popts));
@@ -425,6 +519,7 @@ extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
   // 32, 64: shared-memory scratch (one/two-warp CTAs); 128, 256: tensor-memory scratch (TMEM needs 4-warp multiples)
   if (!b || (tpb != 32 && tpb != 64 && tpb != 128 && tpb != 256)) { g_err = "threads_per_block must be 32, 64 (shared-memory scratch) or 128, 256 (TMEM scratch)"; return UMPC_ERR_ARG; }
   b->tpb = tpb;
+  b->tpb_user = true;   // the rollout then uses this shape too (ntiles / (tpb / 32) CTAs) instead of its persistent default
   return UMPC_OK;
 }
 
@@ -505,10 +600,20 @@ static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par)
   CK(cudaFuncSetAttribute(umpc_update_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024))); \
   CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
   UMPC_SET_SMEM(32) UMPC_SET_SMEM(64)
+  // hybrid TMEM + shared-memory scratch of the TMEM launch shapes (HybridStore): opt in to > 48 KB of dynamic shared memory
+#define UMPC_SET_HYB(K, T, ...) CK(cudaFuncSetAttribute(K<T, SolverF32<T, DefStore<T>, ##__VA_ARGS__>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
+  UMPC_SET_HYB(umpc_update_kernel, 128) UMPC_SET_HYB(umpc_update_kernel, 256) UMPC_SET_HYB(umpc_update_kernel, 128, true)
+  UMPC_SET_HYB(umpc_rollout_kernel, 128) UMPC_SET_HYB(umpc_rollout_kernel, 256) UMPC_SET_HYB(umpc_rollout_kernel, 128, true)
+  UMPC_SET_HYB(umpc_hostio_kernel, 128)
+  {
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, b->device));
+    b->nsm = prop.multiProcessorCount;
+  }
   b->tpb = UMPC_DEFAULT_TPB;
   if (const char* t = getenv("UMPC_TPB")) {  // tuning/testing knob: same values as umpcBatchSetLaunch
     const int v = atoi(t);
-    if (v == 32 || v == 64 || v == 128 || v == 256) b->tpb = v;
+    if (v == 32 || v == 64 || v == 128 || v == 256) { b->tpb = v; b->tpb_user = true; }
   }
   return reset_state(b);
 }
@@ -585,12 +690,12 @@ static int launch_update(UmpcBatch* b, float* uquad, float* accdes, const float*
                                                          b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);                      \
     break;
   if (b->s.wts) {  // per-env weights: TMEM launch shape only
-    umpc_update_kernel<128, SolverF32<128, TmemStore, true>><<<(nenv + 127) / 128, 128, 0, stream>>>(
+    umpc_update_kernel<128, SolverF32<128, DefStore<128>, true>><<<(nenv + 127) / 128, 128, DefStore<128>::kSmemBytes, stream>>>(
         b->kp, b->s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, b->have_qpdata ? 1 : 0, pn, Rn, dqn, env0);
   } else
   switch (tpb) {
     UMPC_LAUNCH_UPDATE(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_UPDATE(64, SmemStore<64>, smem_bytes(64))
-    UMPC_LAUNCH_UPDATE(128, TmemStore, 0) UMPC_LAUNCH_UPDATE(256, TmemStore, 0)
+    UMPC_LAUNCH_UPDATE(128, DefStore<128>, DefStore<128>::kSmemBytes) UMPC_LAUNCH_UPDATE(256, DefStore<256>, DefStore<256>::kSmemBytes)
     default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
   }
   CK(cudaGetLastError());
@@ -691,7 +796,7 @@ static int run_chunked(UmpcBatch* b, HostArr* in, int nin, HostArr* out, int nou
       io.pulled = b->d_pulled;
       CK(cudaMemsetAsync(b->d_pulled, 0, sizeof(unsigned), b->stream));
       CK(cudaEventRecord(b->ev0, b->stream));
-      umpc_hostio_kernel<128, SolverF32<128, TmemStore>><<<b->Bp / 128, 128, 0, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
+      umpc_hostio_kernel<128, SolverF32<128, DefStore<128>>><<<b->Bp / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
       CK(cudaGetLastError());
       CK(cudaEventRecord(b->ev1, b->stream));
       b->timed = true;
@@ -956,12 +1061,17 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
                                                              b->lg);                                                    \
     break;
   if (b->s.wts) {
-    umpc_rollout_kernel<128, SolverF32<128, TmemStore, true>><<<(b->Bp + 127) / 128, 128, 0, b->stream>>>(
+    umpc_rollout_kernel<128, SolverF32<128, DefStore<128>, true>><<<(b->Bp + 127) / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(
+        b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+  } else if (!b->tpb_user) {
+    // default rollout shape: ONE 8-warp CTA per SM (all 512 TMEM columns), warp-tiles dealt statically (umpc_dev.cuh)
+    const int ntiles = b->Bp / 32, pgrid = ntiles < b->nsm ? ntiles : b->nsm;
+    umpc_rollout_kernel<256, SolverF32<256, DefStore<256>>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
         b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
   } else
   switch (tpb) {
     UMPC_LAUNCH_ROLLOUT(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_ROLLOUT(64, SmemStore<64>, smem_bytes(64))
-    UMPC_LAUNCH_ROLLOUT(128, TmemStore, 0) UMPC_LAUNCH_ROLLOUT(256, TmemStore, 0)
+    UMPC_LAUNCH_ROLLOUT(128, DefStore<128>, DefStore<128>::kSmemBytes) UMPC_LAUNCH_ROLLOUT(256, DefStore<256>, DefStore<256>::kSmemBytes)
     default: g_err = "unsupported threads_per_block"; return UMPC_ERR_ARG;
   }
   CK(cudaGetLastError());

@@ -9,6 +9,7 @@ struct HostStore {
   ureal wds[UMPC_GEN_NWORDS], vf[UMPC_NX];
   void issue(int c, ureal (&buf)[UMPC_GEN_CHUNK]) const { for (int i = 0; i < UMPC_GEN_CHUNK; ++i) buf[i] = wds[c * UMPC_GEN_CHUNK + i]; }
   void wait(ureal (&)[UMPC_GEN_CHUNK]) const {}
+  void waitc(int, ureal (&)[UMPC_GEN_CHUNK]) const {}
   void setW(int e, ureal v) { wds[e] = v; }
   void setChunk(int c, const ureal (&v)[UMPC_GEN_CHUNK]) { for (int i = 0; i < UMPC_GEN_CHUNK; ++i) wds[c * UMPC_GEN_CHUNK + i] = v[i]; }
   void end_writes() {}
