@@ -323,6 +323,8 @@ def main():
     ap.add_argument("--hl-interval", type=float, default=None,
                     help="MPC period in ms (controlTest's hlInterval; config 1 uses 5): a step then advances every env by one "
                          "MPC period (26 plant steps at 5 ms) in one launch.  Extra measurement; the headline line uses None")
+    ap.add_argument("--steps-per-launch", type=int, default=0,
+                    help="plant steps (each with an MPC solve when hlInterval is None) advanced per launch of the rollout kernel")
     ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
     ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
     ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran"],
@@ -374,6 +376,8 @@ def main():
         kw["hlInterval"] = args.hl_interval
         spl = int(np.floor(args.hl_interval / 0.2 + 1e-9)) + 1  # t - thlPrev > hlInterval on a 0.2 ms grid
         args.no_e2e = True
+    if args.steps_per_launch:
+        spl = args.steps_per_launch
     b = BatchUMPC(nenv, device=local, **kw)
     if args.tpb:
         b.set_launch(args.tpb)
@@ -437,7 +441,8 @@ def main():
     mean_iter = float(b.solve_info()["iter"].mean()) if args.converged else 50.0
     if rank == 0:
         fl = F.our_flops(mean_iter)
-        per_launch_flops = (fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
+        solves_per_launch = spl if args.hl_interval is None else 1
+        per_launch_flops = (solves_per_launch * fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
         launch_s = dev_s / args.steps
         peak_tf = b.lib.umpcMeasureFp32Peak(local, 4096)
         achieved_tf = per_launch_flops / launch_s * 1e-12
@@ -470,7 +475,7 @@ def main():
                     "workload": "BASELINE configs[3] shape: %d-env cascade per GPU, UprightMPC2 -> %s -> actualT0 feedback every "
                                 "env-step (robobee_test_controllers.py:162-171), WaypointHover constants" % (
                                     nenv, "WLCon" if args.workload == "cascade-wlcon" else "true WLQP (40 iterations)")})),
-                "plant_steps_per_launch": spl, "qp_solves_per_s": nenv * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall / args.steps,
+                "plant_steps_per_launch": spl, "qp_solves_per_s": (spl if args.hl_interval is None else 1) * nenv * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall / args.steps,
                 "gpu_launches": args.steps, "clocks": clocks, "roofline": roofline,
                 "tracking": {"mean_err_mm2": sums[0] / max(sums[3], 1), "mean_eff": sums[1] / max(sums[3], 1),
                              "env_steps_total": sums[3], "non_finite_envs": sums[4]}}
