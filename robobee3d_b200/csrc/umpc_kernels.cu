@@ -601,7 +601,9 @@ static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par)
   CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
   UMPC_SET_SMEM(32) UMPC_SET_SMEM(64)
   // hybrid TMEM + shared-memory scratch of the TMEM launch shapes (HybridStore): opt in to > 48 KB of dynamic shared memory
-#define UMPC_SET_HYB(K, T, ...) CK(cudaFuncSetAttribute(K<T, SolverF32<T, DefStore<T>, ##__VA_ARGS__>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
+#define UMPC_SET_HYB(K, T, ...)                                                                                               \
+  if (DefStore<T>::kSmemBytes > 48 * 1024)                                                                                      \
+    CK(cudaFuncSetAttribute(K<T, SolverF32<T, DefStore<T>, ##__VA_ARGS__>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DefStore<T>::kSmemBytes));
   UMPC_SET_HYB(umpc_update_kernel, 128) UMPC_SET_HYB(umpc_update_kernel, 256) UMPC_SET_HYB(umpc_update_kernel, 128, true)
   UMPC_SET_HYB(umpc_rollout_kernel, 128) UMPC_SET_HYB(umpc_rollout_kernel, 256) UMPC_SET_HYB(umpc_rollout_kernel, 128, true)
   UMPC_SET_HYB(umpc_hostio_kernel, 128)

@@ -9,7 +9,7 @@ import sys,json
 t=sys.stdin.read().strip().splitlines()
 try:
     d=json.loads(t[-1]); print('$label','ms/step %.4f'%d['ms_per_step'],'value %.4g'%d['value'],'frac %.3f'%d['roofline']['frac'])
-except Exception as e: print('$label','FAILED',t[-3:])" >> $O
+except Exception as e: print('$label','FAILED',t[-1][-200:])" >> $O
 }
 B="python bench.py --steps 20 --warmup 3 --no-cpu --no-e2e"
 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_rollout.py -m gpu -q --tb=short -x 2>&1 | tail -15 > gpurun_out/r02b_pytest_default.log
