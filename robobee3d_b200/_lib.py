@@ -64,7 +64,7 @@ EXPORTS = [
     "umpcBatchDefaults", "umpcLastError", "umpcBatchCreate", "umpcBatchDestroy", "umpcBatchSize", "umpcBatchReset",
     "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchUpdateDevOn", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
     "umpcBatchGetState", "umpcBatchRollout", "umpcBatchGetMetrics", "umpcBatchReduceMetrics", "umpcBatchSetLog",
-    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchSetWeights", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch",
+    "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchSetWeights", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch", "umpcBatchSetRolloutInfo",
     "umpcMeasureFp32Peak",
 ]
 
@@ -109,6 +109,7 @@ def load():
     L.umpcBatchTimerStopMs.argtypes = [vp]
     L.umpcBatchTimerStopMs.restype = C.c_float
     L.umpcBatchSetLaunch.argtypes = [vp, C.c_int]
+    L.umpcBatchSetRolloutInfo.argtypes = [vp, C.c_int]
     L.umpcBatchSetWeights.argtypes = [vp, vp]
     L.umpcMeasureFp32Peak.argtypes = [C.c_int, C.c_int]
     L.umpcMeasureFp32Peak.restype = C.c_double

@@ -103,6 +103,10 @@ class BatchUMPC:
             w[:, i] = np.broadcast_to(np.asarray(kw.get(k, getattr(self.params, k)), np.float32), (self.B,))
         _lib.check(self.lib.umpcBatchSetWeights(self.h, _vp(w)), "umpcBatchSetWeights")
 
+    def set_rollout_info(self, on=True):
+        """rollouts also evaluate residuals / status / solution rows after every solve (off by default, see the header)"""
+        _lib.check(self.lib.umpcBatchSetRolloutInfo(self.h, int(bool(on))), "umpcBatchSetRolloutInfo")
+
     def set_launch(self, threads_per_block):
         _lib.check(self.lib.umpcBatchSetLaunch(self.h, int(threads_per_block)), "umpcBatchSetLaunch")
 

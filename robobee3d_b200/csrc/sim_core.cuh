@@ -29,8 +29,6 @@ struct SimParams {
   float mb;          // body mass for the WL glue (ca6dynamics.py:5-10)
   int wl_mode;       // 0: none, 1: WLCon projected gradient, 2: true WLQP
   int int_pos;       // 1: initialPos has integer dtype as in controlTest (see sim_task)
-  int info_every_step;  // rollout: 1 = residuals / status / solution rows after every solve; 0 = only on a launch's last step
-  int stagger_ns;       // rollout: start delay of the second warp of every scheduler (see umpc_rollout_kernel)
 };
 
 UMPC_HD float sim_clip(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }

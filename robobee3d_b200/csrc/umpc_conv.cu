@@ -99,7 +99,6 @@ struct SolverF64 {
   typedef umpc64::UmpcParams Params;
   static constexpr int kMinBlocks = 1;
   GlobStore64 st;
-  bool info_wanted = true;  // (converged mode always evaluates its residuals: they are the termination test)
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t*) { return 0u; }
   template <int TPB>

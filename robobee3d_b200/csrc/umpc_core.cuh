@@ -285,11 +285,11 @@ UMPC_HD ureal umpc_ref(const ureal (&yd)[6], const ureal (&dyd)[6], int j) {
   return j < 18 ? yd[j % 6] : (j < 36 ? dyd[j % 6] : 0.0f);
 }
 
-template <bool CONV, class ST, class IO>
+template <bool CONV, bool INFO = true, class ST, class IO>
 UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], ureal accdes[6], const ureal p0[3],
                          const ureal R0[9], const ureal dq0[6], const ureal pdes[3], const ureal dpdes[3],
-                         const ureal sdes[3], ureal actualT0, ureal& T0, UmpcInfo& info, bool want_info = true) {
-  // want_info = false (C path only): the caller will not read solve info / solution of this update (the reference never acts
+                         const ureal sdes[3], ureal actualT0, ureal& T0, UmpcInfo& info) {
+  // INFO = false (C path only, compile time: the once-per-solve code is instruction-fetch bound, every instruction counts): the caller will not read solve info / solution of this update (the reference never acts
   // on it either: check_termination = 0, uprightmpc2.c:116-117) -- the residual norms, status and the solx/soly rows are
   // skipped; the divergence guard (NaN solution + cold start, auxil.c:538-561) then tests the iterates themselves.
   const ureal dt = par.dt;
@@ -623,9 +623,9 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     // un-scaled norms for the termination test; scaled ones (E, D weighted) for the rho estimate (auxil.c:13-75
     // works on the scaled residual vectors left in z_prev / x_prev)
     const bool adapt = rho_every > 0;
-    const bool full = CONV || want_info;
+    constexpr bool full = CONV || INFO;
     ureal pri = 0.0f, nz = 0.0f, nAx = 0.0f, pri_s = 0.0f, pn_s = 0.0f;
-    if (full) {
+    if constexpr (full) {
       ureal Ax[UMPC_NC];
       umpc_gen_Ax(Ax, xf, a);
 #pragma unroll
@@ -640,7 +640,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       }
     }
     ureal dua = 0.0f, nq = 0.0f, nAty = 0.0f, nPx = 0.0f, dua_s = 0.0f, dn_s = 0.0f;
-    if (full) {
+    if constexpr (full) {
       ureal Aty[UMPC_NX];
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) Aty[j] = 0.0f;
@@ -666,7 +666,7 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
     bool check = last;
     if constexpr (CONV) check = last || (chk_every > 0 && iter_done % chk_every == 0);
     int status;
-    if (!full) {
+    if constexpr (!full) {
       // no residuals: an iterate that left the float range (or is NaN) is what drives a residual past OSQP_INFTY
       ureal mx = 0.0f;
 #pragma unroll
@@ -692,13 +692,13 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
       const bool bad = status == UMPC_ST_NON_CVX;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        if (full) io.st_solx(j, xf[j]);
+        if constexpr (full) io.st_solx(j, xf[j]);
         io.st_xs(j, xf[j] * UMPC_RCP(Dl[j]));
       }
 #pragma unroll
       for (int i = 0; i < UMPC_NC; ++i) {
         const ureal e = El[i];
-        if (full) io.st_soly(i, ys[i] * cinv);
+        if constexpr (full) io.st_soly(i, ys[i] * cinv);
         io.st_zs(i, zs[i] * e);
         io.st_ys(i, ys[i] * UMPC_RCP(e));
       }

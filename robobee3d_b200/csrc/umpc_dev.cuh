@@ -359,12 +359,6 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   // ntiles / (TPB / 32) CTAs degenerates to one tile per warp.
   constexpr int WPC = TPB / 32;
   const int ntiles = s.B >> 5, warp = threadIdx.x >> 5;
-  // Stagger: the two warps of a scheduler (w, w + 4) run identical, deterministic work, i.e. in lockstep -- both in the
-  // issue-bound ADMM loop, then both in the fetch-latency-bound once-per-solve code.  Delaying the second one by a
-  // fraction of a solve keeps one of them in the loop while the other waits on instruction fetch (multi-step launches).
-  if (kp.sim.stagger_ns > 0 && (warp & 4)) {
-    for (int left = kp.sim.stagger_ns; left > 0; left -= 100000) __nanosleep(left < 100000 ? left : 100000);
-  }
   for (int slot = warp; blockIdx.x + gridDim.x * slot < ntiles; slot += WPC) {
   const int e = ((blockIdx.x + gridDim.x * slot) << 5) + (threadIdx.x & 31);
   float* const eb = env_base(s, e);
@@ -412,8 +406,6 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
       for (int i = 0; i < 6; ++i) eb[ROWF(ROW_DQ + i)] = dq[i];
       eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 5)] = cerr; eb[ROWF(ROW_METRICS + 6)] = ceff;
       ((int*)eb)[ROWF(ROW_METRICS + 2)] = nsolve; ((int*)eb)[ROWF(ROW_METRICS + 3)] = nstep;
-      // solve info / solution rows: on the last step of a launch (what the getters read afterwards) or on every step
-      sol.info_wanted = kp.sim.info_every_step || k == nsteps - 1;
       sol.update(kp.mpc, s, e, uq, acc, p, R, dq, pdes, dpdes, sdes, aT0);
 #pragma unroll
       for (int i = 0; i < 6; ++i) eb[ROWF(ROW_ACC + i)] = acc[i];

@@ -244,9 +244,6 @@ struct GlobIO {
   __device__ __forceinline__ void st_soly(int i, float v) { eb[ROWF(ROW_SOLY + i)] = v; }
 };
 
-#ifndef UMPC_DEFAULT_STAGGER_NS
-#define UMPC_DEFAULT_STAGGER_NS 0
-#endif
 #ifndef UMPC_DEFAULT_TPB
 #define UMPC_DEFAULT_TPB 128  // TMEM scratch, two 4-warp CTAs per SM
 #endif
@@ -265,13 +262,12 @@ template <int TPB> using DefStore = HybridStore<TPB, UMPC_SMEM_MASK>;
 // The C path's SOLVER policy (umpc_dev.cuh): float32, scratch store ST, exactly max_iter iterations.
 // PERENV: cost weights per environment (DevState::wts) instead of the batch-wide ones; a separate instantiation so
 // that the default kernel keeps its weights as constant-bank operands.
-template <int TPB_, class ST, bool PERENV = false>
+template <int TPB_, class ST, bool PERENV = false, bool INFO = true>
 struct SolverF32 {
   typedef UmpcParams Params;
   static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
   ST st;
   float* eb;
-  bool info_wanted = true;  // false: skip residuals / status / solution rows of the next update (rollout steps nobody reads)
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) {
     if (ST::kTmem) return tmem_acquire<TPB>(slot);
@@ -302,9 +298,9 @@ struct SolverF32 {
     if constexpr (PERENV) {
       Params pe = par;
       load_env_weights(pe, s, e);
-      umpc_update<false>(pe, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info, info_wanted);
+      umpc_update<false, INFO>(pe, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
     } else {
-      umpc_update<false>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info, info_wanted);
+      umpc_update<false, INFO>(par, st, io, uq, acc, p, R, dq, pd, dpd, sd, aT0, T0, info);
     }
     eb[ROWF(ROW_T0)] = T0;
     store_info(eb, info.iter, info.status, info.pri_res, info.dua_res);
@@ -418,6 +414,7 @@ void umpc_internal_set_error(const char* msg) { g_err = msg; }  // for the other
 struct UmpcBatch {
   int nsm = 148;           // SMs of the device
   bool tpb_user = false;   // launch shape chosen through umpcBatchSetLaunch / UMPC_TPB
+  bool rollout_info = false;  // rollouts also evaluate residuals / status / solution rows after every solve
   int B = 0, Bp = 0, device = 0, tpb = 128;  // B: caller's env count, Bp: padded to whole warps (device stride)
   cudaStream_t stream = nullptr;
   cudaStream_t side[3] = {nullptr, nullptr, nullptr};  // chunk pipeline of the host-buffer calls
@@ -490,11 +487,6 @@ static void fill_kernel_params(UmpcBatch* b) {
   sm.dtsim = (float)p.dtsim; sm.hl_interval = (float)p.hlInterval; sm.taulim = p.taulim; sm.tpert = p.tpert;
   for (int i = 0; i < 3; ++i) sm.Ib[i] = p.Ib[i];
   sm.g = p.g; sm.mb = p.mb; sm.wl_mode = p.wlMode; sm.int_pos = p.intInitialPos;
-  sm.info_every_step = 0;
-  if (const char* ev = getenv("UMPC_INFO_EVERY_STEP")) sm.info_every_step = atoi(ev);
-  // start delay of the second warp per scheduler in multi-step rollouts (umpc_dev.cuh); tuning knob, microseconds
-  sm.stagger_ns = UMPC_DEFAULT_STAGGER_NS;
-  if (const char* ev = getenv("UMPC_STAGGER_US")) sm.stagger_ns = atoi(ev) * 1000;
   WlParams& w = b->wlp;
   memset(&w, 0, sizeof(w));
   memcpy(w.popts, p.wl_popts, sizeof(w.popts));
@@ -513,6 +505,12 @@ static size_t smem_bytes(int tpb) {
   static int pad = -1;
   if (pad < 0) { const char* e = getenv("UMPC_SMEM_PAD_FLOATS"); pad = e ? atoi(e) : 0; }
   return (size_t)(SM_FLOATS_PER_THREAD + pad) * tpb * sizeof(float);
+}
+
+extern "C" int umpcBatchSetRolloutInfo(UmpcBatch* b, int on) {
+  if (!b) return UMPC_ERR_ARG;
+  b->rollout_info = on != 0;
+  return UMPC_OK;
 }
 
 extern "C" int umpcBatchSetLaunch(UmpcBatch* b, int tpb) {
@@ -613,6 +611,7 @@ static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par)
     b->nsm = prop.multiProcessorCount;
   }
   b->tpb = UMPC_DEFAULT_TPB;
+  if (const char* ev = getenv("UMPC_ROLLOUT_INFO")) b->rollout_info = atoi(ev) != 0;
   if (const char* t = getenv("UMPC_TPB")) {  // tuning/testing knob: same values as umpcBatchSetLaunch
     const int v = atoi(t);
     if (v == 32 || v == 64 || v == 128 || v == 256) { b->tpb = v; b->tpb_user = true; }
@@ -1068,8 +1067,15 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
   } else if (!b->tpb_user) {
     // default rollout shape: ONE 8-warp CTA per SM (all 512 TMEM columns), warp-tiles dealt statically (umpc_dev.cuh)
     const int ntiles = b->Bp / 32, pgrid = ntiles < b->nsm ? ntiles : b->nsm;
-    umpc_rollout_kernel<256, SolverF32<256, DefStore<256>>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
-        b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+    // Solve info (residuals, status) and the un-scaled solution rows are NOT produced per rollout step unless asked for
+    // (umpcBatchSetRolloutInfo): nothing on this path reads them -- the reference never acts on them either
+    // (check_termination = 0, uprightmpc2.c:116-117) -- and the once-per-solve code is instruction-fetch bound.
+    if (b->rollout_info)
+      umpc_rollout_kernel<256, SolverF32<256, DefStore<256>>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
+          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+    else
+      umpc_rollout_kernel<256, SolverF32<256, DefStore<256>, false, false>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
+          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
   } else
   switch (tpb) {
     UMPC_LAUNCH_ROLLOUT(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_ROLLOUT(64, SmemStore<64>, smem_bytes(64))
