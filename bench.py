@@ -29,15 +29,21 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 NENV_PER_GPU = 65536
+# plant steps per launch of the fused rollout kernel = per bench "step": 125 x 0.2 ms = 25 ms of flight, so the default
+# K = 20 steps are exactly ONE config-3 flight (tend = 500 ms, 2,500 plant steps, uprightmpc2.py:87) of every env
+STEPS_PER_LAUNCH = 125
 METRIC = "closed-loop UprightMPC2 env-steps/s (MPC every step: = QP solves/s)"
 UNIT = "env-steps/s"
 
 
-def workload_config(n_gpus, nenv):
+def workload_config(n_gpus, nenv, spl=STEPS_PER_LAUNCH):
     return {"workload": "BASELINE configs[2]: %d-env closed-loop Monte Carlo per GPU (quadrotorNLDyn plant + UprightMPC2 "
                         "N=3, faithful C path: 10 Ruiz passes + refactor + 50 fixed-rho float32 ADMM iterations per "
-                        "env-step), perturbed controlTest ICs, hover task, hlInterval=None, dtsim=0.2 ms" % nenv,
+                        "env-step), perturbed controlTest ICs, hover task, hlInterval=None, dtsim=0.2 ms; one bench step = "
+                        "%d plant steps (each with its MPC solve) of every env in ONE launch of the fused rollout kernel "
+                        "(20 steps = one 500 ms flight)" % (nenv, spl),
             "envs_per_gpu": nenv, "envs_total": nenv * n_gpus, "mpc_every_step": True, "max_iter": 50,
+            "plant_steps_per_step": spl,
             "sharding": "contiguous env ranges per rank, no data-path collective; one all-reduce of 8 doubles at the end",
             "l2_policy": "per-step working set %.0f MB/GPU (SoA state of all envs) streams through L2 each step; "
                          "inputs are not re-used between steps except by the same env" % (nenv * 2172 / 1e6)}
@@ -91,7 +97,7 @@ def make_ics(nenv, seed):
 
 def fast_ics(nenv, seed):
     """config-3 ICs vectorised (65k rotations through the python loop of tests/util.py would take a minute)."""
-    from oracle.binding import control_test_ic
+    from robobee3d_b200.sweeps import control_test_ic
     rng = np.random.default_rng(seed)
     p0, R0, dq0 = control_test_ic()
     p = p0[None] + rng.normal(0, 5.0, (nenv, 3))
@@ -117,24 +123,34 @@ def run_reference(args):
     if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle_f32.so")):
         OB.build(ref=os.path.isdir("/root/reference"))
     cores = os.cpu_count() or 1
-    nenv = min(NENV_PER_GPU, cores * 256)  # bounded sample of the workload per step
-    p, R, dq = fast_ics(nenv, seed=0)
-    ics = np.concatenate([p, R.transpose(0, 2, 1).reshape(-1, 9), dq], axis=1)
-    # warm-up + timed: each "step" advances the sampled envs one closed-loop step on all cores
-    OB.cpu_env_steps(ics[: cores * 8], max(1, args.warmup), cores)
-    done, tmax, wall, kind = OB.cpu_env_steps(ics, args.steps, cores)
+    spl = args.steps_per_launch or STEPS_PER_LAUNCH
+    # bounded sample of the workload per step: 64 envs per core, each advanced the step's `spl` plant steps (~0.8 s of work
+    # per core and step at ~100 us per umpcUpdate)
+    nenv = min(NENV_PER_GPU, cores * 64)
+    ics = _cpu_ics(nenv)
+    # warm-up + timed: each "step" advances the sampled envs `spl` closed-loop plant steps on all cores
+    if args.warmup > 0:
+        OB.cpu_env_steps(ics[: cores * 8], max(1, args.warmup), cores)
+    done, tmax, wall, kind, per_core = OB.cpu_env_steps(ics, args.steps * spl, cores, per_worker=True)
     value = done / tmax
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.gpus, NENV_PER_GPU),
+            "config": workload_config(args.gpus, NENV_PER_GPU, spl),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                             "sample": "%d of %d envs x %d steps, one process per core (%s)" % (
-                                 nenv, NENV_PER_GPU, args.steps,
+                             "per_core": {"min": min(per_core), "median": sorted(per_core)[len(per_core) // 2], "max": max(per_core)},
+                             "seconds_per_worker": tmax,
+                             "sample": "%d of %d envs x %d plant steps (%d steps of %d), one process per core (%s)" % (
+                                 nenv, NENV_PER_GPU, args.steps * spl, args.steps, spl,
                                  "reference C sources compiled -O3, oracle/_ref" if kind == "reference" else "oracle port")},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
+
+
+def _cpu_ics(nenv):
+    p, R, dq = fast_ics(nenv, seed=0)
+    return np.concatenate([p, R.transpose(0, 2, 1).reshape(-1, 9), dq], axis=1)
 
 
 def _init_nccl(dist, torch, local):
@@ -188,6 +204,135 @@ def _dt_cpu_worker(job):
     return time.perf_counter() - t0, its
 
 
+def _np_dyn_step(p, R, dq, u, dt, Ib=np.array([3333.0, 3333.0, 1000.0]), g=9.81e-3):
+    """quadrotorNLDyn (genqp.py:24-41) in numpy for the config-1 loop below: explicit Euler, R <- R expm(skew(w) dt)"""
+    dv = u[0] * R[:, 2] - np.array([0, 0, g])
+    w = dq[3:]
+    dw = (-np.cross(w, Ib * w) + np.array([u[1], u[2], 0.0])) / Ib
+    k = w * dt
+    th = np.linalg.norm(k)
+    K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+    a, b = (1 - th * th / 6, 0.5 - th * th / 24) if th < 1e-4 else (np.sin(th) / th, (1 - np.cos(th)) / th ** 2)
+    return p + dt * dq[:3], R @ (np.eye(3) + a * K + b * (K @ K)), np.r_[dq[:3] + dt * dv, w + dt * dw]
+
+
+def run_small(args):
+    """BASELINE configs[0] and configs[1] (extra lines, not the driver's headline):
+    c1     : ONE controlTest flight (tend 500 ms, hlInterval 5 ms: ~96 controller calls) through the drop-in
+             uprightmpc2py.UprightMPC2C -- microseconds per update call of a batch of 1, next to the reference C call.
+    qp4096 : 4,096 independent UprightMPC2 QPs from random upright states, solve only: cold call + warm repeats."""
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from robobee3d_b200 import build as _build
+    _build.build()
+    clocks = ClockSampler(0)
+    clocks.start()
+    if args.workload == "c1":
+        from robobee3d_b200 import uprightmpc2py
+        from robobee3d_b200.sweeps import control_test_ic
+        from robobee3d_b200.batch import DEFAULTS as D
+        mk = lambda: uprightmpc2py.UprightMPC2C(D["dt"], D["g"], D["TtoWmax"], D["ws"], D["wds"], D["wpr"], D["wpf"], D["wvr"],
+                                                D["wvf"], D["wthrust"], D["wmom"], D["Ib"], D["maxIter"])
+
+        def flight(ctrl_update):
+            p, R, dq = control_test_ic()
+            uq, thl, calls, tsum = np.zeros(3), 0.0, [], 0.0
+            pdes, dpdes, sdes = np.zeros(3), np.zeros(3), np.array([0, 0, 1.0])
+            for ti in range(2500):
+                t = ti * 0.2
+                if t - thl > 5.0:
+                    t0 = time.perf_counter()
+                    uq, _ = ctrl_update(p, R, dq, pdes, dpdes, sdes)
+                    calls.append(time.perf_counter() - t0)
+                    uq = np.array(uq, float); thl = t
+                uq[1:] = np.clip(uq[1:], -100, 100)
+                p, R, dq = _np_dyn_step(p, R, dq, uq, 0.2)
+            return np.array(calls), p
+        up = mk()
+        flight(up.update)                     # warm-up flight (first launch, module load)
+        per_flight = []
+        for _ in range(max(1, args.steps)):
+            up = mk()
+            calls, pf = flight(up.update)
+            per_flight.append(calls)
+        calls = np.concatenate(per_flight)
+        line = {"metric": "microseconds per umpcUpdate of ONE controller (drop-in, batch of 1)", "value": 1e6 * float(np.median(calls)),
+                "unit": "us/update", "n_gpus": 1, "steps": args.steps, "warmup": 1, "ms_per_step": 1e3 * float(calls.sum()) / max(1, args.steps),
+                "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[0]: template/uprightmpc2.py controlTest(upc, 500, hlInterval=5), hover from the tilted IC, "
+                                       "%d controller calls per flight through uprightmpc2py.UprightMPC2C (ctypes -> umpcUpdate -> one 128-thread "
+                                       "CTA reading/writing a pinned mapped block)" % len(per_flight[0])},
+                "us_mean": 1e6 * float(calls.mean()), "us_p95": 1e6 * float(np.percentile(calls, 95)), "final_pos_norm_mm": float(np.linalg.norm(pf)),
+                "gpu_launches": int(len(calls)),
+                "e2e": {"value": 1e6 * float(np.median(calls)), "unit": "us/update", "h2d_bytes_per_step": 28 * 4, "d2h_bytes_per_step": (9 + 216) * 4,
+                        "note": "the call IS end to end: host arrays in, host arrays + UprightMPC_t.l/u/q/Px/Ax out"},
+                "roofline": {"bound": "latency", "achieved": None, "peak": None, "unit": "us", "frac": None, "traffic": None,
+                             "note": "a batch of 1 is the serial chain of one solve (~1.8e5 SM cycles) + launch + PCIe round trip; throughput "
+                                     "rooflines do not apply"}}
+        if not args.no_cpu:
+            from oracle import binding as OB
+            if OB.have_ref():
+                ref = OB.RefUMPC()
+                flight(lambda *a: ref.update(*a, -1.0))
+                ref = OB.RefUMPC()
+                rc, _ = flight(lambda *a: ref.update(*a, -1.0))
+                line["cpu_baseline"] = {"value": 1e6 * float(np.median(rc)), "unit": "us/update", "cores": 1, "kind": "reference",
+                                        "sample": "the same flight through the reference C umpcUpdate (oracle/_ref, -O2) via ctypes"}
+    else:
+        import util
+        from robobee3d_b200.batch import BatchUMPC
+        B = args.envs if args.envs != NENV_PER_GPU else 4096
+        p, R, dq = util.config2_states(B, seed=0)
+        Rc = np.ascontiguousarray(R.transpose(0, 2, 1).reshape(B, 9), np.float32)
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).cuda()
+        ins = [dev(p), dev(Rc), dev(dq), dev(np.zeros((B, 3))), dev(np.zeros((B, 3))), dev(np.tile([0, 0, 1.0], (B, 1)))]
+        aT0 = dev(np.full(B, 9.81e-3))
+        uq, acc = torch.empty(B, 3, device="cuda"), torch.empty(B, 6, device="cuda")
+        b = BatchUMPC(B)
+        cold, warm = [], []
+        for rep in range(max(3, args.warmup) + args.steps):
+            b.reset()
+            b.update_dev(uq, acc, *ins, aT0, stream=None); b.sync()
+            c = b.last_kernel_ms()
+            b.update_dev(uq, acc, *ins, None, stream=None); b.sync()
+            w = b.last_kernel_ms()
+            if rep >= max(3, args.warmup):
+                cold.append(c); warm.append(w)
+        # e2e: the same two calls with host buffers (umpcBatchUpdate)
+        z3 = np.zeros((B, 3), np.float32); e3 = np.tile(np.float32([0, 0, 1.0]), (B, 1))
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            b.update(p, R, dq, z3, z3, e3, np.full(B, 9.81e-3, np.float32))
+        te = (time.perf_counter() - t0) / args.steps
+        ms = float(np.median(warm))
+        line = {"metric": "UprightMPC2 QP solves/s (solve only, 4,096 independent QPs)", "value": B / (ms * 1e-3), "unit": "QP-solves/s",
+                "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[1]: %d independent UprightMPC2 QPs from random upright states (SURVEY 8d config 2), QP solve "
+                                       "only (umpcBatchUpdateDev, device-resident inputs): cold start, then one warm repeat; value = warm" % B,
+                           "l2_policy": "whole working set (%.1f MB) is L2 resident; every call re-reads its own state once" % (B * 1.5e-3)},
+                "cold_ms": float(np.median(cold)), "warm_ms": ms, "cold_solves_per_s": B / (float(np.median(cold)) * 1e-3),
+                "gpu_launches": 2 * args.steps,
+                "e2e": {"value": B / te, "unit": "QP-solves/s", "h2d_bytes_per_step": 28 * 4 * B, "d2h_bytes_per_step": 9 * 4 * B,
+                        "call": "umpcBatchUpdate with pageable host arrays"},
+                "roofline": {"bound": "latency", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                             "note": "4,096 QPs = 128 warps on 148 SMs x 8 warp slots: the launch is one solve's serial latency; "
+                                     "the GPU is ~11%% occupied -- see the 65,536-env line for the throughput regime"}}
+        if not args.no_cpu:
+            from oracle import binding as OB
+            cores = os.cpu_count() or 1
+            ics = np.concatenate([p, R.transpose(0, 2, 1).reshape(-1, 9), dq], axis=1)[: cores * 64]
+            done, tmax, _, kind = OB.cpu_env_steps(ics, 50, cores)
+            line["cpu_baseline"] = {"value": done / tmax, "unit": "QP-solves/s", "cores": cores, "kind": kind,
+                                    "sample": "%d of the QPs x 50 warm closed-loop solves, one process per core" % len(ics)}
+        b.close()
+    line["clocks"] = clocks.finish()
+    print(json.dumps(line))
+    return 0
+
+
 def run_dirtran(args):
     """BASELINE configs[4]: planar flapping dir-tran MPC (mpc_thrust_strokedev.py runSim(CTRL_MPC)), B envs x horizon N per
     GPU.  A step = `--dt-steps` closed-loop MPC periods of every env in ONE launch of dt_rollout_kernel (update -> 60 Euler
@@ -234,12 +379,28 @@ def run_dirtran(args):
     clocks = sampler.finish() if rank == 0 else None
     c1 = b.counters()
     its = c1["iters"] - c0["iters"]
+    # guards the uniform-register workaround of mpc_run: every lane must have done all its MPC periods
+    assert c1["solves"] - c0["solves"] == nenv * S * args.steps, ("dt_rollout_kernel lost solves", c1["solves"] - c0["solves"])
     t = torch.tensor([dev_ms * 1e-3, wall], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([its, c1["unsolved"] - c0["unsolved"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     dev_s, wall = float(t[0]), float(t[1])
+    # second regime: the TRANSIENT from the reference's own initial condition (mpc_thrust_strokedev.py:42,79: y0[3:6] = (1, 0, 10)),
+    # where a solve takes ~1.8x the iterations of the at-rest regime above; every timed launch restarts from it
+    ytr = ys.copy(); ytr[:, 3:6] += np.array([1.0, 0.0, 10.0])
+    tr_ms, tr_its = 0.0, 0.0
+    for _ in range(args.steps):
+        b.reset(); b.set_state(y=ytr, xr=xr)
+        ca = b.counters()
+        b.rollout(S)
+        tr_ms += b.last_kernel_ms()
+        tr_its += b.counters()["iters"] - ca["iters"]
+    ttr = torch.tensor([tr_ms * 1e-3, tr_its], dtype=torch.float64, device="cuda")
+    if world > 1:
+        m0 = ttr[0:1].clone(); dist.all_reduce(m0, op=dist.ReduceOp.MAX); dist.all_reduce(ttr, op=dist.ReduceOp.SUM); ttr[0] = m0[0]
+    b.reset(); b.set_state(y=ys, xr=xr)
     # e2e: LTVMPC.update through the C-ABI with host buffers (x0 in, u out), the call mpc_thrust_strokedev.py:171 makes
     e2e = None
     if not args.no_e2e:
@@ -267,7 +428,10 @@ def run_dirtran(args):
         its_all = float(cnt[0])
         bytes_per_it = (N + 1) * 76 * 8           # unique words per knot and iteration (factor 36 R, iterates 20 R + 20 W)
         ach = (its / args.steps) * bytes_per_it / (dev_s / args.steps) * 1e-9   # this rank's launch
-        line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s)", "value": nenv * world * S * args.steps / dev_s,
+        line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s), envs at rest about the hover goal (value) and in the "
+                          "transient from the reference's IC (value_transient)", "value": nenv * world * S * args.steps / dev_s,
+                "value_at_rest": nenv * world * S * args.steps / dev_s, "value_transient": nenv * world * S * args.steps / float(ttr[0]),
+                "iters_per_solve_transient": float(ttr[1]) / (nenv * world * S * args.steps),
                 "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": "BASELINE configs[4]: planar mpc_osqp flapping MPC (PlanarThrustStrokeDev, LTVMPC N=%d, OSQP eps 1e-5, "
@@ -305,6 +469,9 @@ def run_dirtran(args):
     return 0
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one umpc_rollout_kernel launch from the ncu --set full capture under profiles/
+# (key: envs, plant steps per launch); filled in from profiles/r02_ncu_full_umpc_rollout_kernel.txt
+ROLLOUT_TRAFFIC = {}
 # dram__bytes_read.sum + dram__bytes_write.sum of one dt_rollout_kernel launch from the ncu --set full captures under
 # profiles/ (key: envs, horizon, MPC periods per launch)
 DT_TRAFFIC = {(65536, 10, 10): 152.38e9}   # profiles/r01j_ncu_full_dt_rollout_kernel.txt: 110.69 GB read + 41.68 GB written
@@ -327,7 +494,7 @@ def main():
                     help="plant steps (each with an MPC solve when hlInterval is None) advanced per launch of the rollout kernel")
     ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
     ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
-    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran"],
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     ap.add_argument("--converged", action="store_true",
@@ -339,6 +506,8 @@ def main():
         return run_reference(args)
     if args.workload == "dirtran":
         return run_dirtran(args)
+    if args.workload in ("c1", "qp4096"):
+        return run_small(args)
 
     import torch
     import torch.distributed as dist
@@ -371,7 +540,7 @@ def main():
     if args.converged:
         kw.update(maxIter=4000, checkTermination=25, adaptiveRhoInterval=100)
         args.no_e2e = True
-    spl = 1  # plant steps per launch
+    spl = 1 if args.converged else STEPS_PER_LAUNCH  # plant steps per launch
     if args.hl_interval is not None:
         kw["hlInterval"] = args.hl_interval
         spl = int(np.floor(args.hl_interval / 0.2 + 1e-9)) + 1  # t - thlPrev > hlInterval on a 0.2 ms grid
@@ -421,19 +590,22 @@ def main():
         b2 = BatchUMPC(nenv, device=local)
         if args.tpb:
             b2.set_launch(args.tpb)
+        # one e2e "step" = the same `spl` env-steps of every env, each through umpcBatchEnvStep with host buffers
+        ne2e = spl if args.hl_interval is None else 1
         for _ in range(args.warmup):
             b2.env_step_raw(huq, hacc, hp, hR, hdq, hpd, hdp, hsd)
         barrier()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(args.steps * ne2e):
             b2.env_step_raw(huq, hacc, hp, hR, hdq, hpd, hdp, hsd)
         barrier()
         te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         assert torch.isfinite(hp).all()
-        e2e = {"value": nenv * world * args.steps / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 27 * 4 * nenv,
-               "d2h_bytes_per_step": 27 * 4 * nenv, "ms_per_step": 1e3 * float(te[0]) / args.steps,
+        e2e = {"value": nenv * world * args.steps * ne2e / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 27 * 4 * nenv * ne2e,
+               "d2h_bytes_per_step": 27 * 4 * nenv * ne2e, "ms_per_step": 1e3 * float(te[0]) / args.steps,
+               "calls_per_step": ne2e, "ms_per_call": 1e3 * float(te[0]) / (args.steps * ne2e), "gpu_launches": args.steps * ne2e,
                "call": "umpcBatchEnvStep (pinned host buffers read and written in place by one zero-copy kernel; umpcUpdate + clip + "
                        "quadrotorNLDyn per env)"}
         b2.close()
@@ -444,7 +616,10 @@ def main():
         solves_per_launch = spl if args.hl_interval is None else 1
         per_launch_flops = (solves_per_launch * fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
         launch_s = dev_s / args.steps
-        peak_tf = b.lib.umpcMeasureFp32Peak(local, 4096)
+        # FFMA microbenchmark in this process, right after the timed legs (same thermal / clock state): a long run
+        # (sustained, ~0.25 s: the denominator for a step that itself runs for tens of ms) and a short one (burst)
+        peak_burst = b.lib.umpcMeasureFp32Peak(local, 4096)
+        peak_tf = b.lib.umpcMeasureFp32Peak(local, 1 << 18)
         achieved_tf = per_launch_flops / launch_s * 1e-12
         peaks = {}
         try:
@@ -457,7 +632,8 @@ def main():
                     # profiles/r01e_ncu_full_umpc_rollout_kernel_tmem.txt (42.4 + 35.3 MB per launch of 65,536 envs; the
                     # algorithmic figure is 2,172 B x 65,536 = 142 MB -- part of the 96 MB state slab stays in the 126 MB L2
                     # from one launch to the next); only known for that launch shape
-                    "traffic": 77.7e6 if (nenv == 65536 and spl == 1 and args.workload == "mc" and not args.converged) else None,
+                    "traffic": ROLLOUT_TRAFFIC.get((nenv, spl)) if (args.workload == "mc" and not args.converged and args.hl_interval is None) else None,
+                    "peak_burst": peak_burst,
                     "kernel": "umpc_rollout_kernel",
                     "note": "FP32 CUDA-core pipe bound (arithmetic intensity %.0f flop/B vs ridge ~11): peak = FFMA "
                             "microbenchmark run in this process (MEASURED_PEAKS.json has no FP32 figure); achieved = "
@@ -471,7 +647,7 @@ def main():
         line = {"metric": METRIC, "value": spl * nenv * world * args.steps / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64" if args.converged else "f32", "data": "synthetic",
-                "config": dict(workload_config(world, nenv), **({} if args.workload == "mc" else {
+                "config": dict(workload_config(world, nenv, spl), **({} if args.workload == "mc" else {
                     "workload": "BASELINE configs[3] shape: %d-env cascade per GPU, UprightMPC2 -> %s -> actualT0 feedback every "
                                 "env-step (robobee_test_controllers.py:162-171), WaypointHover constants" % (
                                     nenv, "WLCon" if args.workload == "cascade-wlcon" else "true WLQP (40 iterations)")})),
@@ -489,13 +665,13 @@ def main():
         if world == 1 and not args.no_cpu:
             from oracle import binding as OB
             cores = os.cpu_count() or 1
-            ns = min(nenv, cores * 128)
-            pc, Rc, dqc = p[:ns], R[:ns], dq[:ns]
-            ics = np.concatenate([pc, Rc.transpose(0, 2, 1).reshape(-1, 9), dqc], axis=1)
-            steps_cpu = 20
-            done, tmax, _, kind = OB.cpu_env_steps(ics, steps_cpu, cores)
+            ns = min(nenv, cores * 64)
+            steps_cpu = 250                      # ~1.6 s per worker at ~100 us per umpcUpdate: ~25 core-seconds in all
+            done, tmax, _, kind, per_core = OB.cpu_env_steps(_cpu_ics(ns), steps_cpu, cores, per_worker=True)
             line["cpu_baseline"] = {"value": done / tmax, "unit": UNIT, "cores": cores, "kind": kind,
-                                    "sample": "%d of the %d envs x %d steps, one process per host core" % (ns, nenv, steps_cpu)}
+                                    "per_core": {"min": min(per_core), "median": sorted(per_core)[len(per_core) // 2], "max": max(per_core)},
+                                    "seconds_per_worker": tmax,
+                                    "sample": "%d of the %d envs x %d plant steps, one process per host core" % (ns, nenv, steps_cpu)}
         print(json.dumps(line))
     b.close()
     if world > 1:

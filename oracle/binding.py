@@ -308,7 +308,7 @@ def cpu_baseline_kind():
     return "reference" if os.path.exists(os.path.join(REF_DIR, "libref_umpc_f32_fast.so")) else "port"
 
 
-def cpu_env_steps(ics18, nsteps, procs):
+def cpu_env_steps(ics18, nsteps, procs, per_worker=False):
     """Advance the envs in ics18 (n x 18: p, R col-major, dq) nsteps closed-loop steps (hover, MPC every
     step) on `procs` host processes (one per core: the reference's OSQP workspace is a process global,
     template/uprightmpc2/workspace.c:2620, so threads cannot share it).  Returns (env_steps, seconds, kind)
@@ -327,6 +327,8 @@ def cpu_env_steps(ics18, nsteps, procs):
             res = pool.map(_cpu_worker, jobs)
     wall = time.perf_counter() - t0
     done = sum(r[0] for r in res)
+    if per_worker:  # + env-steps/s of every worker (one per core)
+        return done, max(r[1] for r in res), wall, kind, [r[0] / r[1] for r in res]
     return done, max(r[1] for r in res), wall, kind
 
 
