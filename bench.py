@@ -387,9 +387,9 @@ def run_dirtran(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     dev_s, wall = float(t[0]), float(t[1])
-    # second regime: the TRANSIENT from the reference's own initial condition (mpc_thrust_strokedev.py:42,79: y0[3:6] = (1, 0, 10)),
-    # where a solve takes ~1.8x the iterations of the at-rest regime above; every timed launch restarts from it
-    ytr = ys.copy(); ytr[:, 3:6] += np.array([1.0, 0.0, 10.0])
+    # second regime: the TRANSIENT -- the same envs with COLD controllers (no warm start, rho at its default): the first
+    # MPC periods after a reset take ~1.8x the iterations of the at-rest regime above; every timed launch restarts cold
+    ytr = ys
     tr_ms, tr_its = 0.0, 0.0
     for _ in range(args.steps):
         b.reset(); b.set_state(y=ytr, xr=xr)
@@ -429,7 +429,7 @@ def run_dirtran(args):
         bytes_per_it = (N + 1) * 76 * 8           # unique words per knot and iteration (factor 36 R, iterates 20 R + 20 W)
         ach = (its / args.steps) * bytes_per_it / (dev_s / args.steps) * 1e-9   # this rank's launch
         line = {"metric": "closed-loop planar dir-tran MPC env-steps/s (= QP solves/s), envs at rest about the hover goal (value) and in the "
-                          "transient from the reference's IC (value_transient)", "value": nenv * world * S * args.steps / dev_s,
+                          "transient right after a cold start of every controller (value_transient)", "value": nenv * world * S * args.steps / dev_s,
                 "value_at_rest": nenv * world * S * args.steps / dev_s, "value_transient": nenv * world * S * args.steps / float(ttr[0]),
                 "iters_per_solve_transient": float(ttr[1]) / (nenv * world * S * args.steps),
                 "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
