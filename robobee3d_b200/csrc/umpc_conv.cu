@@ -238,7 +238,7 @@ int umpc_conv_launch_rollout(UmpcConv* c, const SimParams* sim, const DevState* 
   const int grid = (s->B + c->tpb - 1) / c->tpb;
 #define UMPC_CONV_ROLLOUT(T)                                                                                              \
   case T:                                                                                                                 \
-    umpc_rollout_kernel<T, SolverF64><<<grid, T, 0, stream>>>(kp, *s, *wlp, step0, nsteps, fire, tvals, lg);             \
+    umpc_rollout_kernel<T, SolverF64><<<grid, T, 0, stream>>>(kp, *s, *wlp, step0, nsteps, fire, tvals, lg, 1);             \
     break;
   switch (c->tpb) { UMPC_CONV_ROLLOUT(64) UMPC_CONV_ROLLOUT(128) }
   return (int)cudaGetLastError();

@@ -72,6 +72,8 @@ struct KernelParamsT {
   SimParams sim;
 };
 
+#define UMPC_MAX_CHUNKED_TILES 512   // tiles per CTA up to which a launch's steps are cut into chunks (umpc_rollout_kernel)
+
 struct LogBuf {
   int env, cap;
   float *y, *u;  // [cap][12], [cap][3]
@@ -349,7 +351,7 @@ template <int TPB, class SOLVER>
 __global__ void __launch_bounds__(TPB, SOLVER::kMinBlocks)
 umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Params> kp, const __grid_constant__ DevState s,
                     const __grid_constant__ WlParams wlp, int step0, int nsteps, const uint8_t* __restrict__ fire,
-                    const double* __restrict__ tvals, LogBuf lg) {
+                    const double* __restrict__ tvals, LogBuf lg, int nch) {
   __shared__ uint32_t tmem_slot;
   const uint32_t scratch_base = SOLVER::template acquire<TPB>(&tmem_slot);
   // Warp-tiles (32 envs, one slab tile) are dealt to warps STATICALLY: tile t belongs to CTA t % gridDim.x, and inside the
@@ -357,9 +359,34 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   // (the default rollout shape) every SM gets ceil or floor of ntiles / nSM tiles -- 65,536 envs = 2,048 tiles = 13 or
   // 14 per SM -- instead of whole CTAs queueing behind each other (512 CTAs on 296 slots: 1.73 waves).  A grid of
   // ntiles / (TPB / 32) CTAs degenerates to one tile per warp.
+  // The steps of a launch are cut into nch chunks and the work items (tile j, chunk c), numbered c * ntile_cta + j, are
+  // handed to the warps of the CTA in that order, each warp taking the next number when it is free (a shared-memory
+  // counter): no warp slot idles while others work through a second tile (14 tiles on 8 slots left 2 of 8 slots idle for
+  // half the launch: 17 % of all warp samples were `barrier` in profiles/r02f).  Chunk c of a tile starts when chunk c - 1,
+  // done by another warp of the same CTA, has published the tile's state (global memory + a shared-memory counter).  Items
+  // are taken in increasing number and an item only waits for a lower one, so the lowest unfinished item never waits: no
+  // deadlock.  (A static round-robin deal was measured too: its last two warps have no slack on their predecessor, and a
+  // one-step difference in chunk length cost 16 %: profiles/r02_rollout_kernel_experiments.txt.)
   constexpr int WPC = TPB / 32;
   const int ntiles = s.B >> 5, warp = threadIdx.x >> 5;
-  for (int slot = warp; blockIdx.x + gridDim.x * slot < ntiles; slot += WPC) {
+  const int ntile_cta = ntiles > (int)blockIdx.x ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  __shared__ int tile_done[UMPC_MAX_CHUNKED_TILES];
+  __shared__ int next_item;
+  if (nch > 1) {
+    for (int i = threadIdx.x; i < ntile_cta; i += TPB) tile_done[i] = 0;
+    if (threadIdx.x == 0) next_item = WPC;   // items 0 .. WPC-1 are the warps' first ones
+    __syncthreads();
+  }
+  for (int item = warp; item < ntile_cta * nch;) {
+  const int chunk = item / ntile_cta, slot = item - chunk * ntile_cta;
+  // equal chunks, the remainder goes to the last one: items of different length in flight at the same time let the warps
+  // drift out of phase, and warps in different phases of the solve (Ruiz loop 21 KB + ADMM loop 15 KB of SASS) do not fit
+  // the 32 KB instruction cache together -- measured 0.190 ms per env-step against 0.158 in step (profiles/r02_*)
+  const int clen = nsteps / nch, k0 = chunk * clen, k1 = chunk == nch - 1 ? nsteps : k0 + clen;
+  if (chunk > 0) {
+    while (*(volatile int*)&tile_done[slot] < chunk) __nanosleep(100);
+    __syncwarp();
+  }
   const int e = ((blockIdx.x + gridDim.x * slot) << 5) + (threadIdx.x & 31);
   float* const eb = env_base(s, e);
   float p[3], R[9], dq[6], uq[3];
@@ -378,7 +405,7 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   float pert_done = eb[ROWF(ROW_METRICS + 4)];
   SOLVER sol;
   sol.init(scratch_base, s, e);
-  for (int k = 0; k < nsteps; ++k) {
+  for (int k = k0; k < k1; ++k) {
     const double t = tvals[k];
     if (task == SIM_TASK_HELIX && kp.sim.tpert >= 0.0f && t > (double)kp.sim.tpert && pert_done == 0.0f) {
       dq[1] += 2.0f; pert_done = 1.0f;
@@ -449,6 +476,16 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 5)] = cerr; eb[ROWF(ROW_METRICS + 6)] = ceff;
   ((int*)eb)[ROWF(ROW_METRICS + 2)] = nsolve; ((int*)eb)[ROWF(ROW_METRICS + 3)] = nstep;
   eb[ROWF(ROW_METRICS + 4)] = pert_done;
+  if (nch > 1) {   // publish the tile's state to the warp that runs its next chunk
+    __threadfence_block();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) *(volatile int*)&tile_done[slot] = chunk + 1;
+    int nxt = 0;
+    if ((threadIdx.x & 31) == 0) nxt = atomicAdd(&next_item, 1);
+    item = __shfl_sync(0xffffffffu, nxt, 0);
+  } else {
+    item += WPC;
+  }
   }
   SOLVER::template release<TPB>(&tmem_slot);
 }

@@ -595,8 +595,8 @@ static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par)
   CK(cudaMemset(b->d_in, 0, (size_t)28 * np * sizeof(float)));
   CK(cudaMalloc(&b->d_sums, 8 * sizeof(double)));
 #define UMPC_SET_SMEM(T)                                                                                                     \
-  CK(cudaFuncSetAttribute(umpc_update_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024))); \
-  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+  CK(cudaFuncSetAttribute(umpc_update_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024))); \
+  CK(cudaFuncSetAttribute(umpc_rollout_kernel<T, SolverF32<T, SmemStore<T>>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
   UMPC_SET_SMEM(32) UMPC_SET_SMEM(64)
   // hybrid TMEM + shared-memory scratch of the TMEM launch shapes (HybridStore): opt in to > 48 KB of dynamic shared memory
 #define UMPC_SET_HYB(K, T, ...)                                                                                               \
@@ -1059,23 +1059,31 @@ extern "C" int umpcBatchRollout(UmpcBatch* b, int nsteps) {
 #define UMPC_LAUNCH_ROLLOUT(T, ST, SMEM)                                                                              \
   case T:                                                                                                             \
     umpc_rollout_kernel<T, SolverF32<T, ST>><<<grid, T, SMEM, b->stream>>>(b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, \
-                                                             b->lg);                                                    \
+                                                             b->lg, 1);                                                 \
     break;
   if (b->s.wts) {
     umpc_rollout_kernel<128, SolverF32<128, DefStore<128>, true>><<<(b->Bp + 127) / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(
-        b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+        b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg, 1);
   } else if (!b->tpb_user) {
     // default rollout shape: ONE 8-warp CTA per SM (all 512 TMEM columns), warp-tiles dealt statically (umpc_dev.cuh)
     const int ntiles = b->Bp / 32, pgrid = ntiles < b->nsm ? ntiles : b->nsm;
+    // steps cut into chunks handed out over the 8 warps (umpc_dev.cuh) when the tiles do not fill the warp slots evenly:
+    // the smallest chunk count that makes (tiles per CTA) x chunks a multiple of 8
+    static int chunk_env = -1;
+    if (chunk_env < 0) { const char* ev = getenv("UMPC_ROLLOUT_CHUNKS"); chunk_env = ev ? atoi(ev) : 0; }
+    const int tiles_cta = (ntiles + pgrid - 1) / pgrid;
+    int nch = tiles_cta % 8 == 0 ? 1 : (tiles_cta % 4 == 0 ? 2 : (tiles_cta % 2 == 0 ? 4 : 8));
+    if (chunk_env > 0) nch = chunk_env;   // tuning knob
+    if (nsteps < 2 * nch || tiles_cta > UMPC_MAX_CHUNKED_TILES) nch = 1;
     // Solve info (residuals, status) and the un-scaled solution rows are NOT produced per rollout step unless asked for
     // (umpcBatchSetRolloutInfo): nothing on this path reads them -- the reference never acts on them either
     // (check_termination = 0, uprightmpc2.c:116-117) -- and the once-per-solve code is instruction-fetch bound.
     if (b->rollout_info)
       umpc_rollout_kernel<256, SolverF32<256, DefStore<256>>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
-          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg, nch);
     else
       umpc_rollout_kernel<256, SolverF32<256, DefStore<256>, false, false>><<<pgrid, 256, DefStore<256>::kSmemBytes, b->stream>>>(
-          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg);
+          b->kp, b->s, b->wlp, (int)b->step, nsteps, b->d_fire, b->d_t, b->lg, nch);
   } else
   switch (tpb) {
     UMPC_LAUNCH_ROLLOUT(32, SmemStore<32>, smem_bytes(32)) UMPC_LAUNCH_ROLLOUT(64, SmemStore<64>, smem_bytes(64))
