@@ -1,4 +1,5 @@
-"""Build libumpc_b200.so in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo)."""
+"""Build libumpc_b200.so in-tree with nvcc for sm_100a (no JIT cache).  The .so is git-ignored (the history stays
+source-only) but not gpurun-ignored: a built library travels to the GPU box with the working-tree snapshot."""
 import os
 import subprocess
 import sys
@@ -7,12 +8,14 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "umpc_kernels.cu")
 SRC_CONV = os.path.join(HERE, "csrc", "umpc_conv.cu")  # converged mode: the same device code in double
 SRC_DT = os.path.join(HERE, "csrc", "dirtran.cu")      # planar dir-tran MPC (config 5)
+SRC_UMG = os.path.join(HERE, "csrc", "umg.cu")        # any-N UprightMPC2 / fused MPC+WLQP QP builder on top of gqp
+SRC_GQP = os.path.join(HERE, "csrc", "gqp.cu")        # generic warp-per-QP OSQP (fused MPC+WLQP, any-N UprightMPC2, LTI quadcopter)
 OUT = os.path.join(HERE, "libumpc_b200.so")
-DEPS = [SRC, SRC_CONV, SRC_DT] + [os.path.join(HERE, "csrc", f) for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh",
+DEPS = [SRC, SRC_CONV, SRC_DT, SRC_GQP, SRC_UMG] + [os.path.join(HERE, "csrc", f) for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh",
                                                                    "umpc_dev.cuh", "umpc_conv.h", "dirtran_core.cuh")] + [
-    os.path.join(HERE, "..", "include", "umpc_b200.h"), os.path.join(HERE, "..", "include", "dirtran_b200.h")]
+    os.path.join(HERE, "..", "include", "umpc_b200.h"), os.path.join(HERE, "..", "include", "dirtran_b200.h"), os.path.join(HERE, "..", "include", "gqp_b200.h"), os.path.join(HERE, "..", "include", "umg_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
-              "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--threads", "3"]
+              "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--threads", "5"]
 
 
 def stale():
@@ -27,7 +30,7 @@ def build(force=False, verbose=False, defines=(), out=None):
     if out is None and not force and not stale():
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC, SRC_CONV, SRC_DT]
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC, SRC_CONV, SRC_DT, SRC_GQP, SRC_UMG]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
     if out is None:

@@ -1,0 +1,635 @@
+// robobee3d_b200/csrc/gqp.cu -- generic batched QP solver, ONE WARP PER QP (include/gqp_b200.h).
+//
+// OSQP 0.6.0's algorithm (the reference calls it through the `osqp` package: template_controllers.py:190-191,216-217,
+// uprightmpc2_withWLQP.py:243-244,283-284, planar/mpc_osqp.py:104-140) on a dense symmetric P and a sparse A whose CSR
+// pattern is shared by the batch:
+//   update_bounds / rho_vec by constraint type   osqp.c:784-832, auxil.c:103-146
+//   Ruiz equilibration + cost scaling            scaling.c:44-156
+//   ADMM step                                    auxil.c:164-228, proj.c:4-14
+//   residuals, termination, status               auxil.c:243-361,567-633,684-790
+//   adaptive rho                                 auxil.c:13-75, osqp.c:1270-1330
+//   solution un-scaling, NaN + cold start        scaling.c:177-192, auxil.c:527-562
+// Mapping: the warp keeps the packed Cholesky factor of the reduced system K = P_s + sigma I + A_s' diag(rho) A_s
+// (n(n+1)/2 doubles), the scaled A values and all ADMM vectors in SHARED memory; vectors are strided over the lanes,
+// norms are warp-shuffle reductions, the triangular solves are column sweeps with one __syncwarp per column.  The
+// scaled problem is never materialised in global memory: P_s = c D P D and A_s = E A D are applied on the fly from the
+// un-scaled data, so "re-scaling" costs no global writes.  Warm start (scaled x, z, y -- NOT rescaled when D, E change,
+// like the reference's workspace), D, E, c, rho and the constraint types persist per QP in global memory.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/umpc_b200.h"
+#include "../../include/gqp_b200.h"
+
+void umpc_internal_set_error(const char* msg);  // umpc_kernels.cu
+
+namespace gqp {
+
+// OSQP constants (constants.h:69-100)
+#define GQ_RHO_MIN 1e-6
+#define GQ_RHO_MAX 1e6
+#define GQ_RHO_EQ_OVER_RHO_INEQ 1e3
+#define GQ_RHO_TOL 1e-4
+#define GQ_MIN_SCALING 1e-4
+#define GQ_MAX_SCALING 1e4
+#define GQ_ST_SOLVED 1
+#define GQ_ST_SOLVED_INACCURATE 2
+#define GQ_ST_MAX_ITER (-2)
+#define GQ_ST_NON_CVX (-7)
+#define GQ_ST_UNSOLVED (-10)
+
+struct Dev {
+  GqpSettings s;
+  int nqp;
+  const int *rowptr, *colidx;           // CSR pattern of A
+  const int *colptr, *cscrow, *cscpos;  // CSC view: for column j the entries cscpos[k] (index into the CSR values), row cscrow[k]
+  // per-QP data (un-scaled), [nqp][...]
+  double *P, *Av, *q, *l, *u;
+  // per-QP persistent solver state
+  double *xs, *zs, *ys, *D, *E, *c, *rho;
+  int* ctype;
+  // results
+  double *x, *y, *info;
+};
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double limit_scaling(double v) {
+  v = v < GQ_MIN_SCALING ? 1.0 : v;
+  return v > GQ_MAX_SCALING ? GQ_MAX_SCALING : v;
+}
+__device__ __forceinline__ int tri(int i, int j) { return (i * (i + 1)) / 2 + j; }  // packed lower triangle, i >= j
+
+// shared-memory map of one warp (doubles)
+struct Smem {
+  double *L, *As, *x, *xt, *wv, *qs, *D, *invd, *tmp, *z, *y, *ls, *us, *rv, *zt, *E;
+  __device__ void carve(double* base, int n, int m, int nnz) {
+    L = base; base += (size_t)n * (n + 1) / 2;
+    As = base; base += nnz;
+    x = base; base += n; xt = base; base += n; wv = base; base += n; qs = base; base += n;
+    D = base; base += n; invd = base; base += n; tmp = base; base += n;
+    z = base; base += m; y = base; base += m; ls = base; base += m; us = base; base += m;
+    rv = base; base += m; zt = base; base += m; E = base; base += m;
+  }
+};
+__host__ __device__ inline size_t smem_doubles(int n, int m, int nnz) { return (size_t)n * (n + 1) / 2 + nnz + 7 * (size_t)n + 7 * (size_t)m; }
+
+// K = c D P D + sigma I + A_s' diag(rho) A_s (packed lower) and its Cholesky factor, in place in sm.L
+__device__ void form_and_factor(const Dev& d, const Smem& sm, const double* __restrict__ P, double c, int lane) {
+  const int n = d.s.n, m = d.s.m;
+  for (int i = 0; i < n; ++i) {
+    const double cdi = c * sm.D[i];
+    for (int j = lane; j <= i; j += 32) sm.L[tri(i, j)] = cdi * sm.D[j] * P[(size_t)i * n + j] + (i == j ? d.s.sigma : 0.0);
+  }
+  __syncwarp();
+  for (int r = lane; r < m; r += 32) {
+    const double rho = sm.rv[r];
+    for (int a = d.rowptr[r]; a < d.rowptr[r + 1]; ++a) {
+      const double ra = rho * sm.As[a];
+      const int ca = d.colidx[a];
+      for (int b = d.rowptr[r]; b <= a; ++b) atomicAdd(&sm.L[tri(ca, d.colidx[b])], ra * sm.As[b]);  // columns increase along a row
+    }
+  }
+  __syncwarp();
+  for (int k = 0; k < n; ++k) {
+    const double dk = sqrt(sm.L[tri(k, k)]);
+    const double inv = 1.0 / dk;
+    __syncwarp();
+    if (lane == 0) { sm.L[tri(k, k)] = dk; sm.invd[k] = inv; }
+    for (int i = k + 1 + lane; i < n; i += 32) sm.L[tri(i, k)] *= inv;
+    __syncwarp();
+    for (int i = k + 1 + lane; i < n; i += 32) {
+      const double lik = sm.L[tri(i, k)];
+      double* row = sm.L + tri(i, 0);
+      for (int j = k + 1; j <= i; ++j) row[j] -= lik * sm.L[tri(j, k)];
+    }
+    __syncwarp();
+  }
+}
+
+// sm.xt <- K^-1 sm.xt
+__device__ __forceinline__ void chol_solve(const Smem& sm, int n, int lane) {
+  for (int k = 0; k < n; ++k) {
+    __syncwarp();
+    const double wk = sm.xt[k] * sm.invd[k];
+    if (lane == 0) sm.wv[k] = wk;
+    for (int i = k + 1 + lane; i < n; i += 32) sm.xt[i] -= sm.L[tri(i, k)] * wk;
+  }
+  for (int k = n - 1; k >= 0; --k) {
+    __syncwarp();
+    const double xk = sm.wv[k] * sm.invd[k];
+    if (lane == 0) sm.xt[k] = xk;
+    const double* row = sm.L + tri(k, 0);
+    for (int j = lane; j < k; j += 32) sm.wv[j] -= row[j] * xk;
+  }
+  __syncwarp();
+}
+
+// per-row rho from the constraint type (set_rho_vec / update_rho_vec, auxil.c:77-146)
+__device__ __forceinline__ double rho_of(int type, double rho) {
+  return type == -1 ? GQ_RHO_MIN : (type == 1 ? GQ_RHO_EQ_OVER_RHO_INEQ * rho : rho);
+}
+
+// un-scaled residual norms and the scaled ones adaptive rho needs (update_info + check_termination, auxil.c:243-361,684-790;
+// compute_rho_estimate, auxil.c:13-75).  Uses sm.tmp / sm.zt as scratch.
+struct Resid {
+  double pri, dua, eps_pri_n, eps_dua_n;  // un-scaled residuals and the norms the relative tolerances multiply
+  double pri_s, pn_s, dua_s, dn_s;         // scaled quantities of the rho estimate
+};
+__device__ Resid residuals(const Dev& d, const Smem& sm, const double* __restrict__ P, double c, int lane) {
+  const int n = d.s.n, m = d.s.m;
+  Resid r;
+  double pri = 0, nz = 0, nAx = 0, pri_s = 0, pn_s = 0;
+  for (int i = lane; i < m; i += 32) {
+    double ax = 0;
+    for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) ax += sm.As[a] * sm.x[d.colidx[a]];
+    const double einv = 1.0 / sm.E[i], rp = ax - sm.z[i];
+    pri = fmax(pri, fabs(einv * rp)); nz = fmax(nz, fabs(einv * sm.z[i])); nAx = fmax(nAx, fabs(einv * ax));
+    pri_s = fmax(pri_s, fabs(rp)); pn_s = fmax(pn_s, fmax(fabs(sm.z[i]), fabs(ax)));
+  }
+  // tmp = D .* x  (for P_s x = c D (P (D x)))
+  for (int j = lane; j < n; j += 32) sm.tmp[j] = sm.D[j] * sm.x[j];
+  __syncwarp();
+  double dua = 0, nq = 0, nAty = 0, nPx = 0, dua_s = 0, dn_s = 0;
+  for (int j = lane; j < n; j += 32) {
+    double px = 0, aty = 0;
+    const double* prow = P + (size_t)j * n;
+    for (int i = 0; i < n; ++i) px += prow[i] * sm.tmp[i];
+    px *= c * sm.D[j];
+    for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) aty += sm.As[d.cscpos[k]] * sm.y[d.cscrow[k]];
+    const double dinv = 1.0 / sm.D[j], rd = sm.qs[j] + px + aty;
+    dua = fmax(dua, fabs(dinv * rd)); nq = fmax(nq, fabs(dinv * sm.qs[j])); nAty = fmax(nAty, fabs(dinv * aty)); nPx = fmax(nPx, fabs(dinv * px));
+    dua_s = fmax(dua_s, fabs(rd)); dn_s = fmax(dn_s, fmax(fabs(sm.qs[j]), fmax(fabs(aty), fabs(px))));
+  }
+  const double cinv = 1.0 / c;
+  r.pri = warp_max(pri); r.dua = cinv * warp_max(dua);
+  r.eps_pri_n = fmax(warp_max(nz), warp_max(nAx));
+  r.eps_dua_n = cinv * fmax(fmax(warp_max(nq), warp_max(nAty)), warp_max(nPx));
+  r.pri_s = warp_max(pri_s); r.pn_s = warp_max(pn_s); r.dua_s = warp_max(dua_s); r.dn_s = warp_max(dn_s);
+  return r;
+}
+
+__global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ Dev d, int rescale) {
+  extern __shared__ double smem_d[];
+  const int qp = blockIdx.x, lane = threadIdx.x;
+  if (qp >= d.nqp) return;
+  const int n = d.s.n, m = d.s.m, nnz = d.s.nnz;
+  Smem sm;
+  sm.carve(smem_d, n, m, nnz);
+  const double* P = d.P + (size_t)qp * n * n;
+  const double* Av = d.Av + (size_t)qp * nnz;
+  const double* q0 = d.q + (size_t)qp * n;
+  const double* l0 = d.l + (size_t)qp * m;
+  const double* u0 = d.u + (size_t)qp * m;
+  double* gD = d.D + (size_t)qp * n; double* gE = d.E + (size_t)qp * m;
+  int* gct = d.ctype + (size_t)qp * m;
+  double c = d.c[qp], rho = d.rho[qp];
+  const double INF = d.s.infty;
+  // ---- osqp_update_bounds with the OLD scaling: constraint types (auxil.c:103-146) ---------------------------------
+  for (int i = lane; i < m; i += 32) {
+    const double eo = gE[i];
+    const double lo = fmax(l0[i], -INF), hi = fmin(u0[i], INF);
+    const double ls = eo * lo, us = eo * hi;
+    int type;
+    if (ls < -INF * GQ_MIN_SCALING && us > INF * GQ_MIN_SCALING) type = -1;
+    else if (us - ls < GQ_RHO_TOL) type = 1;
+    else type = 0;
+    gct[i] = type;
+    sm.E[i] = eo;
+  }
+  for (int j = lane; j < n; j += 32) sm.D[j] = gD[j];
+  __syncwarp();
+  // ---- osqp_update_P_A: re-equilibrate (scale_data, scaling.c:44-156) ------------------------------------------------
+  if (rescale) {
+    for (int j = lane; j < n; j += 32) sm.D[j] = 1.0;
+    for (int i = lane; i < m; i += 32) sm.E[i] = 1.0;
+    c = 1.0;
+    __syncwarp();
+    // |P| (lower triangle) parked in the factor's space during the passes
+    for (int i = 0; i < n; ++i)
+      for (int j = lane; j <= i; j += 32) sm.L[tri(i, j)] = fabs(P[(size_t)i * n + j]);
+    __syncwarp();
+    for (int it = 0; it < d.s.scaling_iters; ++it) {
+      // column norms of [P_s; A_s], row norms of A_s with the current D, E, c
+      for (int j = lane; j < n; j += 32) {
+        double v = 0;
+        for (int i = 0; i < n; ++i) v = fmax(v, sm.L[i >= j ? tri(i, j) : tri(j, i)] * sm.D[i]);
+        v *= c * sm.D[j];
+        double va = 0;
+        for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) va = fmax(va, fabs(Av[d.cscpos[k]]) * sm.E[d.cscrow[k]]);
+        sm.tmp[j] = 1.0 / sqrt(limit_scaling(fmax(v, va * sm.D[j])));
+      }
+      for (int i = lane; i < m; i += 32) {
+        double v = 0;
+        for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) v = fmax(v, fabs(Av[a]) * sm.D[d.colidx[a]]);
+        sm.zt[i] = 1.0 / sqrt(limit_scaling(v * sm.E[i]));
+      }
+      __syncwarp();
+      for (int j = lane; j < n; j += 32) sm.D[j] *= sm.tmp[j];
+      for (int i = lane; i < m; i += 32) sm.E[i] *= sm.zt[i];
+      __syncwarp();
+      // cost normalisation (scaling.c:100-131): mean column norm of P_s, |q_s|_inf
+      double csum = 0, nq = 0;
+      for (int j = lane; j < n; j += 32) {
+        double v = 0;
+        for (int i = 0; i < n; ++i) v = fmax(v, sm.L[i >= j ? tri(i, j) : tri(j, i)] * sm.D[i]);
+        csum += c * sm.D[j] * v;
+        nq = fmax(nq, fabs(c * sm.D[j] * q0[j]));
+      }
+      csum = warp_sum(csum) / (double)n;
+      nq = limit_scaling(warp_max(nq));
+      double ct = limit_scaling(fmax(csum, nq));
+      c *= 1.0 / ct;
+      __syncwarp();
+    }
+    for (int j = lane; j < n; j += 32) gD[j] = sm.D[j];
+    for (int i = lane; i < m; i += 32) gE[i] = sm.E[i];
+  }
+  // ---- scaled data ---------------------------------------------------------------------------------------------------
+  for (int i = lane; i < m; i += 32) {
+    const double e = sm.E[i];
+    sm.ls[i] = e * fmax(l0[i], -INF); sm.us[i] = e * fmin(u0[i], INF);
+    sm.rv[i] = rho_of(gct[i], rho);
+    for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) sm.As[a] = e * Av[a] * sm.D[d.colidx[a]];
+    sm.z[i] = d.zs[(size_t)qp * m + i]; sm.y[i] = d.ys[(size_t)qp * m + i];
+  }
+  for (int j = lane; j < n; j += 32) { sm.qs[j] = c * sm.D[j] * q0[j]; sm.x[j] = d.xs[(size_t)qp * n + j]; }
+  __syncwarp();
+  form_and_factor(d, sm, P, c, lane);
+  // ---- ADMM (osqp.c:352-500) -----------------------------------------------------------------------------------------
+  const double alpha = d.s.alpha, sigma = d.s.sigma;
+  int iter = 0, status = GQ_ST_UNSOLVED, rho_updates = 0;
+  bool checked = false;
+  Resid res;
+  for (iter = 1; iter <= d.s.max_iter; ++iter) {
+    for (int j = lane; j < n; j += 32) {
+      double v = sigma * sm.x[j] - sm.qs[j];
+      for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) {
+        const int r = d.cscrow[k];
+        v += sm.As[d.cscpos[k]] * (sm.rv[r] * sm.z[r] - sm.y[r]);
+      }
+      sm.xt[j] = v;
+    }
+    chol_solve(sm, n, lane);
+    for (int i = lane; i < m; i += 32) {
+      double zt = 0;
+      for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) zt += sm.As[a] * sm.xt[d.colidx[a]];
+      const double rv = sm.rv[i], zi = sm.z[i], yi = sm.y[i];
+      const double zr = alpha * zt + (1.0 - alpha) * zi;
+      const double zn = fmin(fmax(zr + yi / rv, sm.ls[i]), sm.us[i]);
+      sm.y[i] = yi + rv * (zr - zn);
+      sm.z[i] = zn;
+    }
+    for (int j = lane; j < n; j += 32) sm.x[j] = alpha * sm.xt[j] + (1.0 - alpha) * sm.x[j];
+    __syncwarp();
+    checked = d.s.check_termination && (iter % d.s.check_termination == 0);
+    const bool adapt = d.s.adaptive_rho_interval && (iter % d.s.adaptive_rho_interval == 0);
+    if (checked || adapt) res = residuals(d, sm, P, c, lane);
+    if (checked) {
+      if (res.pri > INF || res.dua > INF) { status = GQ_ST_NON_CVX; break; }
+      if (res.pri < d.s.eps_abs + d.s.eps_rel * res.eps_pri_n && res.dua < d.s.eps_abs + d.s.eps_rel * res.eps_dua_n) { status = GQ_ST_SOLVED; break; }
+    }
+    if (adapt) {
+      const double pr = res.pri_s / (res.pn_s + 1e-10), dr = res.dua_s / (res.dn_s + 1e-10);
+      double est = rho * sqrt(pr / (dr + 1e-10));
+      est = fmin(fmax(est, GQ_RHO_MIN), GQ_RHO_MAX);
+      if (est > rho * d.s.adaptive_rho_tol || est < rho / d.s.adaptive_rho_tol) {
+        rho = est; ++rho_updates;
+        for (int i = lane; i < m; i += 32) sm.rv[i] = rho_of(gct[i], rho);
+        __syncwarp();
+        form_and_factor(d, sm, P, c, lane);
+      }
+    }
+  }
+  if (status == GQ_ST_UNSOLVED) {
+    iter = d.s.max_iter;
+    if (!checked) res = residuals(d, sm, P, c, lane);
+    if (res.pri > INF || res.dua > INF) status = GQ_ST_NON_CVX;
+    else if (res.pri < d.s.eps_abs + d.s.eps_rel * res.eps_pri_n && res.dua < d.s.eps_abs + d.s.eps_rel * res.eps_dua_n) status = GQ_ST_SOLVED;
+    else if (res.pri < 10 * d.s.eps_abs + 10 * d.s.eps_rel * res.eps_pri_n && res.dua < 10 * d.s.eps_abs + 10 * d.s.eps_rel * res.eps_dua_n)
+      status = GQ_ST_SOLVED_INACCURATE;
+    else status = GQ_ST_MAX_ITER;
+  }
+  // ---- store_solution (auxil.c:527-562) + persistent state -----------------------------------------------------------
+  const bool bad = status == GQ_ST_NON_CVX;
+  const double cinv = 1.0 / c;
+  for (int j = lane; j < n; j += 32) {
+    d.x[(size_t)qp * n + j] = bad ? nan("") : sm.D[j] * sm.x[j];
+    d.xs[(size_t)qp * n + j] = bad ? 0.0 : sm.x[j];
+  }
+  for (int i = lane; i < m; i += 32) {
+    d.y[(size_t)qp * m + i] = bad ? nan("") : sm.E[i] * sm.y[i] * cinv;
+    d.zs[(size_t)qp * m + i] = bad ? 0.0 : sm.z[i];
+    d.ys[(size_t)qp * m + i] = bad ? 0.0 : sm.y[i];
+  }
+  if (lane == 0) {
+    d.c[qp] = c; d.rho[qp] = rho;
+    double* inf = d.info + (size_t)qp * 6;
+    inf[0] = iter; inf[1] = status; inf[2] = res.pri; inf[3] = res.dua; inf[4] = rho; inf[5] = rho_updates;
+  }
+}
+
+// LTI closed loop (planar/mpc_osqp.py:131-140): x0 <- Ad x0 + Bd u0*, l[:nx] = u[:nx] = -x0
+__global__ void gqp_lti_advance_kernel(const __grid_constant__ Dev d, int nx, int nu, int u_off, const double* __restrict__ Ad,
+                                       const double* __restrict__ Bd, double* __restrict__ x0, double* __restrict__ ulog,
+                                       double* __restrict__ iters_sum) {
+  const int qp = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qp >= d.nqp) return;
+  const double* xs = d.x + (size_t)qp * d.s.n;
+  double* x = x0 + (size_t)qp * nx;
+  double xn[32];
+  for (int i = 0; i < nx; ++i) {
+    double v = 0;
+    for (int j = 0; j < nx; ++j) v += Ad[i * nx + j] * x[j];
+    for (int j = 0; j < nu; ++j) v += Bd[i * nu + j] * xs[u_off + j];
+    xn[i] = v;
+  }
+  for (int i = 0; i < nx; ++i) {
+    x[i] = xn[i];
+    d.l[(size_t)qp * d.s.m + i] = -xn[i];
+    d.u[(size_t)qp * d.s.m + i] = -xn[i];
+  }
+  if (ulog) for (int j = 0; j < nu; ++j) ulog[(size_t)qp * nu + j] = xs[u_off + j];
+  if (iters_sum) atomicAdd(iters_sum, d.info[(size_t)qp * 6]);
+}
+
+}  // namespace gqp
+
+// ================================ host side: C-ABI ============================================
+using gqp::Dev;
+
+#define GCK(call)                                                                         \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      umpc_internal_set_error((std::string(#call) + ": " + cudaGetErrorString(e_)).c_str()); \
+      return UMPC_ERR_CUDA;                                                               \
+    }                                                                                     \
+  } while (0)
+
+struct GqpBatch {
+  int nqp = 0, device = 0;
+  Dev d;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+  size_t smem = 0;
+  std::vector<void*> allocs;
+};
+
+extern "C" void gqpDefaults(GqpSettings* s, int n, int m, int nnz) {
+  memset(s, 0, sizeof(*s));
+  s->n = n; s->m = m; s->nnz = nnz;
+  s->max_iter = 4000; s->check_termination = 25; s->adaptive_rho_interval = 100; s->scaling_iters = 10;
+  s->rho = 0.1; s->sigma = 1e-6; s->alpha = 1.6; s->eps_abs = 1e-3; s->eps_rel = 1e-3; s->adaptive_rho_tol = 5.0;
+  s->infty = 1e30;
+}
+
+template <class T>
+static int galloc(GqpBatch* b, T** p, size_t count) {
+  GCK(cudaMalloc((void**)p, count * sizeof(T)));
+  b->allocs.push_back((void*)*p);
+  GCK(cudaMemsetAsync(*p, 0, count * sizeof(T), b->stream));
+  return UMPC_OK;
+}
+
+extern "C" void gqpBatchDestroy(GqpBatch* b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  if (b->stream) cudaStreamSynchronize(b->stream);
+  for (void* p : b->allocs) cudaFree(p);
+  if (b->ev0) cudaEventDestroy(b->ev0);
+  if (b->ev1) cudaEventDestroy(b->ev1);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  cudaGetLastError();
+  delete b;
+}
+
+__global__ void gqp_fill_kernel(double* p, size_t n, double v) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+static int gqp_fill(GqpBatch* b, double* p, size_t n, double v) {
+  gqp_fill_kernel<<<(unsigned)((n + 255) / 256 > 1184 ? 1184 : (n + 255) / 256), 256, 0, b->stream>>>(p, n, v);
+  GCK(cudaGetLastError());
+  return UMPC_OK;
+}
+
+extern "C" int gqpBatchReset(GqpBatch* b) {
+  if (!b) return UMPC_ERR_ARG;
+  GCK(cudaSetDevice(b->device));
+  const Dev& d = b->d;
+  const size_t B = b->nqp;
+  GCK(cudaMemsetAsync(d.xs, 0, B * d.s.n * 8, b->stream));
+  GCK(cudaMemsetAsync(d.zs, 0, B * d.s.m * 8, b->stream));
+  GCK(cudaMemsetAsync(d.ys, 0, B * d.s.m * 8, b->stream));
+  GCK(cudaMemsetAsync(d.ctype, 0, B * d.s.m * 4, b->stream));
+  int rc;
+  if ((rc = gqp_fill(b, d.D, B * d.s.n, 1.0))) return rc;
+  if ((rc = gqp_fill(b, d.E, B * d.s.m, 1.0))) return rc;
+  if ((rc = gqp_fill(b, d.c, B, 1.0))) return rc;
+  if ((rc = gqp_fill(b, d.rho, B, d.s.rho))) return rc;
+  GCK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+static int gqp_create_body(GqpBatch* b, const GqpSettings* s, const int* rowptr, const int* colidx) {
+  Dev& d = b->d;
+  memset(&d, 0, sizeof(d));
+  d.s = *s; d.nqp = b->nqp;
+  const int n = s->n, m = s->m, nnz = s->nnz;
+  GCK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  GCK(cudaEventCreate(&b->ev0));
+  GCK(cudaEventCreate(&b->ev1));
+  // CSC view of the pattern
+  std::vector<int> colptr(n + 1, 0), cscrow(nnz), cscpos(nnz);
+  for (int r = 0; r < m; ++r)
+    for (int a = rowptr[r]; a < rowptr[r + 1]; ++a) {
+      if (colidx[a] < 0 || colidx[a] >= n || (a > rowptr[r] && colidx[a] <= colidx[a - 1])) {
+        umpc_internal_set_error("gqpBatchCreate: bad CSR pattern (column out of range or not increasing inside a row)");
+        return UMPC_ERR_ARG;
+      }
+      colptr[colidx[a] + 1]++;
+    }
+  for (int j = 0; j < n; ++j) colptr[j + 1] += colptr[j];
+  {
+    std::vector<int> fillp(colptr.begin(), colptr.end() - 1);
+    for (int r = 0; r < m; ++r)
+      for (int a = rowptr[r]; a < rowptr[r + 1]; ++a) { const int k = fillp[colidx[a]]++; cscrow[k] = r; cscpos[k] = a; }
+  }
+  int *d_rowptr, *d_colidx, *d_colptr, *d_cscrow, *d_cscpos;
+  int rc;
+  if ((rc = galloc(b, &d_rowptr, m + 1)) || (rc = galloc(b, &d_colidx, nnz)) || (rc = galloc(b, &d_colptr, n + 1)) ||
+      (rc = galloc(b, &d_cscrow, nnz)) || (rc = galloc(b, &d_cscpos, nnz))) return rc;
+  GCK(cudaMemcpyAsync(d_rowptr, rowptr, (m + 1) * 4, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(d_colidx, colidx, nnz * 4, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(d_colptr, colptr.data(), (n + 1) * 4, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(d_cscrow, cscrow.data(), nnz * 4, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(d_cscpos, cscpos.data(), nnz * 4, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaStreamSynchronize(b->stream));  // the host vectors go out of scope
+  d.rowptr = d_rowptr; d.colidx = d_colidx; d.colptr = d_colptr; d.cscrow = d_cscrow; d.cscpos = d_cscpos;
+  const size_t B = b->nqp;
+  if ((rc = galloc(b, &d.P, B * n * n)) || (rc = galloc(b, &d.Av, B * nnz)) || (rc = galloc(b, &d.q, B * n)) ||
+      (rc = galloc(b, &d.l, B * m)) || (rc = galloc(b, &d.u, B * m)) || (rc = galloc(b, &d.xs, B * n)) ||
+      (rc = galloc(b, &d.zs, B * m)) || (rc = galloc(b, &d.ys, B * m)) || (rc = galloc(b, &d.D, B * n)) ||
+      (rc = galloc(b, &d.E, B * m)) || (rc = galloc(b, &d.c, B)) || (rc = galloc(b, &d.rho, B)) ||
+      (rc = galloc(b, &d.ctype, B * m)) || (rc = galloc(b, &d.x, B * n)) || (rc = galloc(b, &d.y, B * m)) ||
+      (rc = galloc(b, &d.info, B * 6))) return rc;
+  b->smem = gqp::smem_doubles(n, m, nnz) * sizeof(double);
+  if (b->smem > 227 * 1024) {
+    umpc_internal_set_error("gqpBatchCreate: QP too large for one warp's shared memory (n(n+1)/2 + nnz + 7n + 7m doubles <= 227 KB)");
+    return UMPC_ERR_ARG;
+  }
+  if (b->smem > 48 * 1024) GCK(cudaFuncSetAttribute(gqp::gqp_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem));
+  return gqpBatchReset(b);
+}
+
+extern "C" int gqpBatchCreate(GqpBatch** out, int nqp, int device, const GqpSettings* s, const int* rowptr, const int* colidx) {
+  if (!out || nqp <= 0 || !s || !rowptr || !colidx || s->n <= 0 || s->m <= 0 || s->nnz <= 0 || rowptr[s->m] != s->nnz) {
+    umpc_internal_set_error("gqpBatchCreate: bad argument");
+    return UMPC_ERR_ARG;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    umpc_internal_set_error((std::string("gqpBatchCreate: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path").c_str());
+    return UMPC_ERR_CUDA;
+  }
+  GCK(cudaSetDevice(device));
+  GqpBatch* b = new GqpBatch();
+  b->nqp = nqp; b->device = device;
+  const int rc = gqp_create_body(b, s, rowptr, colidx);
+  if (rc) { gqpBatchDestroy(b); return rc; }
+  *out = b;
+  return UMPC_OK;
+}
+
+__global__ void gqp_bcast_kernel(double* dst, size_t per, size_t nqp) {  // dst[0..per) replicated to every QP
+  const size_t tot = per * nqp;
+  for (size_t i = per + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < tot; i += (size_t)gridDim.x * blockDim.x) dst[i] = dst[i % per];
+}
+
+extern "C" int gqpBatchSetData(GqpBatch* b, const double* P, const double* Av, const double* q, const double* l, const double* u,
+                               int broadcast) {
+  if (!b) return UMPC_ERR_ARG;
+  GCK(cudaSetDevice(b->device));
+  const Dev& d = b->d;
+  struct { const double* h; double* dv; size_t per; } arr[5] = {{P, d.P, (size_t)d.s.n * d.s.n}, {Av, d.Av, (size_t)d.s.nnz},
+                                                                 {q, d.q, (size_t)d.s.n}, {l, d.l, (size_t)d.s.m}, {u, d.u, (size_t)d.s.m}};
+  for (auto& a : arr) {
+    if (!a.h) continue;
+    GCK(cudaMemcpyAsync(a.dv, a.h, a.per * (broadcast ? 1 : (size_t)b->nqp) * 8, cudaMemcpyHostToDevice, b->stream));
+    if (broadcast && b->nqp > 1) {
+      gqp_bcast_kernel<<<592, 256, 0, b->stream>>>(a.dv, a.per, (size_t)b->nqp);
+      GCK(cudaGetLastError());
+    }
+  }
+  GCK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+static int gqp_launch(GqpBatch* b, int rescale) {
+  gqp::gqp_solve_kernel<<<b->nqp, 32, b->smem, b->stream>>>(b->d, rescale);
+  GCK(cudaGetLastError());
+  return UMPC_OK;
+}
+
+extern "C" int gqpBatchSolve(GqpBatch* b, int rescale) {
+  if (!b) return UMPC_ERR_ARG;
+  GCK(cudaSetDevice(b->device));
+  GCK(cudaEventRecord(b->ev0, b->stream));
+  int rc = gqp_launch(b, rescale);
+  if (rc) return rc;
+  GCK(cudaEventRecord(b->ev1, b->stream));
+  b->timed = true;
+  return UMPC_OK;
+}
+
+extern "C" int gqpBatchSync(GqpBatch* b) {
+  if (!b) return UMPC_ERR_ARG;
+  GCK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+extern "C" float gqpBatchLastKernelMs(GqpBatch* b) {
+  if (!b || !b->timed) return -1.0f;
+  float ms = -1.0f;
+  if (cudaEventSynchronize(b->ev1) != cudaSuccess) return -1.0f;
+  cudaEventElapsedTime(&ms, b->ev0, b->ev1);
+  return ms;
+}
+
+extern "C" int gqpBatchGetSolution(GqpBatch* b, double* x, double* y, double* info) {
+  if (!b) return UMPC_ERR_ARG;
+  GCK(cudaSetDevice(b->device));
+  const Dev& d = b->d;
+  const size_t B = b->nqp;
+  if (x) GCK(cudaMemcpyAsync(x, d.x, B * d.s.n * 8, cudaMemcpyDeviceToHost, b->stream));
+  if (y) GCK(cudaMemcpyAsync(y, d.y, B * d.s.m * 8, cudaMemcpyDeviceToHost, b->stream));
+  if (info) GCK(cudaMemcpyAsync(info, d.info, B * 6 * 8, cudaMemcpyDeviceToHost, b->stream));
+  GCK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
+extern "C" void* gqpBatchDevPtr(GqpBatch* b, const char* name) {
+  if (!b || !name) return nullptr;
+  const Dev& d = b->d;
+  struct { const char* n; void* p; } tab[] = {{"P", d.P}, {"Av", d.Av}, {"q", d.q}, {"l", d.l}, {"u", d.u}, {"x", d.x}, {"y", d.y},
+                                              {"info", d.info}, {"stream", (void*)b->stream}};
+  for (auto& t : tab)
+    if (!strcmp(t.n, name)) return t.p;
+  return nullptr;
+}
+
+extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off, const double* Ad, const double* Bd, double* x0,
+                             double* u_log, double* iters_sum) {
+  if (!b || nsteps <= 0 || nx <= 0 || nx > 32 || nu <= 0 || !Ad || !Bd || !x0 || u_off < 0 || u_off + nu > b->d.s.n || nx > b->d.s.m) {
+    umpc_internal_set_error("gqpLtiRollout: bad argument (nx <= 32)");
+    return UMPC_ERR_ARG;
+  }
+  GCK(cudaSetDevice(b->device));
+  const size_t B = b->nqp;
+  double *dAd, *dBd, *dx0, *dul = nullptr, *dit = nullptr;
+  GCK(cudaMalloc(&dAd, (size_t)nx * nx * 8)); GCK(cudaMalloc(&dBd, (size_t)nx * nu * 8)); GCK(cudaMalloc(&dx0, B * nx * 8));
+  GCK(cudaMalloc(&dit, 8));
+  if (u_log) GCK(cudaMalloc(&dul, (size_t)nsteps * B * nu * 8));
+  GCK(cudaMemcpyAsync(dAd, Ad, (size_t)nx * nx * 8, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(dBd, Bd, (size_t)nx * nu * 8, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemcpyAsync(dx0, x0, B * nx * 8, cudaMemcpyHostToDevice, b->stream));
+  GCK(cudaMemsetAsync(dit, 0, 8, b->stream));
+  GCK(cudaEventRecord(b->ev0, b->stream));
+  int rc = UMPC_OK;
+  for (int k = 0; k < nsteps && !rc; ++k) {
+    rc = gqp_launch(b, 0);   // only the bounds changed: prob.update(l=l, u=u) (mpc_osqp.py:137-140)
+    if (rc) break;
+    gqp::gqp_lti_advance_kernel<<<(unsigned)((B + 127) / 128), 128, 0, b->stream>>>(b->d, nx, nu, u_off, dAd, dBd, dx0,
+                                                                                  dul ? dul + (size_t)k * B * nu : nullptr, dit);
+    if (cudaGetLastError() != cudaSuccess) rc = UMPC_ERR_CUDA;
+  }
+  cudaEventRecord(b->ev1, b->stream);
+  b->timed = true;
+  if (!rc) {
+    cudaMemcpyAsync(x0, dx0, B * nx * 8, cudaMemcpyDeviceToHost, b->stream);
+    if (u_log) cudaMemcpyAsync(u_log, dul, (size_t)nsteps * B * nu * 8, cudaMemcpyDeviceToHost, b->stream);
+    if (iters_sum) cudaMemcpyAsync(iters_sum, dit, 8, cudaMemcpyDeviceToHost, b->stream);
+  }
+  cudaStreamSynchronize(b->stream);
+  cudaFree(dAd); cudaFree(dBd); cudaFree(dx0); cudaFree(dit); cudaFree(dul);
+  if (cudaGetLastError() != cudaSuccess && !rc) rc = UMPC_ERR_CUDA;
+  return rc;
+}
