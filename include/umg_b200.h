@@ -43,6 +43,8 @@ void umgPattern(int N, int withWL, int *rowptr, int *colidx);
 int umgCreate(UmgBatch **out, int nenv, int device, const UmgParams *par);
 void umgDestroy(UmgBatch *b);
 int umgReset(UmgBatch *b);   /* T0 = 0, u0 = 0, cold solver */
+/* controller state: T0[B] (specific thrust), u0[B][4] (wing inputs of the fused WLQP); either may be NULL (= keep) */
+int umgSetState(UmgBatch *b, const double *T0, const double *u0);
 /* One update per environment, host arrays like umpcBatchUpdate: p0[B][3], R0[B][9] column-major, dq0[B][6], pdes[B][3],
  * dpdes[B][3], sdes[B][3], actualT0[B] or NULL (< 0: keep T0) -> uquad[B][3], accdes[B][6], u_wl[B][4] (withWL; may be NULL) */
 int umgUpdate(UmgBatch *b, double *uquad, double *accdes, double *u_wl, const double *p0, const double *R0, const double *dq0,

@@ -443,3 +443,36 @@ class RefPlanarQP:
 
 def have_ref_planar():
     return os.path.exists(os.path.join(HERE, "_ref", "libref_planar_f32.so"))
+
+
+# ---- generic OSQP object (oracle/gqp_oracle.c): checker of robobee3d_b200/csrc/gqp.cu -----------------------------------
+class OracleQP:
+    """setup once, then update(P, A, q, l, u) + solve like the reference's Python controllers call the osqp package
+    (template_controllers.py:190-191,216-217; uprightmpc2_withWLQP.py:243-244,283-284; planar/mpc_osqp.py:104-140).
+    Dense P (n, n), A (m, n).  P = A = None: only q / l / u change (no re-equilibration)."""
+
+    def __init__(self, n, m, eps=1e-4, rho=0.1, sigma=1e-6, alpha=1.6, max_iter=4000, check=25, adapt=100, tol=5.0, scaling=10,
+                 infty=1e30, flavour="f64"):
+        self.L = _private_copy(os.path.join(HERE, "liboracle_dt_%s.so" % flavour))
+        self.L.gqo_create.restype = C.c_void_p
+        self.L.gqo_create.argtypes = [C.c_int, C.c_int, DP]
+        self.L.gqo_destroy.argtypes = [C.c_void_p]
+        self.L.gqo_update_solve.argtypes = [C.c_void_p, DP, DP, DP, DP, DP, DP, DP, DP]
+        self.n, self.m = n, m
+        st = _d([eps, eps, rho, sigma, alpha, max_iter, check, adapt, tol, scaling, infty])
+        self.h = self.L.gqo_create(n, m, _p(st))
+        assert self.h, "QP larger than the oracle's caps"
+
+    def __del__(self):
+        try:
+            self.L.gqo_destroy(self.h)
+        except Exception:
+            pass
+
+    def update_solve(self, P, A, q, l, u):
+        x, y, info = np.zeros(self.n), np.zeros(self.m), np.zeros(6)
+        nul = C.cast(None, DP)
+        l = np.clip(_d(l, self.m), -1e300, 1e300); u = np.clip(_d(u, self.m), -1e300, 1e300)
+        self.L.gqo_update_solve(self.h, nul if P is None else _p(_d(P, self.n * self.n)), nul if A is None else _p(_d(A, self.m * self.n)),
+                                _p(_d(q, self.n)), _p(l), _p(u), _p(x), _p(y), _p(info))
+        return x, y, dict(iter=int(info[0]), status=int(info[1]), pri_res=info[2], dua_res=info[3], rho=info[4], rho_updates=int(info[5]))

@@ -301,6 +301,15 @@ extern "C" int umgReset(UmgBatch* b) {
   return gqpBatchReset(b->qp);
 }
 
+extern "C" int umgSetState(UmgBatch* b, const double* T0, const double* u0) {
+  if (!b) return UMPC_ERR_ARG;
+  UCK(cudaSetDevice(b->device));
+  if (T0) UCK(cudaMemcpyAsync(b->io.T0, T0, (size_t)b->nenv * 8, cudaMemcpyHostToDevice, b->stream));
+  if (u0) UCK(cudaMemcpyAsync(b->io.u0, u0, (size_t)b->nenv * 4 * 8, cudaMemcpyHostToDevice, b->stream));
+  UCK(cudaStreamSynchronize(b->stream));
+  return UMPC_OK;
+}
+
 static int umg_create_body(UmgBatch* b, const UmgParams* up) {
   umg::Par& p = b->par;
   memset(&p, 0, sizeof(p));

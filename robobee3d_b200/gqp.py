@@ -36,7 +36,7 @@ class UmgParams(C.Structure):
 
 GQP_EXPORTS = ["gqpDefaults", "gqpBatchCreate", "gqpBatchDestroy", "gqpBatchReset", "gqpBatchSetData", "gqpBatchSolve",
                "gqpBatchGetSolution", "gqpBatchSync", "gqpBatchLastKernelMs", "gqpBatchDevPtr", "gqpLtiRollout"]
-UMG_EXPORTS = ["umgDefaults", "umgSizes", "umgPattern", "umgCreate", "umgDestroy", "umgReset", "umgUpdate", "umgGetQP", "umgLastSolveMs"]
+UMG_EXPORTS = ["umgDefaults", "umgSizes", "umgPattern", "umgCreate", "umgDestroy", "umgReset", "umgSetState", "umgUpdate", "umgGetQP", "umgLastSolveMs"]
 
 _bound = False
 
@@ -72,6 +72,7 @@ def _bind():
     L.umgDestroy.argtypes = [vp]
     L.umgDestroy.restype = None
     L.umgReset.argtypes = [vp]
+    L.umgSetState.argtypes = [vp, DP, DP]
     L.umgUpdate.argtypes = [vp] + [DP] * 10
     L.umgGetQP.argtypes = [vp] + [DP] * 8
     L.umgLastSolveMs.argtypes = [vp]
@@ -224,6 +225,11 @@ class BatchUprightMPC2G:
 
     def reset(self):
         _lib.check(self.L.umgReset(self.h), "umgReset")
+
+    def set_state(self, T0=None, u0=None):
+        T0 = None if T0 is None else _d(T0, (self.B,))
+        u0 = None if u0 is None else _d(u0, (self.B, 4))
+        _lib.check(self.L.umgSetState(self.h, _p(T0), _p(u0)), "umgSetState")
 
     def update(self, p0, R0, dq0, pdes, dpdes, sdes, actualT0=None):
         """R0 (B,3,3) numpy row-major; returns uquad (B,3), accdes (B,6), u_wl (B,4) (zeros without the WLQP)"""

@@ -1,0 +1,185 @@
+"""GPU parity tests of the generic warp-per-QP solver (gqp) and the controllers on top of it (umg): SURVEY 8 rows
+a17 (fused MPC + WLQP single QP), a18 second instance (LTI quadcopter of planar/mpc_osqp.py) and f1 (UprightMPC2 for a
+horizon the C build does not ship), against fixtures produced by the reference's own Python functions
+(tests/golden/make_golden_gqp.py) and against the CPU oracle on fresh QPs."""
+import os
+
+import numpy as np
+import pytest
+
+import util
+from util import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return np.abs(np.asarray(a) - np.asarray(b)).max() / max(1.0, np.abs(b).max())
+
+
+def test_quad_kat_first_solve_and_closed_loop(cuda_required):
+    """planar/mpc_osqp.py: n = 92, m = 164, eps 1e-2, warm start; first solve and the 15-step closed loop (:117-140)"""
+    from robobee3d_b200.gqp import BatchQP, csr_pattern, mpc_osqp_problem
+    g = np.load(os.path.join(GOLDEN, "mpc_osqp_quad.npz"))
+    m = mpc_osqp_problem()
+    rp, ci = csr_pattern(m["A"])
+    B = 96
+    b = BatchQP(B, m["n"], m["m"], rp, ci, eps_abs=1e-2, eps_rel=1e-2, adaptive_rho_interval=25)
+    b.set_data(P=m["P"], Av=b.csr_values(m["A"]), q=m["q"], l=m["l"], u=m["u"], broadcast=True)
+    b.solve(rescale=True)
+    x, y, info = b.solution()
+    assert (info["status"] == 1).all() and (info["iter"] == int(g["iters"][0])).all()
+    assert _rel(x[0], g["x_first"]) <= 1e-7 and _rel(y[0], g["y_first"]) <= 1e-7
+    assert np.array_equal(x[0], x[B - 1])            # identical QPs -> identical warps
+    # closed loop: the first solve above is step 0's; roll the remaining plant/solve cycle on the device
+    b.reset()
+    b.set_data(P=m["P"], Av=b.csr_values(m["A"]), q=m["q"], l=m["l"], u=m["u"], broadcast=True)
+    b.solve(rescale=True)                             # prob.setup + first prob.solve (scaling fixed from here on)
+    x0 = np.tile(m["x0"], (B, 1))
+    nx, nu, N = m["nx"], m["nu"], m["N"]
+    u_off = m["n"] - N * nu
+    X = []
+    xs, _, _ = b.solution()
+    for i in range(15):
+        ctrl = xs[:, u_off:u_off + nu]
+        x0 = x0 @ m["Ad"].T + ctrl @ m["Bd"].T
+        X.append(x0[0].copy())
+        l, u = m["l"].copy(), m["u"].copy()
+        L = np.tile(l, (B, 1)); U = np.tile(u, (B, 1))
+        L[:, :nx] = -x0; U[:, :nx] = -x0
+        b.set_data(l=L, u=U)
+        b.solve(rescale=False)                        # prob.update(l=l, u=u)
+        xs, _, inf = b.solution()
+        if i < 14:
+            assert (inf["iter"] == int(g["iters"][i + 1])).all(), (i, inf["iter"][:3])
+    assert _rel(np.array(X), g["X"]) <= 1e-6
+    # the same loop fused on the device (gqpLtiRollout: solve -> x0 <- Ad x0 + Bd u -> bounds), from a fresh set-up
+    b.reset()
+    b.set_data(P=m["P"], Av=b.csr_values(m["A"]), q=m["q"], l=m["l"], u=m["u"], broadcast=True)
+    b.solve(rescale=True)     # prob.setup(...): fixes the scaling; its solution is recomputed by the loop's first solve
+    b.reset_iterates = None
+    xf, ul, its = b.lti_rollout(15, m["Ad"], m["Bd"], np.tile(m["x0"], (B, 1)), u_off, log_u=True)
+    assert _rel(xf[0], g["X"][-1]) <= 1e-4 and _rel(ul[:, 0], g["U"]) <= 1e-4
+    assert np.array_equal(xf[0], xf[B - 1])
+    b.close()
+
+
+def test_umpc_generic_horizon_matches_reference_functions(cuda_required):
+    """UprightMPC2 at N = 5 (nx = 75, nc = 65): QP data equal to template_controllers.py's own initConstraint /
+    updateConstraint / updateObjective, solution equal to the float64 OSQP oracle's, same iteration counts"""
+    from robobee3d_b200.gqp import BatchUprightMPC2G
+    g = np.load(os.path.join(GOLDEN, "umpc_genN.npz"))
+    N, B = int(g["N"]), g["p"].shape[0]
+    b = BatchUprightMPC2G(B, N=N)
+    assert (b.nx, b.nc) == (g["P"].shape[1], g["A"].shape[1])
+    uq, acc, _ = b.update(g["p"], g["R"], g["dq"], g["pdes"], g["dpdes"], g["sdes"], g["T0"])
+    qp = b.qp()
+    from robobee3d_b200.gqp import umg_pattern
+    rp, ci = umg_pattern(N)
+    rows = np.repeat(np.arange(b.nc), np.diff(rp))
+    for e in range(B):
+        assert (np.count_nonzero(g["A"][e]) <= b.nnz)
+        assert _rel(qp["Av"][e], g["A"][e][rows, ci]) <= 1e-13
+        A = np.zeros_like(g["A"][e]); A[rows, ci] = qp["Av"][e]
+        assert np.array_equal(A != 0, g["A"][e] != 0)
+        for k in ("P", "q", "l", "u"):
+            assert _rel(qp[k][e], g[k][e]) <= 1e-13, (e, k)
+    assert (qp["status"] == 1).all()
+    assert (qp["iter"] == g["iter"].astype(int)).all(), (qp["iter"], g["iter"])
+    assert _rel(qp["x"], g["x"]) <= 1e-7
+    # outputs: uquad = (T0 + x[2 N ny], ...), accdes from dy1 (template_controllers.py:239-251)
+    assert _rel(uq[:, 0], g["T0"] + g["x"][:, 2 * N * 6]) <= 1e-7
+    b.close()
+
+
+def test_umpc_generic_n3_matches_converged_kernel(cuda_required):
+    """N = 3 through the warp-per-QP solver = the thread-per-QP converged-mode kernel (umpc_conv.cu) = the reference's
+    float64 OSQP golden (tests/golden/umpc_conv.npz)"""
+    from robobee3d_b200.gqp import BatchUprightMPC2G
+    gold = np.load(os.path.join(GOLDEN, "umpc_seq.npz"))
+    conv = np.load(os.path.join(GOLDEN, "umpc_conv.npz"))
+    B = gold["p"].shape[0]
+    b = BatchUprightMPC2G(B, N=3)
+    b.update(gold["p"][:, 0], gold["R"][:, 0], gold["dq"][:, 0], gold["pdes"][:, 0], gold["dpdes"][:, 0], gold["sdes"][:, 0], gold["aT0"][:, 0])
+    qp = b.qp()
+    tol = 10 * 1e-4 + 1e-4 * np.abs(conv["x"]).max(axis=1)
+    assert (np.abs(qp["x"] - conv["x"]).max(axis=1) <= tol).all()
+    assert (qp["iter"] == conv["iter"]).mean() >= 0.9    # float32 golden inputs vs float64 here: counts may differ at a threshold
+    b.close()
+
+
+def test_fused_mpc_wlqp_matches_reference_class(cuda_required):
+    """a17: template/uprightmpc2_withWLQP.py's UprightMPC2 (nx = 49, nc = 43, dense P blocks, eps 1e-7), 12 controllers x 4
+    consecutive updates: QP data, solution, uquad / accdes / u0 / T0 against the reference's own class run on the
+    float64 OSQP oracle"""
+    from robobee3d_b200.gqp import BatchUprightMPC2G, umg_pattern
+    g = np.load(os.path.join(GOLDEN, "fused_wlqp.npz"))
+    d = util.load_constants()
+    B, ncall = g["p"].shape[:2]
+    b = BatchUprightMPC2G(B, N=3, withWL=True)
+    assert (b.nx, b.nc) == (49, 43)
+    b.set_state(u0=g["u0_init"])
+    rp, ci = umg_pattern(3, True)
+    rows = np.repeat(np.arange(b.nc), np.diff(rp))
+    for c in range(ncall):
+        uq, acc, uwl = b.update(g["p"][:, c], g["R"][:, c], g["dq"][:, c], g["pdes"][:, c], g["dpdes"][:, c], g["sdes"][:, c])
+        qp = b.qp()
+        # call 0: identical inputs -> data to rounding; later calls inherit T0 += x[36], u0 += du of solves that stopped at
+        # max_iter (status -2) in BOTH implementations -- iterates agree, but only to the conditioning of a 4000-iteration path
+        tol_data = 1e-12 if c == 0 else 1e-5
+        for e in range(B):
+            A = g["A"][e, c]
+            assert np.array_equal(np.nonzero(A)[1], ci) or c > 0
+            assert _rel(qp["Av"][e], A[rows, ci]) <= tol_data, (c, e)
+            for k in ("P", "q", "l", "u"):
+                assert _rel(qp[k][e], g[k][e, c]) <= tol_data, (c, e, k)
+        if c == 0:
+            assert (qp["iter"] == g["iter"][:, 0].astype(int)).all(), (qp["iter"], g["iter"][:, 0])
+            assert (qp["status"] == g["status"][:, 0].astype(int)).all()
+        solved = g["status"][:, c] == 1
+        tol_x = 1e-5 if c == 0 else 1e-3
+        assert _rel(qp["x"][solved], g["x"][solved, c]) <= tol_x, (c, _rel(qp["x"][solved], g["x"][solved, c]))
+        assert np.abs(uq[solved] - g["uquad"][solved, c]).max() <= tol_x * max(1.0, np.abs(g["x"][:, c]).max())
+        assert np.abs(uwl[solved] - g["u0"][solved, c]).max() <= tol_x * max(1.0, np.abs(g["u0"][:, c]).max())
+        assert np.isfinite(qp["x"]).all()
+    b.close()
+
+
+def test_gqp_random_qps_match_oracle(cuda_required):
+    """fresh random strictly convex QPs (dense P, sparse A with equality, inequality and loose rows): solution and
+    iteration count against the CPU oracle, through two updates (rescale, then bounds only)"""
+    from oracle import binding as OB
+    from robobee3d_b200.gqp import BatchQP, csr_pattern
+    rng = np.random.default_rng(3)
+    n, m, B = 20, 26, 40
+    mask = rng.uniform(size=(m, n)) < 0.25
+    mask[np.arange(m), rng.integers(0, n, m)] = True
+    rp, ci = csr_pattern(mask)
+    b = BatchQP(B, n, m, rp, ci, eps_abs=1e-6, eps_rel=1e-6)
+    Ps, As, qs, ls, us = [], [], [], [], []
+    for e in range(B):
+        M = rng.normal(size=(n, n)); P = M @ M.T / n + 0.1 * np.eye(n)
+        A = rng.normal(size=(m, n)) * mask
+        xf = rng.normal(size=n); c = A @ xf
+        l, u = c - rng.uniform(0.1, 1, m), c + rng.uniform(0.1, 1, m)
+        l[:5] = u[:5] = c[:5]                     # equalities
+        l[5:8] = -np.inf; u[5:8] = np.inf         # loose rows
+        Ps.append(P); As.append(A); qs.append(rng.normal(size=n)); ls.append(l); us.append(u)
+    Ps, As, qs, ls, us = map(np.array, (Ps, As, qs, ls, us))
+    b.set_data(P=Ps, Av=b.csr_values(As), q=qs, l=ls, u=us)
+    b.solve(rescale=True)
+    x1, y1, i1 = b.solution()
+    ls2, us2 = ls + 0.05, us + 0.05
+    ls2[:, :5] = us2[:, :5]
+    b.set_data(l=ls2, u=us2)
+    b.solve(rescale=False)
+    x2, y2, i2 = b.solution()
+    for e in range(0, B, 4):
+        o = OB.OracleQP(n, m, eps=1e-6)
+        xo, yo, io = o.update_solve(Ps[e], As[e], qs[e], ls[e], us[e])
+        assert io["status"] == 1 and i1["status"][e] == 1
+        assert i1["iter"][e] == io["iter"], (e, i1["iter"][e], io["iter"])
+        assert _rel(x1[e], xo) <= 1e-7 and _rel(y1[e], yo) <= 1e-6
+        xo2, yo2, io2 = o.update_solve(None, None, qs[e], ls2[e], us2[e])
+        assert i2["iter"][e] == io2["iter"] and _rel(x2[e], xo2) <= 1e-7
+    b.close()
