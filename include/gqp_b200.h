@@ -61,7 +61,8 @@ void *gqpBatchDevPtr(GqpBatch *b, const char *name);
  * x0 <- Ad x0 + Bd u0*, l[:nx] = u[:nx] = -x0, solve again: nsteps closed-loop steps of every QP of the batch on the
  * device.  Ad[nx*nx], Bd[nx*nu] row-major; x0[nqp][nx] in/out; the first-input block of x sits at u_off. */
 int gqpLtiRollout(GqpBatch *b, int nsteps, int nx, int nu, int u_off, const double *Ad, const double *Bd, double *x0,
-                  double *u_log /* [nsteps][nqp][nu] or NULL */, double *iters_sum /* or NULL */);
+                  double *u_log /* [nsteps][nqp][nu] or NULL */, double *iters_sum /* or NULL */,
+                  int rescale_first /* 1: the first solve equilibrates (prob.setup + first solve) */);
 
 #ifdef __cplusplus
 }

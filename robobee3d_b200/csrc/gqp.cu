@@ -597,7 +597,7 @@ extern "C" void* gqpBatchDevPtr(GqpBatch* b, const char* name) {
 }
 
 extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off, const double* Ad, const double* Bd, double* x0,
-                             double* u_log, double* iters_sum) {
+                             double* u_log, double* iters_sum, int rescale_first) {
   if (!b || nsteps <= 0 || nx <= 0 || nx > 32 || nu <= 0 || !Ad || !Bd || !x0 || u_off < 0 || u_off + nu > b->d.s.n || nx > b->d.s.m) {
     umpc_internal_set_error("gqpLtiRollout: bad argument (nx <= 32)");
     return UMPC_ERR_ARG;
@@ -615,7 +615,7 @@ extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off,
   GCK(cudaEventRecord(b->ev0, b->stream));
   int rc = UMPC_OK;
   for (int k = 0; k < nsteps && !rc; ++k) {
-    rc = gqp_launch(b, 0);   // only the bounds changed: prob.update(l=l, u=u) (mpc_osqp.py:137-140)
+    rc = gqp_launch(b, k == 0 && rescale_first);   // later steps: only the bounds changed, prob.update(l=l, u=u) (mpc_osqp.py:137-140)
     if (rc) break;
     gqp::gqp_lti_advance_kernel<<<(unsigned)((B + 127) / 128), 128, 0, b->stream>>>(b->d, nx, nu, u_off, dAd, dBd, dx0,
                                                                                   dul ? dul + (size_t)k * B * nu : nullptr, dit);

@@ -1,4 +1,4 @@
-"""ctypes bindings of the generic warp-per-QP solver (include/gqp_b200.h) and of the horizon-generic / fused-WLQP
+"""ctypes wrappers of the generic warp-per-QP solver (include/gqp_b200.h) and of the horizon-generic / fused-WLQP
 UprightMPC2 controller on top of it (include/umg_b200.h).
 
     BatchQP                 B QPs sharing A's sparsity pattern: set_data / solve / solution (OSQP semantics, float64)
@@ -61,7 +61,7 @@ def _bind():
     L.gqpBatchLastKernelMs.restype = C.c_float
     L.gqpBatchDevPtr.argtypes = [vp, C.c_char_p]
     L.gqpBatchDevPtr.restype = vp
-    L.gqpLtiRollout.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, DP, DP, DP, DP, DP]
+    L.gqpLtiRollout.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, DP, DP, DP, DP, DP, C.c_int]
     L.umgDefaults.argtypes = [C.POINTER(UmgParams), C.c_int, C.c_int]
     L.umgDefaults.restype = None
     L.umgSizes.argtypes = [C.c_int, C.c_int, IP, IP, IP]
@@ -163,13 +163,13 @@ class BatchQP:
     def last_kernel_ms(self):
         return float(self.L.gqpBatchLastKernelMs(self.h))
 
-    def lti_rollout(self, nsteps, Ad, Bd, x0, u_off, log_u=False):
+    def lti_rollout(self, nsteps, Ad, Bd, x0, u_off, log_u=False, rescale_first=False):
         """planar/mpc_osqp.py:131-140 on the device: solve, x0 <- Ad x0 + Bd u0*, l[:nx] = u[:nx] = -x0, nsteps times"""
         nx, nu = Bd.shape
         x0 = _d(x0, (self.B, nx)).copy()
         ul = np.empty((nsteps, self.B, nu)) if log_u else None
         its = np.zeros(1)
-        _lib.check(self.L.gqpLtiRollout(self.h, int(nsteps), nx, nu, int(u_off), _p(_d(Ad)), _p(_d(Bd)), _p(x0), _p(ul), _p(its)),
+        _lib.check(self.L.gqpLtiRollout(self.h, int(nsteps), nx, nu, int(u_off), _p(_d(Ad)), _p(_d(Bd)), _p(x0), _p(ul), _p(its), int(bool(rescale_first))),
                    "gqpLtiRollout")
         return x0, ul, float(its[0])
 

@@ -25,11 +25,22 @@ Ib = np.diag([3333.0, 3333.0, 1000.0])  # genqp.py:22
 
 class UprightMPC2:
     def __init__(self, N, dt, g, TtoWmax, ws, wds, wpr, wpf, wvr, wvf, wthrust, wmom, Ib, device=0):
-        if N != 3:
-            raise ValueError("the generated device code is the N = 3 instance the reference ships (uprightmpc2.h:12)")
         self.N, self.dt, self.g, self.Tmax = N, dt, g, TtoWmax * g
-        self._b = BatchUMPC(1, device=device, dt=dt, g=g, TtoWmax=TtoWmax, ws=ws, wds=wds, wpr=wpr, wpf=wpf, wvr=wvr,
-                            wvf=wvf, wthrust=wthrust, wmom=wmom, Ib=tuple(np.asarray(Ib, float).ravel()), **OSQP_DEFAULTS)
+        ib = tuple(np.asarray(Ib, float).ravel())
+        if N == 3:
+            # the generated thread-per-QP device code is the N = 3 instance the reference ships (uprightmpc2.h:19-25)
+            self._b = BatchUMPC(1, device=device, dt=dt, g=g, TtoWmax=TtoWmax, ws=ws, wds=wds, wpr=wpr, wpf=wpf, wvr=wvr,
+                                wvf=wvf, wthrust=wthrust, wmom=wmom, Ib=ib, **OSQP_DEFAULTS)
+            self._g = None
+        else:
+            # any other horizon: the warp-per-QP generic solver (gqp.cu) behind the same QP functions
+            from .gqp import BatchUprightMPC2G
+            self._g = BatchUprightMPC2G(1, N=N, device=device, dt=dt, g=g, TtoWmax=TtoWmax, ws=ws, wds=wds, wpr=wpr, wpf=wpf,
+                                        wvr=wvr, wvf=wvf, wthrust=wthrust, wmom=wmom, Ib=ib, maxIter=OSQP_DEFAULTS["maxIter"],
+                                        checkTermination=OSQP_DEFAULTS["checkTermination"],
+                                        adaptiveRhoInterval=OSQP_DEFAULTS["adaptiveRhoInterval"], epsAbs=OSQP_DEFAULTS["epsAbs"],
+                                        epsRel=OSQP_DEFAULTS["epsRel"])
+            self._b = self._g
         self.T0 = 0.0
         self.prevsol = np.zeros(N * (2 * ny + nu))
         self.obj_val = None
@@ -38,10 +49,14 @@ class UprightMPC2:
     def update(self, p0, R0, dq0, pdes, dpdes, sdes, actualT0):
         # an edit of self.T0 between calls is honoured like the reference's attribute (template_controllers.py:239-241)
         a = actualT0 if actualT0 >= 0 else (self.T0 if self.T0 != self._setT0 else -1.0)
-        uq, acc = self._b.update(np.asarray(p0, float)[None], np.asarray(R0, float)[None], np.asarray(dq0, float)[None],
-                                 np.asarray(pdes, float)[None], np.asarray(dpdes, float)[None], np.asarray(sdes, float)[None],
-                                 np.array([a], np.float32))
-        s = self._b.solve_info(full=True)
+        args = (np.asarray(p0, float)[None], np.asarray(R0, float)[None], np.asarray(dq0, float)[None],
+                np.asarray(pdes, float)[None], np.asarray(dpdes, float)[None], np.asarray(sdes, float)[None])
+        if self._g is not None:
+            uq, acc, _ = self._g.update(*args, np.array([a], float))
+            s = self._g.qp()
+        else:
+            uq, acc = self._b.update(*args, np.array([a], np.float32))
+            s = self._b.solve_info(full=True)
         self.prevsol = s["x"][0].astype(float)
         self.info = dict(iter=int(s["iter"][0]), status=int(s["status"][0]), pri_res=float(s["pri_res"][0]),
                          dua_res=float(s["dua_res"][0]))

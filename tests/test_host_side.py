@@ -211,3 +211,29 @@ def test_c_program_links_against_the_library(tmp_path):
                "-lumpc_b200", "-Wl,-rpath," + libdir], str(tmp_path / "link_check"))
     out = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
     assert "libumpc_b200.so" in out
+
+
+def test_gqp_and_umg_headers_are_exported_and_refuse_without_device():
+    """include/gqp_b200.h and include/umg_b200.h: every declared symbol is exported and listed by the Python wrapper; the
+    pattern / size helpers (host arithmetic of the QP's structure, no compute) agree with the reference's shapes"""
+    from robobee3d_b200 import _lib, gqp
+    L = gqp._bind()
+    for hdr, lst in (("gqp_b200.h", gqp.GQP_EXPORTS), ("umg_b200.h", gqp.UMG_EXPORTS)):
+        src = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", hdr)).read(), flags=re.S)
+        decl = sorted(set(re.findall(r"^\s*(?:const\s+)?(?:void|int|float|double|char)\s*\*?\s*(\w+)\s*\(", src, flags=re.M)))
+        assert decl == sorted(lst), (hdr, decl, sorted(lst))
+        assert all(hasattr(L, s) for s in decl)
+    # shipped instance N = 3: nx 45, nc 39, nnz 111 (uprightmpc2.h:20-25, workspace.c); fused: 49 / 43 (uprightmpc2.h.withWLQP:20-51)
+    assert gqp.umg_sizes(3) == (45, 39, 111) and gqp.umg_sizes(3, True) == (49, 43, 115)
+    rp, ci = gqp.umg_pattern(3)
+    gold = np.load(os.path.join(GOLDEN, "umpc_genN.npz"))
+    rp5, ci5 = gqp.umg_pattern(int(gold["N"]))
+    A = gold["A"][0]
+    rows = np.repeat(np.arange(A.shape[0]), np.diff(rp5))
+    off = A.copy(); off[rows, ci5] = 0
+    assert not off.any() and (A[rows, ci5] != 0).sum() >= len(ci5) - 3     # pattern of template_controllers.initConstraint at N = 5
+    if not util.has_cuda():
+        with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
+            gqp.BatchQP(2, 45, 39, rp, ci)
+        with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
+            gqp.BatchUprightMPC2G(2, N=5)
