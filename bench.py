@@ -333,6 +333,117 @@ def run_small(args):
     return 0
 
 
+def gqp_flops(n, m, nnz, iters, scaling_iters=10, refactors=1):
+    """executed-algorithm flops of one gqp solve (gqp.cu): Ruiz passes, K formation + dense Cholesky, ADMM iterations"""
+    ruiz = scaling_iters * (4 * n * n + 6 * nnz + 8 * n + 4 * m)
+    factor = refactors * (n * n + n ** 3 / 3.0 + 6 * nnz)
+    it = 2 * n * n + 8 * nnz + 12 * m + 6 * n
+    return ruiz + factor + iters * it
+
+
+def run_gqp(args):
+    """Extra lines (not the driver's headline) for the rows that run on the generic warp-per-QP solver:
+    quad       : BASELINE configs[4]'s namesake -- the LTI quadcopter MPC of planar/mpc_osqp.py (n = 92, m = 164), B
+                 closed loops of 15 steps each on the device (gqpLtiRollout); value = QP solves/s
+    fused-wlqp : BASELINE configs[3]'s single-QP variant -- uprightmpc2_withWLQP (nx = 49, nc = 43, eps 1e-7): one
+                 umgUpdate of B controllers per step (host buffers: the call IS the e2e number; value = the solve kernel alone)
+    umpc-n     : UprightMPC2 at horizon --horizon through the same path (f1)"""
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import util
+    from robobee3d_b200 import build as _build, _lib
+    from robobee3d_b200 import gqp as G
+    _build.build()
+    L = _lib.load()
+    clocks = ClockSampler(0)
+    clocks.start()
+    B = args.envs if args.envs != NENV_PER_GPU else (16384 if args.workload == "quad" else 32768)
+    if args.workload == "quad":
+        m = G.mpc_osqp_problem()
+        rp, ci = G.csr_pattern(m["A"])
+        b = G.BatchQP(B, m["n"], m["m"], rp, ci, eps_abs=1e-2, eps_rel=1e-2, adaptive_rho_interval=25)
+        rng = np.random.default_rng(0)
+        x0 = np.tile(m["x0"], (B, 1)); x0[:, 2] = rng.uniform(-0.5, 0.5, B); x0[:, :2] = rng.uniform(-0.1, 0.1, (B, 2))
+        u_off, nst = m["n"] - m["N"] * m["nu"], 15
+        ms, its = [], []
+        for rep in range(max(3, args.warmup) + args.steps):
+            b.reset()
+            l, u = np.tile(m["l"], (B, 1)), np.tile(m["u"], (B, 1)); l[:, :12] = -x0; u[:, :12] = -x0
+            b.set_data(P=m["P"], Av=b.csr_values(m["A"]), q=m["q"], broadcast=True)
+            b.set_data(l=l, u=u)
+            xf, _, it = b.lti_rollout(nst, m["Ad"], m["Bd"], x0, u_off, rescale_first=True)
+            if rep >= max(3, args.warmup):
+                ms.append(b.last_kernel_ms()); its.append(it)
+        assert np.isfinite(xf).all()
+        msm, itm = float(np.median(ms)), float(np.median(its)) / (B * nst)
+        n_, m_, nnz = m["n"], m["m"], len(ci)
+        fl = B * nst * gqp_flops(n_, m_, nnz, itm, refactors=1.0 / nst, scaling_iters=10.0 / nst)
+        name, unit, solves = "LTI quadcopter MPC (planar/mpc_osqp.py) QP solves/s", "QP-solves/s", B * nst
+        cfgw = "planar/mpc_osqp.py:29-140: n = 92, m = 164, eps 1e-2, warm start; %d closed loops x %d steps per launch sequence, initial states perturbed per loop" % (B, nst)
+        e2e = None
+        oracle_job = ("quad", m)
+    else:
+        wl = args.workload == "fused-wlqp"
+        N = 3 if wl else args.horizon
+        p, R, dq = util.config2_states(B, seed=0)
+        z3, e3 = np.zeros((B, 3)), np.tile([0, 0, 1.0], (B, 1))
+        b = G.BatchUprightMPC2G(B, N=N, withWL=wl)
+        ms, wall, its = [], [], []
+        for rep in range(max(3, args.warmup) + args.steps):
+            b.reset()
+            t0 = time.perf_counter()
+            uq, acc, uwl = b.update(p, R, dq, z3, z3, e3, np.full(B, 9.81e-3))
+            t1 = time.perf_counter() - t0
+            if rep >= max(3, args.warmup):
+                ms.append(b.last_solve_ms()); wall.append(t1); its.append(float(b.qp()["iter"].mean()) if rep == max(3, args.warmup) else its[-1])
+        assert np.isfinite(uq).all()
+        msm, itm = float(np.median(ms)), its[0]
+        n_, m_, nnz = b.nx, b.nc, b.nnz
+        fl = B * gqp_flops(n_, m_, nnz, itm, refactors=1 + itm / 400.0)
+        name = ("fused UprightMPC2 + WLQP single QP (uprightmpc2_withWLQP) solves/s" if wl else "UprightMPC2 N=%d QP solves/s (generic horizon)" % N)
+        unit, solves = "QP-solves/s", B
+        cfgw = ("template/uprightmpc2_withWLQP.py: nx = 49, nc = 43, dense P blocks, eps 1e-7, max_iter 4000; " if wl else
+                "template_controllers.UprightMPC2(N=%d): nx = %d, nc = %d, eps 1e-4; " % (N, n_, m_)) + "%d controllers, cold start, config-2 random upright states" % B
+        e2e = {"value": B / float(np.median(wall)), "unit": unit, "h2d_bytes_per_step": 28 * 8 * B, "d2h_bytes_per_step": 13 * 8 * B,
+               "call": "umgUpdate with host arrays (build kernel + warp-per-QP solve + extract kernel inside)"}
+        oracle_job = None
+    peak64 = L.umpcMeasureFp64Peak(0, 1 << 16)
+    ach = fl / (msm * 1e-3) * 1e-12
+    line = {"metric": name, "value": solves / (msm * 1e-3), "unit": unit, "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": msm, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": cfgw, "l2_policy": "every QP's data is read once per solve; state (<= 100 MB) is L2 resident"},
+            "iters_per_solve": itm, "gpu_launches": args.steps * (15 if args.workload == "quad" else 3),
+            "roofline": {"bound": "fp64", "achieved": ach, "peak": peak64, "unit": "TFLOP/s", "frac": ach / peak64, "traffic": None,
+                         "kernel": "gqp_solve_kernel",
+                         "note": "one warp per QP, factor and vectors in shared memory: the column sweeps of the triangular solves are "
+                                 "__syncwarp-latency bound, not pipe bound; peak = DFMA microbenchmark in this process"}}
+    if e2e:
+        line["e2e"] = e2e
+    if not args.no_cpu and oracle_job:
+        from oracle import binding as OB
+        mm = oracle_job[1]
+        t0 = time.perf_counter(); nq = 0
+        for e in range(8):
+            o = OB.OracleQP(mm["n"], mm["m"], eps=1e-2, adapt=25)
+            l, u = mm["l"].copy(), mm["u"].copy(); xx = x0[e].copy()
+            l[:12] = -xx; u[:12] = -xx
+            xs, _, _ = o.update_solve(mm["P"], mm["A"], mm["q"], l, u)
+            for k in range(14):
+                xx = mm["Ad"] @ xx + mm["Bd"] @ xs[u_off:u_off + 4]; l[:12] = -xx; u[:12] = -xx
+                xs, _, _ = o.update_solve(None, None, mm["q"], l, u)
+            nq += 15
+        dtc = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": nq / dtc, "unit": unit, "cores": 1, "kind": "port",
+                                "sample": "8 of the loops x 15 steps through the oracle's dense OSQP restatement on one core (the reference's "
+                                          "solver here is the un-vendored osqp wheel)"}
+    line["clocks"] = clocks.finish()
+    print(json.dumps(line))
+    b.close()
+    return 0
+
+
 def run_dirtran(args):
     """BASELINE configs[4]: planar flapping dir-tran MPC (mpc_thrust_strokedev.py runSim(CTRL_MPC)), B envs x horizon N per
     GPU.  A step = `--dt-steps` closed-loop MPC periods of every env in ONE launch of dt_rollout_kernel (update -> 60 Euler
@@ -494,7 +605,7 @@ def main():
                     help="plant steps (each with an MPC solve when hlInterval is None) advanced per launch of the rollout kernel")
     ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
     ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
-    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096"],
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096", "quad", "fused-wlqp", "umpc-n"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     ap.add_argument("--converged", action="store_true",
@@ -508,6 +619,8 @@ def main():
         return run_dirtran(args)
     if args.workload in ("c1", "qp4096"):
         return run_small(args)
+    if args.workload in ("quad", "fused-wlqp", "umpc-n"):
+        return run_gqp(args)
 
     import torch
     import torch.distributed as dist

@@ -230,6 +230,8 @@ int umpcBatchSetRolloutInfo(UmpcBatch *b, int on);
 int umpcBatchSetLaunch(UmpcBatch *b, int threads_per_block);
 /* FP32 FMA-pipe peak of the device, measured with a register-resident FFMA loop (TFLOP/s) */
 double umpcMeasureFp32Peak(int device, int iters);
+/* FP64 pipe peak, DFMA loop (TFLOP/s): the roofline denominator of the float64 kernels (converged mode, dir-tran, gqp) */
+double umpcMeasureFp64Peak(int device, int iters);
 
 #ifdef __cplusplus
 }

@@ -65,7 +65,7 @@ EXPORTS = [
     "umpcBatchUpdate", "umpcBatchEnvStep", "umpcBatchUpdateDev", "umpcBatchUpdateDevOn", "umpcBatchGetSolve", "umpcBatchGetQPData", "umpcBatchSetState",
     "umpcBatchGetState", "umpcBatchRollout", "umpcBatchGetMetrics", "umpcBatchReduceMetrics", "umpcBatchSetLog",
     "umpcBatchGetLog", "umpcBatchSync", "umpcBatchDevPtr", "umpcBatchSetWeights", "umpcBatchLastKernelMs", "umpcBatchTimerStart", "umpcBatchTimerStopMs", "umpcBatchSetLaunch", "umpcBatchSetRolloutInfo",
-    "umpcMeasureFp32Peak",
+    "umpcMeasureFp32Peak", "umpcMeasureFp64Peak",
 ]
 
 _lib = None
@@ -113,6 +113,8 @@ def load():
     L.umpcBatchSetWeights.argtypes = [vp, vp]
     L.umpcMeasureFp32Peak.argtypes = [C.c_int, C.c_int]
     L.umpcMeasureFp32Peak.restype = C.c_double
+    L.umpcMeasureFp64Peak.argtypes = [C.c_int, C.c_int]
+    L.umpcMeasureFp64Peak.restype = C.c_double
     f = C.c_float
     L.umpcInit.argtypes = [C.POINTER(UprightMPC_t)] + [f] * 11 + [FP, C.c_int]
     L.umpcInit.restype = None

@@ -394,6 +394,24 @@ __global__ void fp32_peak_kernel(float* out, int iters) {
   if (sacc == 12345.678f) out[0] = sacc;
 }
 
+// ---- kernel 5b: FP64 pipe peak (independent DFMA chains in registers) -----------------------
+__global__ void fp64_peak_kernel(double* out, int iters) {
+  double a[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a[i] = 1.0 + 1e-3 * (threadIdx.x + i);
+  const double m = 0.999, c = 1e-3;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = fma(a[i], m, c);
+  }
+  double sacc = 0.0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sacc += a[i];
+  if (sacc == 12345.678) out[0] = sacc;
+}
+
 // ================================ host side: C-ABI ============================================
 static thread_local std::string g_err;
 static int set_err(const char* what, cudaError_t e) {
@@ -1178,6 +1196,31 @@ extern "C" double umpcMeasureFp32Peak(int device, int iters) {
     cudaEventElapsedTime(&ms, e0, e1);
     const double flop = 2.0 * 16 * 8 * (double)iters * grid * tpb;
     const double tf = flop / (ms * 1e-3) * 1e-12;
+    if (tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  return best;
+}
+
+extern "C" double umpcMeasureFp64Peak(int device, int iters) {
+  if (cudaSetDevice(device) != cudaSuccess) return -1.0;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1.0;
+  double* d = nullptr;
+  if (cudaMalloc(&d, 8) != cudaSuccess) return -1.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int grid = prop.multiProcessorCount * 8, tpb = 256;
+  fp64_peak_kernel<<<grid, tpb>>>(d, 16);
+  double best = 0.0;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0);
+    fp64_peak_kernel<<<grid, tpb>>>(d, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double tf = 2.0 * 8 * 8 * (double)iters * grid * tpb / (ms * 1e-3) * 1e-12;
     if (tf > best) best = tf;
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
