@@ -124,7 +124,18 @@ UMPC_HD ureal umpc_limit_scaling(ureal v) {
 
 // sigma / D_j^2 pairs share one scratch word.  float build: two bf16 halves (8 significant bits, full float range);
 // double build: two floats.  The term is ~1e-6 of the diagonal of K, and it multiplies xh and (xh - xt) only.
-#ifdef UMPC_REAL_IS_FLOAT
+#if defined(UMPC_SG_FULL) && !defined(__CUDA_ARCH__)
+// A/B aid of the HOST build only (tests/hostcheck, -DUMPC_SG_FULL): the pairs keep their full precision in a side table and
+// the scratch word carries the table index -- shows what the bf16 packing of the device build costs (tests/test_host_side.py)
+static thread_local ureal umpc_sg_tab[2048][2];
+static thread_local int umpc_sg_n = 0;
+UMPC_HD ureal umpc_pack2(ureal a, ureal b) {
+  const int i = umpc_sg_n++ & 2047;
+  umpc_sg_tab[i][0] = a; umpc_sg_tab[i][1] = b;
+  return (ureal)i;
+}
+UMPC_HD void umpc_unpack2(ureal w, ureal& a, ureal& b) { a = umpc_sg_tab[(int)w][0]; b = umpc_sg_tab[(int)w][1]; }
+#elif defined(UMPC_REAL_IS_FLOAT)
 UMPC_HD ureal umpc_pack2(ureal a, ureal b) {
   union { float f; unsigned u; } ua, ub, r;
   ua.f = a; ub.f = b;

@@ -34,8 +34,8 @@ def make_par(d, f64=False):
 
 
 class HostUMPC:
-    def __init__(self, defaults, f64=False):
-        self.lib = C.CDLL(os.path.join(HERE, 'libhostcheck64.so' if f64 else 'libhostcheck.so'))
+    def __init__(self, defaults, f64=False, lib=None):
+        self.lib = C.CDLL(os.path.join(HERE, lib or ('libhostcheck64.so' if f64 else 'libhostcheck.so')))
         self.par = make_par(defaults, f64)
         self.np, self.P = (np.float64, C.POINTER(C.c_double)) if f64 else (np.float32, C.POINTER(C.c_float))
         self.creal = C.c_double if f64 else C.c_float

@@ -61,10 +61,16 @@ def test_batch_update_matches_reference_golden(cuda_required, gold):
         # accdes = (x[18:24] - dq0)/dt: same absolute tolerance as x, divided by dt
         assert np.abs(acc - gold["accdes"][:, c]).max() <= TOL_X_REL * np.abs(gold["x"][:, c]).max() / 5.0
         assert (s["iter"] == 50).all()
-        # status is a threshold test on residuals; allow disagreement only where the reference's
-        # residual is within 5% of its threshold -> simply require >= 90% agreement
-        agree = (s["status"] == gold["info"][:, c, 1].astype(int)).mean()
-        assert agree >= 0.9, agree
+        # status is a threshold test on the residuals of a TRUNCATED iterate.  Where the reference says "solved" we must
+        # too.  The un-converged ones sit between "solved inaccurate" (10x the tolerance) and "max iter" by their DUAL
+        # residual, which after 50 float32 iterations differs by factors between implementations (the reference's own
+        # float32 and float64 builds disagree the same way): there, and only there, the two labels may swap -- measured
+        # 2 of the 144 golden QPs on the host build of this code.
+        ref_st = gold["info"][:, c, 1].astype(int)
+        differ = s["status"] != ref_st
+        assert not differ[ref_st == 1].any(), "status differs on a QP the reference solved"
+        assert set(s["status"][differ]) <= {2, -2} and set(ref_st[differ]) <= {2, -2}
+        assert differ.mean() <= 0.05, differ.mean()
         _close_rel(s["pri_res"][:, None], gold["info"][:, c, 2:3], 1e-3, "pri_res")
     b.close()
 

@@ -237,3 +237,26 @@ def test_gqp_and_umg_headers_are_exported_and_refuse_without_device():
             gqp.BatchQP(2, 45, 39, rp, ci)
         with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
             gqp.BatchUprightMPC2G(2, N=5)
+
+
+def test_bf16_sigma_pairs_ab_against_full_precision():
+    """A/B of the two arithmetic shortcuts of the float32 path on the host build of the device code: the sigma / D^2 pairs
+    packed as bf16 halves (umpc_pack2) against the same code with the pairs at full precision (-DUMPC_SG_FULL), over the
+    48 x 3 golden QPs.  The term is ~1e-6 of K's diagonal: the packing must not move x beyond float32 noise."""
+    sys.path.insert(0, os.path.join(ROOT, "tests", "hostcheck"))
+    import hc
+    gold = np.load(os.path.join(GOLDEN, "umpc_seq.npz"))
+    d = util.load_constants()["umpc_defaults"]
+    B, ncall = gold["p"].shape[:2]
+    worst = werr_a = werr_b = 0.0
+    for e in range(B):
+        ha, hb = hc.HostUMPC(d), hc.HostUMPC(d, lib="libhostcheck_sgfull.so")
+        for c in range(ncall):
+            a = (gold["p"][e, c], gold["R"][e, c], gold["dq"][e, c], gold["pdes"][e, c], gold["dpdes"][e, c], gold["sdes"][e, c], float(gold["aT0"][e, c]))
+            ha.update(*a); hb.update(*a)
+            xa, xb = ha.get()["x"], hb.get()["x"]
+            worst = max(worst, util.relerr(xa, xb))
+            werr_a = max(werr_a, util.relerr(xa, gold["x"][e, c])); werr_b = max(werr_b, util.relerr(xb, gold["x"][e, c]))
+    print("bf16 pairs vs full precision: max rel diff of x %.2e; error vs reference C: packed %.2e, full %.2e" % (worst, werr_a, werr_b))
+    assert worst <= 5e-5           # the packing's own effect (measured 2.2e-5): an order below the float32 noise floor of the 50-iteration iterate
+    assert werr_a <= max(1.15 * werr_b, werr_b + 2e-4)   # and it does not make parity with the reference worse

@@ -13,8 +13,8 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 # golden QPs (tests/golden/umpc_seq.npz): the reference C code (float32) against the SAME algorithm in
 # float64 (oracle f64) differs by up to 1.2e-3 of |x|_inf (median 3e-5) -- i.e. the reference's own
 # float32 rounding -- and our kernel's arithmetic gives up to 2.3e-3 (median 6e-5) on the same worst env.
-TOL_X_REL = 5e-3      # |x - x_ref|_inf <= TOL_X_REL * max(1, |x_ref|_inf)   per QP
-TOL_Y_REL = 5e-3      # same for the duals
+TOL_X_REL = 2.5e-3    # |x - x_ref|_inf <= TOL_X_REL * max(1, |x_ref|_inf)   per QP: 2x the reference's own f32-vs-f64 gap (1.2e-3)
+TOL_Y_REL = 2.5e-3    # same for the duals
 TOL_QPDATA = 2e-6     # QP data l,u,q,Px,Ax: relative (float32 rounding)
 TOL_TRAJ_P = 0.5      # mm, closed-loop position over the 500 ms horizon
 TOL_TRAJ_S = 1e-2     # body z-axis components
