@@ -183,3 +183,27 @@ def test_gqp_random_qps_match_oracle(cuda_required):
         xo2, yo2, io2 = o.update_solve(None, None, qs[e], ls2[e], us2[e])
         assert i2["iter"][e] == io2["iter"] and _rel(x2[e], xo2) <= 1e-7
     b.close()
+
+
+def test_wrench_map_fit_matches_reference_curve_fit(cuda_required):
+    """f3: template/sdab_num_wrenchmap.py on the reference's own bench data (tests/golden/wrenchfit.npz, produced by the
+    file's own functions + scipy curve_fit): wrenchFromKinematics to rounding, the fitted maps' VALUES to 1e-5 of the
+    wrench scale and the parameters to 1e-5 of their scale (rank-10 design: curve_fit's answer is the least-squares
+    solution closest to p0 = ones, which the SVD kernel computes)"""
+    from robobee3d_b200.wrenchfit import wrench_from_kinematics, fit_wrench_map
+    g = np.load(os.path.join(GOLDEN, "wrenchfit.npz"))
+    tags = sorted({k.split("_")[0] for k in g.files if k.startswith("d")})
+    assert len(tags) >= 3
+    X, W = [], []
+    for t in tags:
+        ws = wrench_from_kinematics(g[t + "_kins"], g[t + "_fs"], kaerox=1.0, strokex=1.5)
+        assert _rel(ws, g[t + "_ws"]) <= 1e-12
+        popts, info = fit_wrench_map(g[t + "_xdata"], g[t + "_ws"], return_info=True)
+        assert info["rank"] == 10
+        assert np.abs(info["fit"] - g[t + "_fit"]).max() <= 1e-5 * np.abs(g[t + "_ws"]).max()
+        assert np.abs(popts - g[t + "_popts"]).max() <= 1e-5 * np.abs(g[t + "_popts"]).max()
+        X.append(g[t + "_xdata"]); W.append(g[t + "_ws"])
+    # batched: all datasets in one launch give the same answers
+    pb = fit_wrench_map(np.array(X), np.array(W))
+    for i, t in enumerate(tags):
+        assert np.abs(pb[i] - g[t + "_popts"]).max() <= 1e-5 * np.abs(g[t + "_popts"]).max()

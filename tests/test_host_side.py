@@ -260,3 +260,20 @@ def test_bf16_sigma_pairs_ab_against_full_precision():
     print("bf16 pairs vs full precision: max rel diff of x %.2e; error vs reference C: packed %.2e, full %.2e" % (worst, werr_a, werr_b))
     assert worst <= 5e-5           # the packing's own effect (measured 2.2e-5): an order below the float32 noise floor of the 50-iteration iterate
     assert werr_a <= max(1.15 * werr_b, werr_b + 2e-4)   # and it does not make parity with the reference worse
+
+
+def test_wrenchfit_header_is_exported_and_refuses_without_device():
+    """include/wrenchfit_b200.h: every declared symbol is exported and bound; no CPU fallback behind it"""
+    from robobee3d_b200 import wrenchfit
+    L = wrenchfit._bind()
+    src = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", "wrenchfit_b200.h")).read(), flags=re.S)
+    decl = sorted(set(re.findall(r"^\s*(?:const\s+)?(?:void|int|float|double|char)\s*\*?\s*(\w+)\s*\(", src, flags=re.M)))
+    assert decl == sorted(wrenchfit.EXPORTS), decl
+    assert all(hasattr(L, s) for s in decl)
+    g = np.load(os.path.join(GOLDEN, "wrenchfit.npz"))
+    assert g["d0_popts"].shape == (6, 15) and g["d0_xdata"].shape[1] == 4 and g["d0_kins"].shape[1] == 9
+    if not util.has_cuda():
+        with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
+            wrenchfit.fit_wrench_map(g["d0_xdata"], g["d0_ws"])
+        with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
+            wrenchfit.wrench_from_kinematics(g["d0_kins"], g["d0_fs"])
