@@ -581,9 +581,9 @@ def run_dirtran(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one umpc_rollout_kernel launch from the ncu --set full capture under profiles/
-# (key: envs, plant steps per launch); from profiles/r02m_ncu_full_umpc_rollout_kernel.txt (69.2 MB read + 1.505 GB written:
+# (key: envs, plant steps per launch); from profiles/r02m_ncu_full_umpc_rollout_kernel.txt (69.2 MB read + 1.498 GB written;
 # the L2 write-back of the slab's state rows every step, not algorithmic traffic)
-ROLLOUT_TRAFFIC = {(65536, 125): 1.574e9}
+ROLLOUT_TRAFFIC = {(65536, 125): 1.568e9}
 # dram__bytes_read.sum + dram__bytes_write.sum of one dt_rollout_kernel launch from the ncu --set full captures under
 # profiles/ (key: envs, horizon, MPC periods per launch)
 DT_TRAFFIC = {(65536, 10, 10): 152.38e9}   # profiles/r01j_ncu_full_dt_rollout_kernel.txt: 110.69 GB read + 41.68 GB written
