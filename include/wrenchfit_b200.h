@@ -21,6 +21,22 @@ int wfitWrenchFromKinematics(int M, const double *kins, const double *freq, cons
  * least-squares solution closest to p0 = ones, which is what Levenberg-Marquardt from p0 converges to. */
 int wfitFit(int F, int M, const double *xdata, const double *ws, double *popts, double *fit, int *rank, float *kernel_ms);
 
+/* wfitFitNoAlloc has NO counterpart in the reference: it was added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same fit as
+ * wfitFit (same kernel arithmetic, rcond 1e-10), but it allocates nothing -- no cudaMalloc / cudaFree / host staging: the
+ * working set (design matrix, V, sigma, coefficients) lives in one file-scope device array of the library, which every
+ * GPU that loads libumpc_b200.so holds until exit (2.05 MiB).  LIMITS: F <= WFIT_NOALLOC_MAX_DATASETS and
+ * F * M <= WFIT_NOALLOC_MAX_TRIALS per call; beyond them the call returns UMPC_ERR_ARG with a message (umpcLastError).
+ * d_xdata[F][M][4], d_ws[F][M][6], d_popts[F][90], d_rank[F] (or NULL) are DEVICE pointers of the CURRENT device, owned by
+ * the caller; the kernel is enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call returns without
+ * synchronising.  The first call on each device looks the array's device address up once (cudaGetSymbolAddress): make
+ * that call before starting a graph capture.  Every call on a device SHARES the array, which keeps the last call's
+ * contents: the kernel rewrites every word it reads, but two calls that overlap on the GPU (different streams, no
+ * dependency between them) RACE on it -- serialise them. */
+#define WFIT_NOALLOC_MAX_DATASETS 64
+#define WFIT_NOALLOC_MAX_TRIALS 16384
+int wfitFitNoAlloc(int F, int M, const double *d_xdata, const double *d_ws, double *d_popts, int *d_rank, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,8 +12,10 @@
 // applies the pseudo-inverse to the six right-hand sides.  Batched over F datasets (sweeps of trials, re-fits).
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdio.h>
 #include <string.h>
 
+#include <mutex>
 #include <string>
 
 #include "../../include/umpc_b200.h"
@@ -175,6 +177,94 @@ __global__ void __launch_bounds__(128) fit_kernel(int M, const double* __restric
     }
 }
 
+
+// ---- allocation-free variant (wfitFitNoAlloc) ------------------------------------------------------------------
+// The same fit with the working set (design matrix / U diag(sigma), V, sigma, coefficients) in a file-scope device
+// array instead of dynamic shared memory: no opt-in attribute, no allocation, any M up to the array's size.
+// Every GPU that loads the library holds the array until exit (WFIT_NOALLOC_SCRATCH_DOUBLES * 8 bytes = 2.05 MiB).
+enum { SMALL_STRIDE = 352 };   // per dataset: V 225 | sigma 15 | coef 90, padded to a multiple of 256 bytes
+static __device__ __align__(256) double g_noalloc_scratch[WFIT_NOALLOC_MAX_TRIALS * NP + WFIT_NOALLOC_MAX_DATASETS * SMALL_STRIDE];
+
+// one CTA per dataset; `scratch` is the DEVICE address of g_noalloc_scratch (cudaGetSymbolAddress, host side below)
+__global__ void __launch_bounds__(128) fit_noalloc_kernel(int F, int M, const double* __restrict__ xdata, const double* __restrict__ ws,
+                                                          double* __restrict__ popts, double rcond, int* __restrict__ rank_out,
+                                                          double* __restrict__ scratch) {
+  __shared__ double red[8];
+  const int f = blockIdx.x, t = threadIdx.x, nt = blockDim.x;
+  double* A = scratch + (size_t)f * M * NP;                                   // M x 15, column-major
+  double* V = scratch + (size_t)F * M * NP + (size_t)f * SMALL_STRIDE;        // 15 x 15, column-major
+  double* sig = V + NP * NP;
+  double* coef = sig + NP;
+  const double* X = xdata + (size_t)f * M * 4;
+  const double* W = ws + (size_t)f * M * 6;
+  // the array keeps the last call's contents: every word read below is written first (A, V = I here; sigma, coef later)
+  for (int r = t; r < M; r += nt) {
+    double phi[NP];
+    basis(X + (size_t)r * 4, phi);
+    for (int j = 0; j < NP; ++j) A[(size_t)j * M + r] = phi[j];
+  }
+  for (int i = t; i < SMALL_STRIDE; i += nt) V[i] = (i < NP * NP && i / NP == i % NP) ? 1.0 : 0.0;   // V = I, sigma = coef = 0
+  __syncthreads();
+  for (int sweep = 0; sweep < 30; ++sweep) {
+    double off = 0.0;
+    for (int p = 0; p < NP - 1; ++p)
+      for (int q = p + 1; q < NP; ++q) {
+        double a = 0, b = 0, c = 0;
+        for (int r = t; r < M; r += nt) { const double x = A[(size_t)p * M + r], y = A[(size_t)q * M + r]; a += x * x; b += y * y; c += x * y; }
+        a = block_sum(a, red); b = block_sum(b, red); c = block_sum(c, red);
+        if (fabs(c) <= 1e-15 * sqrt(a * b) || c == 0.0) continue;
+        off = fmax(off, fabs(c) / sqrt(a * b));
+        const double zeta = (b - a) / (2.0 * c);
+        const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+        for (int r = t; r < M; r += nt) {
+          const double x = A[(size_t)p * M + r], y = A[(size_t)q * M + r];
+          A[(size_t)p * M + r] = cs * x - sn * y; A[(size_t)q * M + r] = sn * x + cs * y;
+        }
+        for (int r = t; r < NP; r += nt) {
+          const double x = V[p * NP + r], y = V[q * NP + r];
+          V[p * NP + r] = cs * x - sn * y; V[q * NP + r] = sn * x + cs * y;
+        }
+        __syncthreads();
+      }
+    if (off < 1e-14) break;
+  }
+  double smax = 0.0;
+  for (int j = 0; j < NP; ++j) {
+    double a = 0;
+    for (int r = t; r < M; r += nt) { const double x = A[(size_t)j * M + r]; a += x * x; }
+    a = block_sum(a, red);
+    if (t == 0) sig[j] = sqrt(a);
+    smax = fmax(smax, sqrt(a));
+  }
+  __syncthreads();
+  int rank = 0;
+  for (int j = 0; j < NP; ++j) {
+    const bool keep = sig[j] > rcond * smax;
+    rank += keep;
+    for (int i = 0; i < 6; ++i) {
+      double a = 0;
+      if (keep)
+        for (int r = t; r < M; r += nt) {
+          double phi[NP], p1 = 0;
+          basis(X + (size_t)r * 4, phi);
+          for (int k = 0; k < NP; ++k) p1 += phi[k];
+          a += A[(size_t)j * M + r] * (W[(size_t)r * 6 + i] - p1);
+        }
+      a = block_sum(a, red);
+      if (t == 0) coef[j * 6 + i] = keep ? a / (sig[j] * sig[j]) : 0.0;
+    }
+  }
+  __syncthreads();
+  if (t == 0 && rank_out) rank_out[f] = rank;
+  for (int idx = t; idx < 6 * NP; idx += nt) {
+    const int i = idx / NP, k = idx % NP;
+    double v = 1.0;
+    for (int j = 0; j < NP; ++j) v += V[j * NP + k] * coef[j * 6 + i];
+    popts[(size_t)f * 90 + idx] = v;
+  }
+}
+
 }  // namespace wfit
 
 #define WCK(call)                                                                         \
@@ -236,5 +326,48 @@ extern "C" int wfitFit(int F, int M, const double* xdata, const double* ws, doub
   if (kernel_ms) cudaEventElapsedTime(kernel_ms, e0, e1);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   cudaFree(dx); cudaFree(dw); cudaFree(dp); cudaFree(dfit); cudaFree(dr);
+  return UMPC_OK;
+}
+
+// ---- wfitFitNoAlloc: no counterpart in the reference; for callers that cannot allocate (see include/wrenchfit_b200.h) ----
+namespace {
+enum { kMaxDevices = 64 };
+std::mutex g_noalloc_mu;
+double* g_noalloc_ptr[kMaxDevices];   // device address of wfit::g_noalloc_scratch on each device, 0 = not set up yet
+}  // namespace
+
+// Set-up, once per device, with that device current: in host code `wfit::g_noalloc_scratch` is only a host-side stand-in
+// for the symbol, never a device address -- the kernel gets the address cudaGetSymbolAddress returns for THIS device.
+static int noalloc_scratch(double** out) {
+  int dev = -1;
+  WCK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { umpc_internal_set_error("wfitFitNoAlloc: device ordinal out of range"); return UMPC_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    double* ptr = nullptr;
+    WCK(cudaGetSymbolAddress((void**)&ptr, wfit::g_noalloc_scratch));
+    if (!ptr) { umpc_internal_set_error("wfitFitNoAlloc: cudaGetSymbolAddress returned a null address"); return UMPC_ERR_CUDA; }
+    g_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return UMPC_OK;
+}
+
+extern "C" int wfitFitNoAlloc(int F, int M, const double* d_xdata, const double* d_ws, double* d_popts, int* d_rank, void* stream) {
+  if (F <= 0 || M <= 0 || !d_xdata || !d_ws || !d_popts) { umpc_internal_set_error("wfitFitNoAlloc: bad argument"); return UMPC_ERR_ARG; }
+  if (F > WFIT_NOALLOC_MAX_DATASETS || (long long)F * M > WFIT_NOALLOC_MAX_TRIALS) {
+    char msg[256];
+    snprintf(msg, sizeof msg, "wfitFitNoAlloc: F = %d datasets x M = %d trials exceeds the static scratch (at most %d datasets and %d trials "
+             "in all per call); use wfitFit for larger problems", F, M, (int)WFIT_NOALLOC_MAX_DATASETS, (int)WFIT_NOALLOC_MAX_TRIALS);
+    umpc_internal_set_error(msg);
+    return UMPC_ERR_ARG;
+  }
+  int rc = need_device("wfitFitNoAlloc");
+  if (rc) return rc;
+  double* scratch = nullptr;
+  rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  wfit::fit_noalloc_kernel<<<F, 128, 0, (cudaStream_t)stream>>>(F, M, d_xdata, d_ws, d_popts, 1e-10, d_rank, scratch);
+  WCK(cudaGetLastError());
   return UMPC_OK;
 }

@@ -11,7 +11,8 @@ import numpy as np
 from . import _lib
 
 DP = C.POINTER(C.c_double)
-EXPORTS = ["wfitWrenchFromKinematics", "wfitFit"]
+EXPORTS = ["wfitWrenchFromKinematics", "wfitFit", "wfitFitNoAlloc"]
+NOALLOC_MAX_DATASETS, NOALLOC_MAX_TRIALS = 64, 16384   # include/wrenchfit_b200.h
 # aero constants of template/robobee.py:7-17 and the wing parameters sdab_num_wrenchmap.py:252-253 uses
 DEFAULT_PARAMS = dict(Aw=54.4, AR=4.5, r2h=0.551, ycp=7.5, R=3.0, RHO=1.225e-3, CD0=0.4, CDmax=3.4, CLmax=1.8)
 
@@ -20,7 +21,15 @@ def _bind():
     L = _lib.load()
     L.wfitWrenchFromKinematics.argtypes = [C.c_int, DP, DP, DP, DP]
     L.wfitFit.argtypes = [C.c_int, C.c_int, DP, DP, DP, DP, C.POINTER(C.c_int), C.POINTER(C.c_float)]
+    L.wfitFitNoAlloc.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     return L
+
+
+def fit_wrench_map_noalloc(F, M, d_xdata, d_ws, d_popts, d_rank=None, stream=None):
+    """wfitFitNoAlloc: device addresses (ints) in and out, nothing allocated, enqueued on `stream` (a cudaStream_t handle
+    as an int, None = default stream) without synchronising.  No counterpart in the reference (see the header)."""
+    L = _bind()
+    _lib.check(L.wfitFitNoAlloc(int(F), int(M), d_xdata, d_ws, d_popts, d_rank, stream), "wfitFitNoAlloc")
 
 
 def _d(a):
