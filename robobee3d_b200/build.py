@@ -31,8 +31,12 @@ def build(force=False, verbose=False, defines=(), out=None):
     if out is None and not force and not stale():
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out or OUT, SRC, SRC_CONV, SRC_DT, SRC_GQP, SRC_UMG, SRC_WFIT]
+    final = out or OUT
+    tmp = final + ".partial"     # linked beside the target and renamed: a reader (or a snapshot) never sees half a library
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", tmp, SRC, SRC_CONV, SRC_DT, SRC_GQP, SRC_UMG, SRC_WFIT]
     r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode == 0:
+        os.replace(tmp, final)
     log = r.stdout + r.stderr
     if out is None:
         with open(os.path.join(HERE, "csrc", "ptxas_v.log"), "w") as f:
