@@ -22,6 +22,7 @@
 #include "umpc_conv.h"
 
 #define UMPC_REAL double
+#define UMPC_SCALE_FLOAT  // the ten Ruiz passes in float (umpc_core.cuh `sreal`); host A/B: tests/hostcheck libhostcheck64_sf.so
 namespace umpc64 {
 #include "umpc_core.cuh"
 }  // namespace umpc64
@@ -70,6 +71,61 @@ struct GlobStore64 {
   __device__ __forceinline__ void setVf(int i, double v) { __stcg(vf + ROWD(i), v); }
 };
 
+// ---- on-chip store (default): the 256-word scratch in TENSOR MEMORY, the loop vectors in SHARED MEMORY -------------------
+// One 4-warp CTA per SM owns all of tensor memory (128 lanes x 512 columns x 32 bit): thread i of warp w reads "word e
+// of my own QP" as columns 2e, 2e+1 of lane 32 (w % 4) + i with a warp-uniform address, 256 doubles per thread = the whole
+// 256 KB.  A chunk of 16 doubles is one tcgen05.ld.32x32b.x32; the load lands in 32 raw registers that are in/out
+// operands of the wait (nothing can be scheduled above it) and are paired into doubles after it -- exactly one load
+// is in flight at any time in the generated solve (issue / wait alternate), so one raw buffer serves both chunk arrays.
+// In double the ADMM loop's state would be 252 registers (xs 45 + w 36 + r 45 doubles): xs and w -- touched element by
+// element, twice per iteration -- and the first-iteration fix-up vector live in shared memory as [word][thread]
+// (conflict-free 8-byte accesses, immediate offsets from one per-thread pointer); r, which the triangular solves
+// chain through, stays in registers.  117 doubles per thread = 117 KB per CTA: also what keeps a second CTA (which
+// could not get tensor memory anyway) off the SM.
+#define CONV_TPB 128
+enum { CONV_SV_XS = 0, CONV_SV_VF = UMPC_NX + UMPC_NEQ, CONV_SV_WORDS = UMPC_NX + 2 * UMPC_NEQ };
+extern __shared__ double g_smem64[];
+
+struct TmemStore64 {
+  typedef void has_vec;
+  template <int N, int OFF>
+  struct Vec {
+    double* b;
+    __device__ __forceinline__ explicit Vec(const TmemStore64& st) : b(st.sv + OFF * CONV_TPB) {}
+    __device__ __forceinline__ double& operator[](int i) const { return b[i * CONV_TPB]; }
+  };
+  uint32_t tbase;  // TMEM address of this thread's lane block, column 0
+  double* sv;      // this thread's column of the CTA's shared vectors
+  uint32_t raw[32];
+  __device__ __forceinline__ void init(uint32_t tbase_) { tbase = tbase_; sv = g_smem64 + threadIdx.x; }
+  __device__ __forceinline__ void begin_iteration(int) {}
+  __device__ __forceinline__ void issue(int c, double (&)[UMPC_GEN_CHUNK]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(raw[0]), "=r"(raw[1]), "=r"(raw[2]), "=r"(raw[3]), "=r"(raw[4]), "=r"(raw[5]), "=r"(raw[6]), "=r"(raw[7]), "=r"(raw[8]), "=r"(raw[9]), "=r"(raw[10]), "=r"(raw[11]), "=r"(raw[12]), "=r"(raw[13]), "=r"(raw[14]), "=r"(raw[15]), "=r"(raw[16]), "=r"(raw[17]), "=r"(raw[18]), "=r"(raw[19]), "=r"(raw[20]), "=r"(raw[21]), "=r"(raw[22]), "=r"(raw[23]), "=r"(raw[24]), "=r"(raw[25]), "=r"(raw[26]), "=r"(raw[27]), "=r"(raw[28]), "=r"(raw[29]), "=r"(raw[30]), "=r"(raw[31])
+                 : "r"(tbase + (uint32_t)c * (2 * UMPC_GEN_CHUNK)));
+  }
+  __device__ __forceinline__ void waitc(int, double (&v)[UMPC_GEN_CHUNK]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(raw[0]), "+r"(raw[1]), "+r"(raw[2]), "+r"(raw[3]), "+r"(raw[4]), "+r"(raw[5]), "+r"(raw[6]), "+r"(raw[7]), "+r"(raw[8]), "+r"(raw[9]), "+r"(raw[10]), "+r"(raw[11]), "+r"(raw[12]), "+r"(raw[13]), "+r"(raw[14]), "+r"(raw[15]), "+r"(raw[16]), "+r"(raw[17]), "+r"(raw[18]), "+r"(raw[19]), "+r"(raw[20]), "+r"(raw[21]), "+r"(raw[22]), "+r"(raw[23]), "+r"(raw[24]), "+r"(raw[25]), "+r"(raw[26]), "+r"(raw[27]), "+r"(raw[28]), "+r"(raw[29]), "+r"(raw[30]), "+r"(raw[31]) :: "memory");
+#pragma unroll
+    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) v[i] = __hiloint2double((int)raw[2 * i + 1], (int)raw[2 * i]);
+  }
+  __device__ __forceinline__ void setW(int e, double v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(tbase + 2u * (uint32_t)e), "r"(__double2loint(v)),
+                 "r"(__double2hiint(v)) : "memory");
+  }
+  __device__ __forceinline__ void setChunk(int c, const double (&v)[UMPC_GEN_CHUNK]) {
+    int u[32];
+#pragma unroll
+    for (int i = 0; i < UMPC_GEN_CHUNK; ++i) { u[2 * i] = __double2loint(v[i]); u[2 * i + 1] = __double2hiint(v[i]); }
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(tbase + (uint32_t)c * (2 * UMPC_GEN_CHUNK)), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7]), "r"(u[8]), "r"(u[9]), "r"(u[10]), "r"(u[11]), "r"(u[12]), "r"(u[13]), "r"(u[14]), "r"(u[15]), "r"(u[16]), "r"(u[17]), "r"(u[18]), "r"(u[19]), "r"(u[20]), "r"(u[21]), "r"(u[22]), "r"(u[23]), "r"(u[24]), "r"(u[25]), "r"(u[26]), "r"(u[27]), "r"(u[28]), "r"(u[29]), "r"(u[30]), "r"(u[31]) : "memory");
+  }
+  __device__ __forceinline__ void end_writes() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ void sync() const {}
+  __device__ __forceinline__ bool all(bool p) const { return __all_sync(0xffffffffu, p); }
+  __device__ __forceinline__ double Vf(int i) const { return sv[(CONV_SV_VF + i) * CONV_TPB]; }
+  __device__ __forceinline__ void setVf(int i, double v) { sv[(CONV_SV_VF + i) * CONV_TPB] = v; }
+};
+
 // controller state in double; the float rows of DevState are kept as mirrors for the getters of the C-ABI
 struct GlobIO64 {
   float* eb;  // float mirrors: the env's rows of the tiled slab (umpc_dev.cuh)
@@ -94,16 +150,49 @@ struct GlobIO64 {
   __device__ __forceinline__ void st_soly(int i, double v) { eb[ROWF(ROW_SOLY + i)] = (float)v; }
 };
 
+// all of tensor memory for one 128-thread CTA: 512 columns, warp w owns lanes 32 (w % 4) ..
+static __device__ __forceinline__ uint32_t tmem64_acquire(uint32_t* slot) {
+  if ((threadIdx.x >> 5) == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  return *slot + ((uint32_t)(32 * ((threadIdx.x >> 5) & 3)) << 16);
+}
+static __device__ __forceinline__ void tmem64_release(const uint32_t* slot) {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(*slot) : "memory");
+}
+
+template <class ST> struct Store64Traits;
+template <> struct Store64Traits<GlobStore64> {
+  template <int TPB> static __device__ __forceinline__ uint32_t acquire(uint32_t*) { return 0u; }
+  template <int TPB> static __device__ __forceinline__ void release(const uint32_t*) {}
+  static __device__ __forceinline__ void init(GlobStore64& st, uint32_t, const DevState& s, int e) { st.init(s.c64, e); }
+};
+template <> struct Store64Traits<TmemStore64> {
+  template <int TPB> static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) {
+    static_assert(TPB == CONV_TPB, "the tensor-memory store is laid out for 128-thread CTAs");
+    return tmem64_acquire(slot);
+  }
+  template <int TPB> static __device__ __forceinline__ void release(const uint32_t* slot) { tmem64_release(slot); }
+  static __device__ __forceinline__ void init(TmemStore64& st, uint32_t base, const DevState&, int) { st.init(base); }
+};
+
 // SOLVER policy of the kernel templates in umpc_dev.cuh
-struct SolverF64 {
+template <class ST64>
+struct SolverF64T {
   typedef umpc64::UmpcParams Params;
   static constexpr int kMinBlocks = 1;
-  GlobStore64 st;
+  ST64 st;
   template <int TPB>
-  static __device__ __forceinline__ uint32_t acquire(uint32_t*) { return 0u; }
+  static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) { return Store64Traits<ST64>::template acquire<TPB>(slot); }
   template <int TPB>
-  static __device__ __forceinline__ void release(const uint32_t*) {}
-  __device__ __forceinline__ void init(uint32_t, const DevState& s, int e) { st.init(s.c64, e); }
+  static __device__ __forceinline__ void release(const uint32_t* slot) { Store64Traits<ST64>::template release<TPB>(slot); }
+  __device__ __forceinline__ void init(uint32_t base, const DevState& s, int e) { Store64Traits<ST64>::init(st, base, s, e); }
   __device__ __forceinline__ void qpdata(const Params& par, const DevState& s, int e, const float p[3], const float R[9],
                                          const float dq[6], const float pd[3], const float dpd[3], const float sd[3], float aT0) {
     double p_[3], R_[9], dq_[6], pd_[3], dpd_[3], sd_[3];
@@ -147,6 +236,8 @@ struct SolverF64 {
     for (int i = 0; i < 6; ++i) acc[i] = (float)acc_[i];
   }
 };
+typedef SolverF64T<GlobStore64> SolverF64;      // scratch streamed from L2 (the round-1 kernel; UMPC_CONV_STORE=glob)
+typedef SolverF64T<TmemStore64> SolverF64Tmem;  // on-chip (default)
 
 // ================================ host side ======================================================================
 typedef KernelParamsT<umpc64::UmpcParams> KernelParams64;
@@ -155,7 +246,9 @@ struct UmpcConv {
   umpc64::UmpcParams mpc;
   double* slab = nullptr;
   int Bp = 0;
-  int tpb = 64;  // measured: 64 slightly ahead of 128 (UMPC_CONV_TPB to override)
+  int tpb = 64;  // streamed store only: 64 slightly ahead of 128 (UMPC_CONV_TPB to override)
+  bool on_chip = true;  // TmemStore64 (one 128-thread CTA per SM); UMPC_CONV_STORE=glob selects the streamed store
+  bool attr_set = false;
 };
 
 int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState* s) {
@@ -181,6 +274,7 @@ int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState
   m.adaptive_rho_tol = 5.0;
   cudaError_t e = cudaMalloc(&c->slab, (size_t)C64_ROWS * Bp * sizeof(double));
   if (e != cudaSuccess) { delete c; return (int)e; }
+  if (const char* t = getenv("UMPC_CONV_STORE")) c->on_chip = strcmp(t, "glob") != 0;
   if (const char* t = getenv("UMPC_CONV_TPB")) {  // tuning knob
     const int v = atoi(t);
     if (v == 64 || v == 128) c->tpb = v;
@@ -215,12 +309,31 @@ void umpc_conv_destroy(UmpcConv* c) {
   delete c;
 }
 
+static constexpr size_t kConvSmem = (size_t)CONV_SV_WORDS * sizeof(double) * CONV_TPB;
+
+// opt-in to the 117 KB of dynamic shared memory, once per process (the attribute is per function, not per device context
+// here: one device per process)
+static int conv_set_attrs(UmpcConv* c) {
+  if (c->attr_set) return 0;
+  cudaError_t e = cudaFuncSetAttribute(umpc_update_kernel<CONV_TPB, SolverF64Tmem>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kConvSmem);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(umpc_rollout_kernel<CONV_TPB, SolverF64Tmem>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kConvSmem);
+  c->attr_set = e == cudaSuccess;
+  return (int)e;
+}
+
 int umpc_conv_launch_update(UmpcConv* c, const SimParams* sim, const DevState* s, float* uquad, float* accdes, const float* p0,
                             const float* R0, const float* dq0, const float* pdes, const float* dpdes, const float* sdes,
                             const float* aT0, int want_qpdata, float* pn, float* Rn, float* dqn, int env0, int nenv,
                             cudaStream_t stream) {
   KernelParams64 kp;
   kp.mpc = c->mpc; kp.sim = *sim;
+  if (c->on_chip) {
+    if (int rc = conv_set_attrs(c)) return rc;
+    umpc_update_kernel<CONV_TPB, SolverF64Tmem><<<(nenv + CONV_TPB - 1) / CONV_TPB, CONV_TPB, kConvSmem, stream>>>(
+        kp, *s, uquad, accdes, p0, R0, dq0, pdes, dpdes, sdes, aT0, want_qpdata, pn, Rn, dqn, env0);
+    return (int)cudaGetLastError();
+  }
   const int grid = (nenv + c->tpb - 1) / c->tpb;
 #define UMPC_CONV_UPDATE(T)                                                                                              \
   case T:                                                                                                                \
@@ -235,6 +348,12 @@ int umpc_conv_launch_rollout(UmpcConv* c, const SimParams* sim, const DevState* 
                              const uint8_t* fire, const double* tvals, LogBuf lg, cudaStream_t stream) {
   KernelParams64 kp;
   kp.mpc = c->mpc; kp.sim = *sim;
+  if (c->on_chip) {
+    if (int rc = conv_set_attrs(c)) return rc;
+    umpc_rollout_kernel<CONV_TPB, SolverF64Tmem><<<(s->B + CONV_TPB - 1) / CONV_TPB, CONV_TPB, kConvSmem, stream>>>(
+        kp, *s, *wlp, step0, nsteps, fire, tvals, lg, 1);
+    return (int)cudaGetLastError();
+  }
   const int grid = (s->B + c->tpb - 1) / c->tpb;
 #define UMPC_CONV_ROLLOUT(T)                                                                                              \
   case T:                                                                                                                 \

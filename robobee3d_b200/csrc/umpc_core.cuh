@@ -91,6 +91,19 @@ struct UmpcAVals {
 #elif defined(UMPC_REAL_IS_FLOAT)
 #define UMPC_RCP(x) (1.0f / (x))
 #define UMPC_RSQRT(x) (1.0f / sqrtf(x))
+#elif defined(__CUDA_ARCH__)
+// double on the device: rsqrt() is MUFU.RSQ64H + Newton steps (~1 ulp), a sixth of the instructions of sqrt + divide --
+// the 84 of them per Ruiz pass were two thirds of the pass
+// 1 / x for NORMAL x (scalings, rho-weighted diagonals: 1e-10 .. 1e10): MUFU.RCP64H (20 bits) + two Newton steps = 1 ulp
+// in 5 instructions; the IEEE division it replaces is ~25 with a slow-path call, 190 of them in the once-per-check code
+__device__ __forceinline__ double umpc_drcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(r, fma(-x, r, 1.0), r);
+  return fma(r, fma(-x, r, 1.0), r);
+}
+#define UMPC_RCP(x) umpc_drcp(x)
+#define UMPC_RSQRT(x) rsqrt(x)
 #else
 #define UMPC_RCP(x) (1.0 / (x))
 #define UMPC_RSQRT(x) (1.0 / sqrt(x))
@@ -108,6 +121,37 @@ UMPC_HD ureal umpc_fabs(ureal a) { return fabs(a); }
 UMPC_HD ureal umpc_sqrt(ureal a) { return sqrt(a); }
 UMPC_HD ureal umpc_nan() { return nan(""); }
 #endif
+
+// ---- arithmetic of the Ruiz equilibration ("sreal") ---------------------------------------------------------------
+// Any positive D, E, c is a valid equilibration (the termination test runs on un-scaled residuals), so the ten passes
+// need not run in the width of the iterates: -DUMPC_SCALE_FLOAT computes them in float also in the double build (the
+// GPU's converged mode: the passes in double were 30 % of the kernel); the results are widened once and used
+// consistently from there on.  Default: the width of the iterates, like OSQP.
+#if defined(UMPC_REAL_IS_FLOAT) || defined(UMPC_SCALE_FLOAT)
+typedef float sreal;
+#else
+typedef double sreal;
+#endif
+UMPC_HD float umpc_tmax(float a, float b) { return fmaxf(a, b); }
+UMPC_HD double umpc_tmax(double a, double b) { return fmax(a, b); }
+UMPC_HD float umpc_tmin(float a, float b) { return fminf(a, b); }
+UMPC_HD double umpc_tmin(double a, double b) { return fmin(a, b); }
+UMPC_HD float umpc_tabs(float a) { return fabsf(a); }
+UMPC_HD double umpc_tabs(double a) { return fabs(a); }
+#if defined(__CUDA_ARCH__)
+UMPC_HD float umpc_trsqrt(float a) { return rsqrtf(a); }
+UMPC_HD double umpc_trsqrt(double a) { return rsqrt(a); }
+UMPC_HD float umpc_trcp(float a) { return __fdividef(1.0f, a); }
+#else
+UMPC_HD float umpc_trsqrt(float a) { return 1.0f / sqrtf(a); }
+UMPC_HD double umpc_trsqrt(double a) { return 1.0 / sqrt(a); }
+UMPC_HD float umpc_trcp(float a) { return 1.0f / a; }
+#endif
+UMPC_HD double umpc_trcp(double a) { return 1.0 / a; }
+template <class T> UMPC_HD T umpc_tlimit(T v) {   // MIN_SCALING / MAX_SCALING (constants.h:97-98), see umpc_limit_scaling
+  v = v < (T)1e-4f ? (T)1.0f : v;
+  return umpc_tmin(v, (T)1e4f);
+}
 
 #include "umpc_gen.cuh"
 
@@ -296,6 +340,22 @@ UMPC_HD ureal umpc_ref(const ureal (&yd)[6], const ureal (&dyd)[6], int j) {
   return j < 18 ? yd[j % 6] : (j < 36 ? dyd[j % 6] : 0.0f);
 }
 
+// Where the two vectors that live across the whole ADMM loop (xs: the shifted iterate, w: the own-column part of
+// g + kappa) are kept.  Default: registers.  A store policy that declares `typedef void has_vec` and a member template
+// `Vec<N, OFF>` (constructible from the policy, indexable with []) places them elsewhere -- converged mode keeps them
+// in shared memory because in double the loop state alone would be 252 registers (umpc_conv.cu).
+template <int N>
+struct UmpcRegVec {
+  ureal v[N];
+  template <class ST> UMPC_HD explicit UmpcRegVec(const ST&) {}
+  UMPC_HD ureal& operator[](int i) { return v[i]; }
+  UMPC_HD const ureal& operator[](int i) const { return v[i]; }
+};
+template <class ST, int N, int OFF, class = void>
+struct UmpcVecOf { typedef UmpcRegVec<N> type; };
+template <class ST, int N, int OFF>
+struct UmpcVecOf<ST, N, OFF, typename ST::has_vec> { typedef typename ST::template Vec<N, OFF> type; };
+
 template <bool CONV, bool INFO = true, class ST, class IO>
 UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], ureal accdes[6], const ureal p0[3],
                          const ureal R0[9], const ureal dq0[6], const ureal pdes[3], const ureal dpdes[3],
@@ -351,38 +411,51 @@ UMPC_HD void umpc_update(const UmpcParams& par, ST& st, IO& io, ureal uquad[3], 
 
   // ---- Ruiz equilibration + cost scaling (scale_data, scaling.c:44-156) -------------------
   ureal c = 1.0f;
-  ureal xs[UMPC_NX], w[UMPC_NEQ], z3[3], y3[3];
+  typename UmpcVecOf<ST, UMPC_NX, 0>::type xs(st);
+  typename UmpcVecOf<ST, UMPC_NEQ, UMPC_NX>::type w(st);
+  ureal z3[3], y3[3];
   {
-    ureal D[UMPC_NX], E[UMPC_NC];
+    sreal Ds[UMPC_NX], Es[UMPC_NC], cs = 1.0f;
 #pragma unroll
-    for (int j = 0; j < UMPC_NX; ++j) D[j] = 1.0f;
+    for (int j = 0; j < UMPC_NX; ++j) Ds[j] = 1.0f;
 #pragma unroll
-    for (int i = 0; i < UMPC_NC; ++i) E[i] = 1.0f;
+    for (int i = 0; i < UMPC_NC; ++i) Es[i] = 1.0f;
     for (int it = 0; it < par.scaling_iters; ++it) {
       st.sync();  // keep the warps of a CTA on the same code (shared instruction fetch), see TmemStore::sync
-      ureal cn[UMPC_NX], rn[UMPC_NC];
-      umpc_gen_norms(cn, rn, D, E, a);
+      sreal cn[UMPC_NX], rn[UMPC_NC];
+      umpc_gen_norms(cn, rn, Ds, Es, a);
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const ureal pc = c * umpc_px(par, j) * D[j] * D[j];
-        const ureal nj = umpc_fmax(pc, cn[j] * D[j]);
-        D[j] *= UMPC_RSQRT(umpc_limit_scaling(nj));
+        const sreal pc = cs * (sreal)umpc_px(par, j) * Ds[j] * Ds[j];
+        const sreal nj = umpc_tmax(pc, cn[j] * Ds[j]);
+        Ds[j] *= umpc_trsqrt(umpc_tlimit(nj));
       }
 #pragma unroll
-      for (int i = 0; i < UMPC_NC; ++i) E[i] *= UMPC_RSQRT(umpc_limit_scaling(rn[i] * E[i]));
+      for (int i = 0; i < UMPC_NC; ++i) Es[i] *= umpc_trsqrt(umpc_tlimit(rn[i] * Es[i]));
       // cost normalisation (scaling.c:100-131)
-      ureal psum = 0.0f, nq = 0.0f;
+      sreal psum = 0.0f, nq = 0.0f;
 #pragma unroll
       for (int j = 0; j < UMPC_NX; ++j) {
-        const ureal px = umpc_px(par, j);
-        psum += c * px * D[j] * D[j];
-        if (j < 36) nq = umpc_fmax(nq, umpc_fabs(c * D[j] * px * umpc_ref(yd, dyd, j)));
+        const sreal px = (sreal)umpc_px(par, j);
+        psum += cs * px * Ds[j] * Ds[j];
+        if (j < 36) nq = umpc_tmax(nq, umpc_tabs(cs * Ds[j] * px * (sreal)umpc_ref(yd, dyd, j)));
       }
-      ureal ct = psum * (1.0f / UMPC_NX);
-      ct = umpc_fmax(ct, umpc_limit_scaling(nq));
-      ct = umpc_limit_scaling(ct);
-      c *= UMPC_RCP(ct);
+      sreal ct = psum * (1.0f / UMPC_NX);
+      ct = umpc_tmax(ct, umpc_tlimit(nq));
+      ct = umpc_tlimit(ct);
+      cs *= umpc_trcp(ct);
     }
+    c = cs;
+#if defined(UMPC_REAL_IS_FLOAT) || !defined(UMPC_SCALE_FLOAT)
+    sreal (&D)[UMPC_NX] = Ds;
+    sreal (&E)[UMPC_NC] = Es;
+#else
+    ureal D[UMPC_NX], E[UMPC_NC];   // widened once
+#pragma unroll
+    for (int j = 0; j < UMPC_NX; ++j) D[j] = Ds[j];
+#pragma unroll
+    for (int i = 0; i < UMPC_NC; ++i) E[i] = Es[i];
+#endif
     // ---- K = c P0 + sigma D^-2 + A0' W A0 and its LDL' ----------------------------------
     {
       st.sync();

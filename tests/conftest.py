@@ -18,7 +18,8 @@ def pytest_configure(config):
     hc = os.path.join(ROOT, "tests", "hostcheck")
     srcs = [os.path.join(hc, "hostcheck.cpp")] + [os.path.join(ROOT, "robobee3d_b200", "csrc", f)
                                                    for f in ("umpc_core.cuh", "umpc_gen.cuh", "sim_core.cuh", "wl_core.cuh")]
-    for name, defs in (("libhostcheck.so", []), ("libhostcheck64.so", ["-DUMPC_REAL=double"]), ("libhostcheck_sgfull.so", ["-DUMPC_SG_FULL"])):
+    for name, defs in (("libhostcheck.so", []), ("libhostcheck64.so", ["-DUMPC_REAL=double"]), ("libhostcheck_sgfull.so", ["-DUMPC_SG_FULL"]),
+                       ("libhostcheck64_sf.so", ["-DUMPC_REAL=double", "-DUMPC_SCALE_FLOAT"])):
         so = os.path.join(hc, name)
         if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
             subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-ffp-contract=off"] + defs + ["-o", so, srcs[0]], check=True)

@@ -129,10 +129,12 @@ def test_device_formulation_on_host_matches_reference_golden():
     print("hostcheck worst rel err vs reference C: %.2e" % worst)
 
 
-def test_converged_formulation_on_host_matches_oracle_f64():
+@pytest.mark.parametrize("lib", ["libhostcheck64.so", "libhostcheck64_sf.so"])
+def test_converged_formulation_on_host_matches_oracle_f64(lib):
     """converged mode (termination test every 25 iterations, rho re-estimated every 100, osqp.c:431-500) of the device
     code, compiled for the host in double, against the oracle's float64 OSQP restatement and the golden solutions of
-    the reference's vendored OSQP in float64: same iteration counts, solutions within 10 eps_abs + eps_rel |x*|."""
+    the reference's vendored OSQP in float64: same iteration counts, solutions within 10 eps_abs + eps_rel |x*|.
+    `_sf` = the build the GPU runs: Ruiz equilibration in float (-DUMPC_SCALE_FLOAT), everything else in double."""
     sys.path.insert(0, os.path.join(ROOT, "tests", "hostcheck"))
     import hc
     from oracle import binding as OB
@@ -141,7 +143,7 @@ def test_converged_formulation_on_host_matches_oracle_f64():
     d = util.load_constants()["umpc_defaults"]
     B, ncall = gold["p"].shape[:2]
     for e in range(0, B, 3):
-        h = hc.HostUMPC(d, f64=True)
+        h = hc.HostUMPC(d, f64=True, lib=lib)
         h.set_converged()
         o = OB.OracleUMPC("f64")
         o.set_converged()
