@@ -727,6 +727,8 @@ def main():
     mean_iter = float(b.solve_info()["iter"].mean()) if args.converged else 50.0
     if rank == 0:
         fl = F.our_flops(mean_iter)
+        if args.converged:   # the residual block runs after every 25 iterations, not once
+            fl = dict(fl, total=fl["setup"] + mean_iter * fl["per_iter"] + max(mean_iter / 25.0, 1.0) * fl["post"])
         solves_per_launch = spl if args.hl_interval is None else 1
         per_launch_flops = (solves_per_launch * fl["total"] + spl * F.DYN_STEP_FLOPS) * nenv
         launch_s = dev_s / args.steps
@@ -734,6 +736,8 @@ def main():
         # (sustained, ~0.25 s: the denominator for a step that itself runs for tens of ms) and a short one (burst)
         peak_burst = b.lib.umpcMeasureFp32Peak(local, 4096)
         peak_tf = b.lib.umpcMeasureFp32Peak(local, 1 << 18)
+        if args.converged:   # float64 kernel: the DFMA pipe is the roof
+            peak_burst = peak_tf = b.lib.umpcMeasureFp64Peak(local, 1 << 16)
         achieved_tf = per_launch_flops / launch_s * 1e-12
         peaks = {}
         try:
@@ -741,15 +745,18 @@ def main():
         except Exception:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
+        roofline = {"bound": "fp64" if args.converged else "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
                     # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the ncu --set full capture summarised in
                     # profiles/r01e_ncu_full_umpc_rollout_kernel_tmem.txt (42.4 + 35.3 MB per launch of 65,536 envs; the
                     # algorithmic figure is 2,172 B x 65,536 = 142 MB -- part of the 96 MB state slab stays in the 126 MB L2
                     # from one launch to the next); only known for that launch shape
                     "traffic": ROLLOUT_TRAFFIC.get((nenv, spl)) if (args.workload == "mc" and not args.converged and args.hl_interval is None) else None,
                     "peak_burst": peak_burst,
-                    "kernel": "umpc_rollout_kernel",
-                    "note": "FP32 CUDA-core pipe bound (arithmetic intensity %.0f flop/B vs ridge ~11): peak = FFMA "
+                    "kernel": "umpc_rollout_kernel<128, SolverF64T<TmemStore64>>" if args.converged else "umpc_rollout_kernel",
+                    "note": ("FP64 pipe roof (DFMA microbenchmark in this process); achieved = executed-algorithm flops at the lanes' MEAN "
+                             "iteration count (%.1f; a warp runs to its slowest lane's count) x envs / CUDA-event launch time; the loop is bound "
+                             "by the per-warp tensor-memory read rate, the rest by instruction fetch at 4 warps per SM (DESIGN 4.1)" % mean_iter)
+                            if args.converged else "FP32 CUDA-core pipe bound (arithmetic intensity %.0f flop/B vs ridge ~11): peak = FFMA "
                             "microbenchmark run in this process (MEASURED_PEAKS.json has no FP32 figure); achieved = "
                             "executed-algorithm flops %d/solve (FMA=2; reference formulation would be %d) x envs / "
                             "CUDA-event launch time" % (fl["total"] / F.BYTES_PER_SOLVE, fl["total"],
@@ -774,8 +781,8 @@ def main():
         if args.converged:
             line["converged_mode"] = {"mean_iter_last_step": mean_iter, "max_iter": 4000, "check_termination": 25,
                                       "adaptive_rho_interval": 100, "eps": 1e-4,
-                                      "note": "extra measurement: float64 kernel (umpc_conv.cu), scratch in HBM/L2; roofline "
-                                              "above is still quoted against the FP32 pipe peak and does not apply"}
+                                      "note": "float64 kernel (umpc_conv.cu): scratch in tensor memory, loop vectors in shared "
+                                              "memory (UMPC_CONV_STORE=glob: the round-1 kernel, scratch streamed from L2)"}
         if world == 1 and not args.no_cpu:
             from oracle import binding as OB
             cores = os.cpu_count() or 1

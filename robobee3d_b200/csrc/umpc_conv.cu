@@ -82,12 +82,26 @@ struct GlobStore64 {
 // (conflict-free 8-byte accesses, immediate offsets from one per-thread pointer); r, which the triangular solves
 // chain through, stays in registers.  117 doubles per thread = 117 KB per CTA: also what keeps a second CTA (which
 // could not get tensor memory anyway) off the SM.
+// The ADMM loop reads the factor twice per iteration (31 chunks = 127 KB per warp): a warp gets ~23 B/clk out of tensor
+// memory however many loads it keeps in flight (tests/microbench/tmem_bw.cu), i.e. >= 5.5k cycles per iteration with all
+// chunks there.  The chunks whose bit is set in CONV_SMEM_MASK live in the spare shared memory instead ([slot][pair]
+// [thread][2] doubles: a chunk = 8 conflict-free LDS.128), a second, independent read path with a fifth of the latency;
+// alternating chunks, so that a tensor-memory load is in flight while a shared-memory chunk is consumed.
 #define CONV_TPB 128
-enum { CONV_SV_XS = 0, CONV_SV_VF = UMPC_NX + UMPC_NEQ, CONV_SV_WORDS = UMPC_NX + 2 * UMPC_NEQ };
+#ifndef CONV_SMEM_MASK
+#define CONV_SMEM_MASK 0x0AAAu   // chunks 1, 3, .., 11 of the 14 factor chunks
+#endif
+__host__ __device__ constexpr int conv_popc(unsigned v) { int n = 0; while (v) { n += v & 1u; v >>= 1; } return n; }
+enum { CONV_SV_XS = 0, CONV_SV_VF = UMPC_NX + UMPC_NEQ, CONV_SV_WORDS = UMPC_NX + 2 * UMPC_NEQ,
+       CONV_SMEM_CHUNKS = conv_popc(CONV_SMEM_MASK) };
 extern __shared__ double g_smem64[];
 
 struct TmemStore64 {
   typedef void has_vec;
+  static __host__ __device__ constexpr bool in_smem(int c) { return (CONV_SMEM_MASK >> c) & 1u; }
+  static __host__ __device__ constexpr int slot(int c) { return conv_popc(CONV_SMEM_MASK & ((1u << c) - 1u)); }
+  // this thread's pair p of shared-memory chunk slot q
+  __device__ __forceinline__ double2* spair(int q, int p) const { return (double2*)(sf + ((size_t)(q * (UMPC_GEN_CHUNK / 2) + p) * CONV_TPB) * 2); }
   template <int N, int OFF>
   struct Vec {
     double* b;
@@ -96,24 +110,44 @@ struct TmemStore64 {
   };
   uint32_t tbase;  // TMEM address of this thread's lane block, column 0
   double* sv;      // this thread's column of the CTA's shared vectors
+  double* sf;      // this thread's pair column of the shared-memory factor chunks
   uint32_t raw[32];
-  __device__ __forceinline__ void init(uint32_t tbase_) { tbase = tbase_; sv = g_smem64 + threadIdx.x; }
+  __device__ __forceinline__ void init(uint32_t tbase_) {
+    tbase = tbase_; sv = g_smem64 + threadIdx.x;
+    sf = g_smem64 + (size_t)CONV_SV_WORDS * CONV_TPB + 2 * threadIdx.x;
+  }
   __device__ __forceinline__ void begin_iteration(int) {}
-  __device__ __forceinline__ void issue(int c, double (&)[UMPC_GEN_CHUNK]) {
+  __device__ __forceinline__ void issue(int c, double (&v)[UMPC_GEN_CHUNK]) {
+    if (in_smem(c)) {
+#pragma unroll
+      for (int p = 0; p < UMPC_GEN_CHUNK / 2; ++p) { const double2 t = *spair(slot(c), p); v[2 * p] = t.x; v[2 * p + 1] = t.y; }
+      return;
+    }
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
                  : "=r"(raw[0]), "=r"(raw[1]), "=r"(raw[2]), "=r"(raw[3]), "=r"(raw[4]), "=r"(raw[5]), "=r"(raw[6]), "=r"(raw[7]), "=r"(raw[8]), "=r"(raw[9]), "=r"(raw[10]), "=r"(raw[11]), "=r"(raw[12]), "=r"(raw[13]), "=r"(raw[14]), "=r"(raw[15]), "=r"(raw[16]), "=r"(raw[17]), "=r"(raw[18]), "=r"(raw[19]), "=r"(raw[20]), "=r"(raw[21]), "=r"(raw[22]), "=r"(raw[23]), "=r"(raw[24]), "=r"(raw[25]), "=r"(raw[26]), "=r"(raw[27]), "=r"(raw[28]), "=r"(raw[29]), "=r"(raw[30]), "=r"(raw[31])
                  : "r"(tbase + (uint32_t)c * (2 * UMPC_GEN_CHUNK)));
   }
-  __device__ __forceinline__ void waitc(int, double (&v)[UMPC_GEN_CHUNK]) {
+  __device__ __forceinline__ void waitc(int c, double (&v)[UMPC_GEN_CHUNK]) {
+    if (in_smem(c)) return;
     asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(raw[0]), "+r"(raw[1]), "+r"(raw[2]), "+r"(raw[3]), "+r"(raw[4]), "+r"(raw[5]), "+r"(raw[6]), "+r"(raw[7]), "+r"(raw[8]), "+r"(raw[9]), "+r"(raw[10]), "+r"(raw[11]), "+r"(raw[12]), "+r"(raw[13]), "+r"(raw[14]), "+r"(raw[15]), "+r"(raw[16]), "+r"(raw[17]), "+r"(raw[18]), "+r"(raw[19]), "+r"(raw[20]), "+r"(raw[21]), "+r"(raw[22]), "+r"(raw[23]), "+r"(raw[24]), "+r"(raw[25]), "+r"(raw[26]), "+r"(raw[27]), "+r"(raw[28]), "+r"(raw[29]), "+r"(raw[30]), "+r"(raw[31]) :: "memory");
 #pragma unroll
     for (int i = 0; i < UMPC_GEN_CHUNK; ++i) v[i] = __hiloint2double((int)raw[2 * i + 1], (int)raw[2 * i]);
   }
   __device__ __forceinline__ void setW(int e, double v) {
+    if (in_smem(e / UMPC_GEN_CHUNK)) {
+      const int r = e % UMPC_GEN_CHUNK;
+      ((double*)spair(slot(e / UMPC_GEN_CHUNK), r / 2))[r & 1] = v;
+      return;
+    }
     asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(tbase + 2u * (uint32_t)e), "r"(__double2loint(v)),
                  "r"(__double2hiint(v)) : "memory");
   }
   __device__ __forceinline__ void setChunk(int c, const double (&v)[UMPC_GEN_CHUNK]) {
+    if (in_smem(c)) {
+#pragma unroll
+      for (int p = 0; p < UMPC_GEN_CHUNK / 2; ++p) *spair(slot(c), p) = make_double2(v[2 * p], v[2 * p + 1]);
+      return;
+    }
     int u[32];
 #pragma unroll
     for (int i = 0; i < UMPC_GEN_CHUNK; ++i) { u[2 * i] = __double2loint(v[i]); u[2 * i + 1] = __double2hiint(v[i]); }
@@ -187,6 +221,7 @@ template <class ST64>
 struct SolverF64T {
   typedef umpc64::UmpcParams Params;
   static constexpr int kMinBlocks = 1;
+  static constexpr bool kDynamicItems = true;   // 25, 50, 75 .. iterations per tile: warps take their next tile when free
   ST64 st;
   template <int TPB>
   static __device__ __forceinline__ uint32_t acquire(uint32_t* slot) { return Store64Traits<ST64>::template acquire<TPB>(slot); }
@@ -249,6 +284,7 @@ struct UmpcConv {
   int tpb = 64;  // streamed store only: 64 slightly ahead of 128 (UMPC_CONV_TPB to override)
   bool on_chip = true;  // TmemStore64 (one 128-thread CTA per SM); UMPC_CONV_STORE=glob selects the streamed store
   bool attr_set = false;
+  int nsm = 148;
 };
 
 int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState* s) {
@@ -275,6 +311,7 @@ int umpc_conv_create(UmpcConv** out, int Bp, const UmpcBatchParams* bp, DevState
   cudaError_t e = cudaMalloc(&c->slab, (size_t)C64_ROWS * Bp * sizeof(double));
   if (e != cudaSuccess) { delete c; return (int)e; }
   if (const char* t = getenv("UMPC_CONV_STORE")) c->on_chip = strcmp(t, "glob") != 0;
+  { int dev = 0; cudaGetDevice(&dev); int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) c->nsm = n; }
   if (const char* t = getenv("UMPC_CONV_TPB")) {  // tuning knob
     const int v = atoi(t);
     if (v == 64 || v == 128) c->tpb = v;
@@ -309,7 +346,8 @@ void umpc_conv_destroy(UmpcConv* c) {
   delete c;
 }
 
-static constexpr size_t kConvSmem = (size_t)CONV_SV_WORDS * sizeof(double) * CONV_TPB;
+static constexpr size_t kConvSmem = (size_t)(CONV_SV_WORDS + CONV_SMEM_CHUNKS * UMPC_GEN_CHUNK) * sizeof(double) * CONV_TPB;
+static_assert(kConvSmem + 4096 <= 227 * 1024, "shared memory of the converged-mode CTA");
 
 // opt-in to the 117 KB of dynamic shared memory, once per process (the attribute is per function, not per device context
 // here: one device per process)
@@ -350,8 +388,11 @@ int umpc_conv_launch_rollout(UmpcConv* c, const SimParams* sim, const DevState* 
   kp.mpc = c->mpc; kp.sim = *sim;
   if (c->on_chip) {
     if (int rc = conv_set_attrs(c)) return rc;
-    umpc_rollout_kernel<CONV_TPB, SolverF64Tmem><<<(s->B + CONV_TPB - 1) / CONV_TPB, CONV_TPB, kConvSmem, stream>>>(
-        kp, *s, *wlp, step0, nsteps, fire, tvals, lg, 1);
+    // persistent: one CTA per SM, its warps take the CTA's tiles (t = blockIdx + k gridDim) one after the other
+    const int ntiles = s->B / 32;
+    int grid = c->nsm < ntiles ? c->nsm : ntiles;
+    if ((ntiles + grid - 1) / grid > UMPC_MAX_CHUNKED_TILES) grid = (ntiles + UMPC_MAX_CHUNKED_TILES - 1) / UMPC_MAX_CHUNKED_TILES;
+    umpc_rollout_kernel<CONV_TPB, SolverF64Tmem><<<grid, CONV_TPB, kConvSmem, stream>>>(kp, *s, *wlp, step0, nsteps, fire, tvals, lg, 1);
     return (int)cudaGetLastError();
   }
   const int grid = (s->B + c->tpb - 1) / c->tpb;

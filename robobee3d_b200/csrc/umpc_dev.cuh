@@ -372,7 +372,10 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   const int ntile_cta = ntiles > (int)blockIdx.x ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   __shared__ int tile_done[UMPC_MAX_CHUNKED_TILES];
   __shared__ int next_item;
-  if (nch > 1) {
+  // SOLVER::kDynamicItems: hand the items out through the counter also when nch == 1 (solvers whose solve time differs
+  // from tile to tile -- converged mode: 25, 50, 75 .. iterations -- would leave warp slots idle with a static deal)
+  constexpr bool kDyn = SOLVER::kDynamicItems;
+  if (nch > 1 || kDyn) {
     for (int i = threadIdx.x; i < ntile_cta; i += TPB) tile_done[i] = 0;
     if (threadIdx.x == 0) next_item = WPC;   // items 0 .. WPC-1 are the warps' first ones
     __syncthreads();
@@ -476,7 +479,7 @@ umpc_rollout_kernel(const __grid_constant__ KernelParamsT<typename SOLVER::Param
   eb[ROWF(ROW_METRICS + 0)] = err; eb[ROWF(ROW_METRICS + 1)] = eff; eb[ROWF(ROW_METRICS + 5)] = cerr; eb[ROWF(ROW_METRICS + 6)] = ceff;
   ((int*)eb)[ROWF(ROW_METRICS + 2)] = nsolve; ((int*)eb)[ROWF(ROW_METRICS + 3)] = nstep;
   eb[ROWF(ROW_METRICS + 4)] = pert_done;
-  if (nch > 1) {   // publish the tile's state to the warp that runs its next chunk
+  if (nch > 1 || kDyn) {   // publish the tile's state to the warp that runs its next chunk
     __threadfence_block();
     __syncwarp();
     if ((threadIdx.x & 31) == 0) *(volatile int*)&tile_done[slot] = chunk + 1;

@@ -266,6 +266,7 @@ template <int TPB_, class ST, bool PERENV = false, bool INFO = true>
 struct SolverF32 {
   typedef UmpcParams Params;
   static constexpr int kMinBlocks = ST::kTmem ? 1 : 224 / TPB_;
+  static constexpr bool kDynamicItems = false;  // fixed iteration count: every item of a launch takes the same time
   ST st;
   float* eb;
   template <int TPB>
