@@ -85,8 +85,16 @@ class ClockSampler:
         sm = sorted(float(r[0]) for r in self.rows)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for j, n in enumerate(names) if any(r[3 + j].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
+        out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+               "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
+        rec = os.environ.get("BENCH_CLOCK_RECORD")   # full record of the sampler (one row per 0.1 s) for sustained runs
+        if rec:
+            with open(rec, "w") as f:
+                f.write("sm_mhz,sm_max_mhz,power_w,hw_slowdown,hw_thermal_slowdown,sw_thermal_slowdown,sw_power_cap\n")
+                for r in self.rows:
+                    f.write(",".join(r) + "\n")
+            out["sm_mhz_min"], out["sm_mhz_max_seen"] = sm[0], sm[-1]
+        return out
 
 
 def make_ics(nenv, seed):
@@ -214,6 +222,65 @@ def _np_dyn_step(p, R, dq, u, dt, Ib=np.array([3333.0, 3333.0, 1000.0]), g=9.81e
     K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
     a, b = (1 - th * th / 6, 0.5 - th * th / 24) if th < 1e-4 else (np.sin(th) / th, (1 - np.cos(th)) / th ** 2)
     return p + dt * dq[:3], R @ (np.eye(3) + a * K + b * (K @ K)), np.r_[dq[:3] + dt * dv, w + dt * dw]
+
+
+def run_hostlink(args):
+    """--workload hostlink: the host link's own ceiling for the e2e call's traffic.  Every rank copies exactly the bytes one
+    `umpcBatchEnvStep` call moves (108 B per env each way, pinned buffers) with plain asynchronous copies -- host->device and
+    device->host on two streams at once, no kernel -- and reports bytes/s per rank and in all, and the env-steps/s a call
+    that did NOTHING but move its bytes could reach.  VERDICT r01 item 8: the measurement to hold the 8-GPU e2e figure against."""
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _bind_to_gpu_numa_node(local)
+    nenv = args.envs
+    nbytes = 108 * nenv
+    hin = torch.empty(nbytes, dtype=torch.uint8).pin_memory(); hout = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    din = torch.empty(nbytes, dtype=torch.uint8, device="cuda"); dout = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    calls = 125
+
+    def step():
+        for _ in range(calls):
+            with torch.cuda.stream(s1):
+                din.copy_(hin, non_blocking=True)
+            with torch.cuda.stream(s2):
+                hout.copy_(dout, non_blocking=True)
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    s1.wait_stream(torch.cuda.current_stream()); s2.wait_stream(torch.cuda.current_stream())
+    for _ in range(args.steps):
+        step()
+    torch.cuda.current_stream().wait_stream(s1); torch.cuda.current_stream().wait_stream(s2)
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+    sec = float(t[0])
+    if rank == 0:
+        per_dir = nbytes * calls * args.steps / sec
+        print(json.dumps({"metric": "host link ceiling for the e2e call's bytes (plain async copies, both directions at once)",
+                          "value": 2 * per_dir * world * 1e-9, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                          "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "u8", "data": "synthetic",
+                          "config": {"workload": "hostlink: %d envs per GPU x 108 B each way per call, %d calls per step, pinned host buffers" % (nenv, calls)},
+                          "gb_per_s_per_rank_each_way": per_dir * 1e-9, "ms_per_call": 1e3 * sec / (args.steps * calls),
+                          "env_steps_per_s_if_a_call_only_moved_its_bytes": nenv * calls * args.steps * world / sec,
+                          "gpu_launches": 0}))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
 
 
 def run_small(args):
@@ -606,7 +673,7 @@ def main():
                     help="plant steps (each with an MPC solve when hlInterval is None) advanced per launch of the rollout kernel")
     ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
     ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
-    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096", "quad", "fused-wlqp", "umpc-n"],
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096", "quad", "fused-wlqp", "umpc-n", "hostlink"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     ap.add_argument("--converged", action="store_true",
@@ -620,6 +687,8 @@ def main():
         return run_dirtran(args)
     if args.workload in ("c1", "qp4096"):
         return run_small(args)
+    if args.workload == "hostlink":
+        return run_hostlink(args)
     if args.workload in ("quad", "fused-wlqp", "umpc-n"):
         return run_gqp(args)
 
@@ -719,9 +788,39 @@ def main():
         assert torch.isfinite(hp).all()
         e2e = {"value": nenv * world * args.steps * ne2e / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": 27 * 4 * nenv * ne2e,
                "d2h_bytes_per_step": 27 * 4 * nenv * ne2e, "ms_per_step": 1e3 * float(te[0]) / args.steps,
-               "calls_per_step": ne2e, "ms_per_call": 1e3 * float(te[0]) / (args.steps * ne2e), "gpu_launches": args.steps * ne2e,
+               "calls_per_step": ne2e, "pull_window_ctas": int(os.environ.get("UMPC_E2E_WINDOW", "32")), "ms_per_call": 1e3 * float(te[0]) / (args.steps * ne2e), "gpu_launches": args.steps * ne2e,
                "call": "umpcBatchEnvStep (pinned host buffers read and written in place by one zero-copy kernel; umpcUpdate + clip + "
                        "quadrotorNLDyn per env)"}
+        # second host-buffer call of the API, the one a caller of the reference's controlTest makes: initial conditions in,
+        # `spl` closed-loop steps on the device, final states + logMetric sums out (reported beside, not instead of, the above)
+        if args.hl_interval is None and not args.tpb:
+            from robobee3d_b200.batch import _vp
+            gp, gR, gdq, guq = (np.empty((nenv, 3), np.float32), np.empty((nenv, 9), np.float32), np.empty((nenv, 6), np.float32),
+                                np.empty((nenv, 3), np.float32))
+            gm = np.empty((nenv, 4), np.float32)
+            sp, sR, sdq = hp.numpy().copy(), hR.numpy().copy(), hdq.numpy().copy()
+
+            def flight():
+                L = b2.lib
+                L.umpcBatchSetState(b2.h, _vp(sp), _vp(sR), _vp(sdq), None, None)
+                L.umpcBatchRollout(b2.h, spl)
+                L.umpcBatchGetState(b2.h, _vp(gp), _vp(gR), _vp(gdq), _vp(guq))
+                L.umpcBatchGetMetrics(b2.h, _vp(gm))
+            for _ in range(args.warmup):
+                flight()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                flight()
+            barrier()
+            tf = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+            assert np.isfinite(gp).all()
+            e2e["flight_call"] = {"value": nenv * world * args.steps * spl / float(tf[0]), "unit": UNIT, "ms_per_step": 1e3 * float(tf[0]) / args.steps,
+                                  "h2d_bytes_per_step": 18 * 4 * nenv, "d2h_bytes_per_step": (21 + 4) * 4 * nenv,
+                                  "call": "umpcBatchSetState (host ICs) + umpcBatchRollout(%d) + umpcBatchGetState + umpcBatchGetMetrics (pageable host "
+                                          "arrays): the controlTest-shaped call, plant on the device" % spl}
         b2.close()
 
     mean_iter = float(b.solve_info()["iter"].mean()) if args.converged else 50.0
@@ -787,7 +886,7 @@ def main():
             from oracle import binding as OB
             cores = os.cpu_count() or 1
             ns = min(nenv, cores * 64)
-            steps_cpu = 250                      # ~1.6 s per worker at ~100 us per umpcUpdate: ~25 core-seconds in all
+            steps_cpu = 800                      # ~2.2 s per worker at ~27k env-steps/s per core (>= 2 s per worker)
             done, tmax, _, kind, per_core = OB.cpu_env_steps(_cpu_ics(ns), steps_cpu, cores, per_worker=True)
             line["cpu_baseline"] = {"value": done / tmax, "unit": UNIT, "cores": cores, "kind": kind,
                                     "per_core": {"min": min(per_core), "median": sorted(per_core)[len(per_core) // 2], "max": max(per_core)},
