@@ -283,6 +283,54 @@ def run_hostlink(args):
     return 0
 
 
+def run_flapsweep(args):
+    """--workload flapsweep (row f2): sweepFile's open-loop wing simulations (sdab_num_wrenchmap_simgen.py:19-75), the
+    reference's 8 x 8 x 1 x 8 x 8 grid (4,096 simulations x 1,001 steps of 0.1 ms) or a finer grid with --envs (rounded to k^4),
+    all in ONE launch.  value = simulation steps/s (one step of one two-wing simulation); e2e = the same through host arrays
+    (grid in, numkins rows out); cpu_baseline = the numpy oracle (vectorised over simulations) on a sample."""
+    from robobee3d_b200 import flapping
+    k = 8 if args.envs == NENV_PER_GPU else max(2, int(round(args.envs ** 0.25)))
+    grids = (np.linspace(90, 160, k), np.linspace(-0.5, 0.5, k), [0.17], np.linspace(-0.2, 0.2, k), np.linspace(-0.2, 0.2, k))
+    nsim, nst = k ** 4, flapping.open_loop_steps(100.0, 0.1)
+    clocks = ClockSampler(0)
+    for _ in range(max(args.warmup, 3)):
+        flapping.sweep(*grids)
+    clocks.start()
+    ms, wall = [], []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        res, m = flapping.sweep(*grids, return_ms=True)
+        wall.append(time.perf_counter() - t0); ms.append(m)
+    ck = clocks.finish()
+    assert np.isfinite(res).all()
+    kms = float(np.mean(ms))
+    L = flapping._bind()
+    peak64 = L.umpcMeasureFp64Peak(0, 1 << 16)
+    fl = 2 * 721.0 * nsim * nst      # executed DFMA(2) + DMUL + DADD per wing and step in the kernel's SASS, sincos polynomials included
+    line = {"metric": "open-loop flapping-wing simulation steps/s (sweepFile: two wings, quasi-steady aero, fixed base)",
+            "value": nsim * nst / (kms * 1e-3), "unit": "sim-steps/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": kms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "sdab_num_wrenchmap_simgen.py grid %d^4 = %d simulations x %d steps of 0.1 ms, one launch; inputs are KB: "
+                                   "nothing to flush between launches" % (k, nsim, nst)},
+            "gpu_launches": args.steps, "clocks": ck,
+            "roofline": {"bound": "fp64", "achieved": fl / (kms * 1e-3) * 1e-12, "peak": peak64, "unit": "TFLOP/s",
+                         "frac": fl / (kms * 1e-3) * 1e-12 / peak64, "traffic": None, "kernel": "fw::sweep_kernel",
+                         "note": "%d threads (one per wing) on 148 SMs: the reference's grid does not fill the GPU; latency-bound "
+                                 "dependent chain of ~1,250 instructions per step" % (2 * nsim)},
+            "e2e": {"value": nsim * nst / float(np.median(wall)), "unit": "sim-steps/s", "h2d_bytes_per_step": 40 * nsim,
+                    "d2h_bytes_per_step": 120 * nsim, "call": "flapping.sweep (fwOpenLoopSweep with host arrays)"}}
+    if not args.no_cpu:
+        from oracle import flapping_oracle as fo
+        ns = min(nsim, 1024)
+        t0 = time.perf_counter()
+        fo.sweep_features(res[:ns, :5])
+        tc = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": ns * nst / tc, "unit": "sim-steps/s", "cores": 1, "kind": "port",
+                                "sample": "%d of the %d simulations, numpy oracle vectorised over simulations (the reference steps pybullet, absent here)" % (ns, nsim)}
+    print(json.dumps(line))
+    return 0
+
+
 def run_small(args):
     """BASELINE configs[0] and configs[1] (extra lines, not the driver's headline):
     c1     : ONE controlTest flight (tend 500 ms, hlInterval 5 ms: ~96 controller calls) through the drop-in
@@ -673,7 +721,7 @@ def main():
                     help="plant steps (each with an MPC solve when hlInterval is None) advanced per launch of the rollout kernel")
     ap.add_argument("--horizon", type=int, default=10, help="--workload dirtran: knots N (3, 5, 10, 15, 20)")
     ap.add_argument("--dt-steps", type=int, default=10, help="--workload dirtran: MPC periods per launch")
-    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096", "quad", "fused-wlqp", "umpc-n", "hostlink"],
+    ap.add_argument("--workload", default="mc", choices=["mc", "cascade-wlcon", "cascade-wlqp", "dirtran", "c1", "qp4096", "quad", "fused-wlqp", "umpc-n", "hostlink", "flapsweep"],
                     help="mc: BASELINE configs[2] (the headline line); cascade-*: configs[3], UprightMPC2 -> WL stage -> "
                          "actualT0 feedback per env-step (extra measurement, not the driver's line)")
     ap.add_argument("--converged", action="store_true",
@@ -689,6 +737,8 @@ def main():
         return run_small(args)
     if args.workload == "hostlink":
         return run_hostlink(args)
+    if args.workload == "flapsweep":
+        return run_flapsweep(args)
     if args.workload in ("quad", "fused-wlqp", "umpc-n"):
         return run_gqp(args)
 
