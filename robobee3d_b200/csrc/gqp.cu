@@ -77,6 +77,9 @@ __device__ __forceinline__ int tri(int i, int j) { return (i * (i + 1)) / 2 + j;
 // shared-memory map of one warp (doubles)
 struct Smem {
   double *L, *As, *x, *xt, *wv, *qs, *D, *invd, *tmp, *z, *y, *ls, *us, *rv, *zt, *E;
+  // the batch's pattern of A (CSR + CSC view), copied in at kernel start: every ADMM iteration walks it twice, and from
+  // global memory each walk was a chain of dependent L1 hits
+  int *rowptr, *colidx, *colptr, *cscrow, *cscpos;
   __device__ void carve(double* base, int n, int m, int nnz) {
     L = base; base += (size_t)n * (n + 1) / 2;
     As = base; base += nnz;
@@ -84,38 +87,63 @@ struct Smem {
     D = base; base += n; invd = base; base += n; tmp = base; base += n;
     z = base; base += m; y = base; base += m; ls = base; base += m; us = base; base += m;
     rv = base; base += m; zt = base; base += m; E = base; base += m;
+    int* ib = (int*)base;
+    rowptr = ib; ib += m + 1; colptr = ib; ib += n + 1; colidx = ib; ib += nnz; cscrow = ib; ib += nnz; cscpos = ib;
   }
 };
-__host__ __device__ inline size_t smem_doubles(int n, int m, int nnz) { return (size_t)n * (n + 1) / 2 + nnz + 7 * (size_t)n + 7 * (size_t)m; }
+__host__ __device__ inline size_t smem_doubles(int n, int m, int nnz) {
+  return (size_t)n * (n + 1) / 2 + nnz + 7 * (size_t)n + 7 * (size_t)m + ((size_t)(m + 1) + (n + 1) + 3 * (size_t)nnz + 1) / 2;
+}
+
+// Loop over "my" entries lane, lane + 32, .. < n with a WARP-UNIFORM trip count and the bound test inside.  Written as
+// `for (j = lane; j < n; j += 32)` the lanes that run one trip fewer leave the loop as a group of their own, and the
+// groups were seen not to re-converge: every later warp-collective (the shuffles of the triangular solves, __syncwarp)
+// then took its divergent path and the kernel executed 1.7x the instructions (ncu r02x).
+#define LANE_LOOP(i, n) for (int i##_b = 0, i = lane; i##_b < (n); i##_b += 32, i += 32) if (i < (n))
 
 // K = c D P D + sigma I + A_s' diag(rho) A_s (packed lower) and its Cholesky factor, in place in sm.L
 __device__ void form_and_factor(const Dev& d, const Smem& sm, const double* __restrict__ P, double c, int lane) {
   const int n = d.s.n, m = d.s.m;
   for (int i = 0; i < n; ++i) {
     const double cdi = c * sm.D[i];
-    for (int j = lane; j <= i; j += 32) sm.L[tri(i, j)] = cdi * sm.D[j] * P[(size_t)i * n + j] + (i == j ? d.s.sigma : 0.0);
+    LANE_LOOP(j, i + 1) sm.L[tri(i, j)] = cdi * sm.D[j] * P[(size_t)i * n + j] + (i == j ? d.s.sigma : 0.0);
   }
   __syncwarp();
-  for (int r = lane; r < m; r += 32) {
+  // + A_s' diag(rho) A_s: rows one after the other, the row's entry pairs (a >= b) spread over the lanes -- within one row
+  // every pair is a different entry of K, so no atomics (the shared-memory double atomicAdd is a compare-and-swap loop,
+  // and its retries split the warp)
+  for (int r = 0; r < m; ++r) {
+    const int r0 = sm.rowptr[r], cnt = sm.rowptr[r + 1] - r0, npair = (cnt * (cnt + 1)) >> 1;
     const double rho = sm.rv[r];
-    for (int a = d.rowptr[r]; a < d.rowptr[r + 1]; ++a) {
-      const double ra = rho * sm.As[a];
-      const int ca = d.colidx[a];
-      for (int b = d.rowptr[r]; b <= a; ++b) atomicAdd(&sm.L[tri(ca, d.colidx[b])], ra * sm.As[b]);  // columns increase along a row
+    for (int pb = 0; pb < npair; pb += 32) {
+      const int p = pb + lane;
+      if (p < npair) {
+        int a = (int)((sqrtf(8.0f * (float)p + 1.0f) - 1.0f) * 0.5f);   // pair p = (a, b), b <= a; branch-free decode
+        a += (((a + 1) * (a + 2)) >> 1) <= p;
+        a -= ((a * (a + 1)) >> 1) > p;
+        const int b = p - ((a * (a + 1)) >> 1);
+        sm.L[tri(sm.colidx[r0 + a], sm.colidx[r0 + b])] += rho * sm.As[r0 + a] * sm.As[r0 + b];   // columns increase along a row
+      }
     }
+    __syncwarp();
   }
-  __syncwarp();
   for (int k = 0; k < n; ++k) {
     const double dk = sqrt(sm.L[tri(k, k)]);
     const double inv = 1.0 / dk;
     __syncwarp();
     if (lane == 0) { sm.L[tri(k, k)] = dk; sm.invd[k] = inv; }
-    for (int i = k + 1 + lane; i < n; i += 32) sm.L[tri(i, k)] *= inv;
+    for (int ib = k + 1; ib < n; ib += 32) {
+      const int i = ib + lane;
+      if (i < n) sm.L[tri(i, k)] *= inv;
+    }
     __syncwarp();
-    for (int i = k + 1 + lane; i < n; i += 32) {
-      const double lik = sm.L[tri(i, k)];
-      double* row = sm.L + tri(i, 0);
-      for (int j = k + 1; j <= i; ++j) row[j] -= lik * sm.L[tri(j, k)];
+    for (int ib = k + 1; ib < n; ib += 32) {
+      const int i = ib + lane;
+      if (i < n) {
+        const double lik = sm.L[tri(i, k)];
+        double* row = sm.L + tri(i, 0);
+        for (int j = k + 1; j <= i; ++j) row[j] -= lik * sm.L[tri(j, k)];
+      }
     }
     __syncwarp();
   }
@@ -134,9 +162,71 @@ __device__ __forceinline__ void chol_solve(const Smem& sm, int n, int lane) {
     const double xk = sm.wv[k] * sm.invd[k];
     if (lane == 0) sm.xt[k] = xk;
     const double* row = sm.L + tri(k, 0);
-    for (int j = lane; j < k; j += 32) sm.wv[j] -= row[j] * xk;
+    LANE_LOOP(j, k) sm.wv[j] -= row[j] * xk;
   }
   __syncwarp();
+}
+
+// The same two sweeps with the vector in REGISTERS (lane l owns entries l, l + 32, ..: NR = ceil(n / 32) of them): the
+// pivot entry travels by shuffle, each lane updates its own entries.  Same operations in the same order as chol_solve
+// (bit-identical results), a tenth of the instructions: the shared-memory version spends ~60 instructions per column on
+// loop control, index arithmetic and the round trip of the vector (ncu r02v: its two inner loops were 70 % of all
+// executed instructions of the kernel).
+template <int NR>
+__device__ __forceinline__ void chol_solve_reg(const Smem& sm, int n, int lane) {
+  double v[NR];
+  int base[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const int i = lane + 32 * r;
+    v[r] = i < n ? sm.xt[i] : 0.0;
+    base[r] = (i * (i + 1)) / 2;
+  }
+#pragma unroll
+  for (int s = 0; s < NR; ++s) {            // forward: L w = b, column by column
+    const int kend = min(32, n - 32 * s);
+    for (int kk = 0; kk < kend; ++kk) {
+      const int k = 32 * s + kk;
+      const double wk = __shfl_sync(0xffffffffu, v[s], kk) * sm.invd[k];
+      if (lane == kk) v[s] = wk;
+#pragma unroll
+      for (int r = s; r < NR; ++r) {
+        const int i = lane + 32 * r;
+        if (i > k && i < n) v[r] -= sm.L[base[r] + k] * wk;
+      }
+    }
+  }
+#pragma unroll
+  for (int s = NR - 1; s >= 0; --s) {       // backward: L' x = w, row k of L holds column k of L'
+    const int kend = min(32, n - 32 * s);
+    for (int kk = kend - 1; kk >= 0; --kk) {
+      const int k = 32 * s + kk;
+      const double xk = __shfl_sync(0xffffffffu, v[s], kk) * sm.invd[k];
+      if (lane == kk) v[s] = xk;
+      const double* row = sm.L + (k * (k + 1)) / 2;
+#pragma unroll
+      for (int r = 0; r <= s; ++r) {
+        const int j = lane + 32 * r;
+        if (j < k) v[r] -= row[j] * xk;
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const int i = lane + 32 * r;
+    if (i < n) sm.xt[i] = v[r];
+  }
+  __syncwarp();
+}
+__device__ __forceinline__ void chol_solve_any(const Smem& sm, int n, int lane) {
+  __syncwarp();
+  switch ((n + 31) >> 5) {
+    case 1: chol_solve_reg<1>(sm, n, lane); break;
+    case 2: chol_solve_reg<2>(sm, n, lane); break;
+    case 3: chol_solve_reg<3>(sm, n, lane); break;
+    case 4: chol_solve_reg<4>(sm, n, lane); break;
+    default: chol_solve(sm, n, lane);
+  }
 }
 
 // per-row rho from the constraint type (set_rho_vec / update_rho_vec, auxil.c:77-146)
@@ -154,23 +244,23 @@ __device__ Resid residuals(const Dev& d, const Smem& sm, const double* __restric
   const int n = d.s.n, m = d.s.m;
   Resid r;
   double pri = 0, nz = 0, nAx = 0, pri_s = 0, pn_s = 0;
-  for (int i = lane; i < m; i += 32) {
+  LANE_LOOP(i, m) {
     double ax = 0;
-    for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) ax += sm.As[a] * sm.x[d.colidx[a]];
+    for (int a = sm.rowptr[i]; a < sm.rowptr[i + 1]; ++a) ax += sm.As[a] * sm.x[sm.colidx[a]];
     const double einv = 1.0 / sm.E[i], rp = ax - sm.z[i];
     pri = fmax(pri, fabs(einv * rp)); nz = fmax(nz, fabs(einv * sm.z[i])); nAx = fmax(nAx, fabs(einv * ax));
     pri_s = fmax(pri_s, fabs(rp)); pn_s = fmax(pn_s, fmax(fabs(sm.z[i]), fabs(ax)));
   }
   // tmp = D .* x  (for P_s x = c D (P (D x)))
-  for (int j = lane; j < n; j += 32) sm.tmp[j] = sm.D[j] * sm.x[j];
+  LANE_LOOP(j, n) sm.tmp[j] = sm.D[j] * sm.x[j];
   __syncwarp();
   double dua = 0, nq = 0, nAty = 0, nPx = 0, dua_s = 0, dn_s = 0;
-  for (int j = lane; j < n; j += 32) {
+  LANE_LOOP(j, n) {
     double px = 0, aty = 0;
     const double* prow = P + (size_t)j * n;
     for (int i = 0; i < n; ++i) px += prow[i] * sm.tmp[i];
     px *= c * sm.D[j];
-    for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) aty += sm.As[d.cscpos[k]] * sm.y[d.cscrow[k]];
+    for (int k = sm.colptr[j]; k < sm.colptr[j + 1]; ++k) aty += sm.As[sm.cscpos[k]] * sm.y[sm.cscrow[k]];
     const double dinv = 1.0 / sm.D[j], rd = sm.qs[j] + px + aty;
     dua = fmax(dua, fabs(dinv * rd)); nq = fmax(nq, fabs(dinv * sm.qs[j])); nAty = fmax(nAty, fabs(dinv * aty)); nPx = fmax(nPx, fabs(dinv * px));
     dua_s = fmax(dua_s, fabs(rd)); dn_s = fmax(dn_s, fmax(fabs(sm.qs[j]), fmax(fabs(aty), fabs(px))));
@@ -190,6 +280,10 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   const int n = d.s.n, m = d.s.m, nnz = d.s.nnz;
   Smem sm;
   sm.carve(smem_d, n, m, nnz);
+  LANE_LOOP(i, m + 1) sm.rowptr[i] = d.rowptr[i];
+  LANE_LOOP(i, n + 1) sm.colptr[i] = d.colptr[i];
+  LANE_LOOP(i, nnz) { sm.colidx[i] = d.colidx[i]; sm.cscrow[i] = d.cscrow[i]; sm.cscpos[i] = d.cscpos[i]; }
+  __syncwarp();
   const double* P = d.P + (size_t)qp * n * n;
   const double* Av = d.Av + (size_t)qp * nnz;
   const double* q0 = d.q + (size_t)qp * n;
@@ -200,7 +294,7 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   double c = d.c[qp], rho = d.rho[qp];
   const double INF = d.s.infty;
   // ---- osqp_update_bounds with the OLD scaling: constraint types (auxil.c:103-146) ---------------------------------
-  for (int i = lane; i < m; i += 32) {
+  LANE_LOOP(i, m) {
     const double eo = gE[i];
     const double lo = fmax(l0[i], -INF), hi = fmin(u0[i], INF);
     const double ls = eo * lo, us = eo * hi;
@@ -211,40 +305,40 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
     gct[i] = type;
     sm.E[i] = eo;
   }
-  for (int j = lane; j < n; j += 32) sm.D[j] = gD[j];
+  LANE_LOOP(j, n) sm.D[j] = gD[j];
   __syncwarp();
   // ---- osqp_update_P_A: re-equilibrate (scale_data, scaling.c:44-156) ------------------------------------------------
   if (rescale) {
-    for (int j = lane; j < n; j += 32) sm.D[j] = 1.0;
-    for (int i = lane; i < m; i += 32) sm.E[i] = 1.0;
+    LANE_LOOP(j, n) sm.D[j] = 1.0;
+    LANE_LOOP(i, m) sm.E[i] = 1.0;
     c = 1.0;
     __syncwarp();
     // |P| (lower triangle) parked in the factor's space during the passes
     for (int i = 0; i < n; ++i)
-      for (int j = lane; j <= i; j += 32) sm.L[tri(i, j)] = fabs(P[(size_t)i * n + j]);
+      LANE_LOOP(j, i + 1) sm.L[tri(i, j)] = fabs(P[(size_t)i * n + j]);
     __syncwarp();
     for (int it = 0; it < d.s.scaling_iters; ++it) {
       // column norms of [P_s; A_s], row norms of A_s with the current D, E, c
-      for (int j = lane; j < n; j += 32) {
+      LANE_LOOP(j, n) {
         double v = 0;
         for (int i = 0; i < n; ++i) v = fmax(v, sm.L[i >= j ? tri(i, j) : tri(j, i)] * sm.D[i]);
         v *= c * sm.D[j];
         double va = 0;
-        for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) va = fmax(va, fabs(Av[d.cscpos[k]]) * sm.E[d.cscrow[k]]);
+        for (int k = sm.colptr[j]; k < sm.colptr[j + 1]; ++k) va = fmax(va, fabs(Av[sm.cscpos[k]]) * sm.E[sm.cscrow[k]]);
         sm.tmp[j] = 1.0 / sqrt(limit_scaling(fmax(v, va * sm.D[j])));
       }
-      for (int i = lane; i < m; i += 32) {
+      LANE_LOOP(i, m) {
         double v = 0;
-        for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) v = fmax(v, fabs(Av[a]) * sm.D[d.colidx[a]]);
+        for (int a = sm.rowptr[i]; a < sm.rowptr[i + 1]; ++a) v = fmax(v, fabs(Av[a]) * sm.D[sm.colidx[a]]);
         sm.zt[i] = 1.0 / sqrt(limit_scaling(v * sm.E[i]));
       }
       __syncwarp();
-      for (int j = lane; j < n; j += 32) sm.D[j] *= sm.tmp[j];
-      for (int i = lane; i < m; i += 32) sm.E[i] *= sm.zt[i];
+      LANE_LOOP(j, n) sm.D[j] *= sm.tmp[j];
+      LANE_LOOP(i, m) sm.E[i] *= sm.zt[i];
       __syncwarp();
       // cost normalisation (scaling.c:100-131): mean column norm of P_s, |q_s|_inf
       double csum = 0, nq = 0;
-      for (int j = lane; j < n; j += 32) {
+      LANE_LOOP(j, n) {
         double v = 0;
         for (int i = 0; i < n; ++i) v = fmax(v, sm.L[i >= j ? tri(i, j) : tri(j, i)] * sm.D[i]);
         csum += c * sm.D[j] * v;
@@ -256,18 +350,18 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
       c *= 1.0 / ct;
       __syncwarp();
     }
-    for (int j = lane; j < n; j += 32) gD[j] = sm.D[j];
-    for (int i = lane; i < m; i += 32) gE[i] = sm.E[i];
+    LANE_LOOP(j, n) gD[j] = sm.D[j];
+    LANE_LOOP(i, m) gE[i] = sm.E[i];
   }
   // ---- scaled data ---------------------------------------------------------------------------------------------------
-  for (int i = lane; i < m; i += 32) {
+  LANE_LOOP(i, m) {
     const double e = sm.E[i];
     sm.ls[i] = e * fmax(l0[i], -INF); sm.us[i] = e * fmin(u0[i], INF);
     sm.rv[i] = rho_of(gct[i], rho);
-    for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) sm.As[a] = e * Av[a] * sm.D[d.colidx[a]];
+    for (int a = sm.rowptr[i]; a < sm.rowptr[i + 1]; ++a) sm.As[a] = e * Av[a] * sm.D[sm.colidx[a]];
     sm.z[i] = d.zs[(size_t)qp * m + i]; sm.y[i] = d.ys[(size_t)qp * m + i];
   }
-  for (int j = lane; j < n; j += 32) { sm.qs[j] = c * sm.D[j] * q0[j]; sm.x[j] = d.xs[(size_t)qp * n + j]; }
+  LANE_LOOP(j, n) { sm.qs[j] = c * sm.D[j] * q0[j]; sm.x[j] = d.xs[(size_t)qp * n + j]; }
   __syncwarp();
   form_and_factor(d, sm, P, c, lane);
   // ---- ADMM (osqp.c:352-500) -----------------------------------------------------------------------------------------
@@ -276,25 +370,37 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   bool checked = false;
   Resid res;
   for (iter = 1; iter <= d.s.max_iter; ++iter) {
-    for (int j = lane; j < n; j += 32) {
-      double v = sigma * sm.x[j] - sm.qs[j];
-      for (int k = d.colptr[j]; k < d.colptr[j + 1]; ++k) {
-        const int r = d.cscrow[k];
-        v += sm.As[d.cscpos[k]] * (sm.rv[r] * sm.z[r] - sm.y[r]);
+    // (loops over the lanes' entries have WARP-UNIFORM trip counts with the bound test inside: a `for (j = lane; j < n; ..)`
+    // leaves the lanes that ran one trip fewer in a group of their own, and the groups do not re-converge on their own --
+    // the shuffles of the triangular solves then ran once per group through the divergent-shuffle slow path, ncu r02x)
+    for (int jb = 0; jb < n; jb += 32) {
+      const int j = jb + lane;
+      if (j < n) {
+        double v = sigma * sm.x[j] - sm.qs[j];
+        for (int k = sm.colptr[j]; k < sm.colptr[j + 1]; ++k) {
+          const int r = sm.cscrow[k];
+          v += sm.As[sm.cscpos[k]] * (sm.rv[r] * sm.z[r] - sm.y[r]);
+        }
+        sm.xt[j] = v;
       }
-      sm.xt[j] = v;
     }
-    chol_solve(sm, n, lane);
-    for (int i = lane; i < m; i += 32) {
-      double zt = 0;
-      for (int a = d.rowptr[i]; a < d.rowptr[i + 1]; ++a) zt += sm.As[a] * sm.xt[d.colidx[a]];
-      const double rv = sm.rv[i], zi = sm.z[i], yi = sm.y[i];
-      const double zr = alpha * zt + (1.0 - alpha) * zi;
-      const double zn = fmin(fmax(zr + yi / rv, sm.ls[i]), sm.us[i]);
-      sm.y[i] = yi + rv * (zr - zn);
-      sm.z[i] = zn;
+    chol_solve_any(sm, n, lane);
+    for (int ib = 0; ib < m; ib += 32) {
+      const int i = ib + lane;
+      if (i < m) {
+        double zt = 0;
+        for (int a = sm.rowptr[i]; a < sm.rowptr[i + 1]; ++a) zt += sm.As[a] * sm.xt[sm.colidx[a]];
+        const double rv = sm.rv[i], zi = sm.z[i], yi = sm.y[i];
+        const double zr = alpha * zt + (1.0 - alpha) * zi;
+        const double zn = fmin(fmax(zr + yi / rv, sm.ls[i]), sm.us[i]);
+        sm.y[i] = yi + rv * (zr - zn);
+        sm.z[i] = zn;
+      }
     }
-    for (int j = lane; j < n; j += 32) sm.x[j] = alpha * sm.xt[j] + (1.0 - alpha) * sm.x[j];
+    for (int jb = 0; jb < n; jb += 32) {
+      const int j = jb + lane;
+      if (j < n) sm.x[j] = alpha * sm.xt[j] + (1.0 - alpha) * sm.x[j];
+    }
     __syncwarp();
     checked = d.s.check_termination && (iter % d.s.check_termination == 0);
     const bool adapt = d.s.adaptive_rho_interval && (iter % d.s.adaptive_rho_interval == 0);
@@ -309,7 +415,7 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
       est = fmin(fmax(est, GQ_RHO_MIN), GQ_RHO_MAX);
       if (est > rho * d.s.adaptive_rho_tol || est < rho / d.s.adaptive_rho_tol) {
         rho = est; ++rho_updates;
-        for (int i = lane; i < m; i += 32) sm.rv[i] = rho_of(gct[i], rho);
+        LANE_LOOP(i, m) sm.rv[i] = rho_of(gct[i], rho);
         __syncwarp();
         form_and_factor(d, sm, P, c, lane);
       }
@@ -327,11 +433,11 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   // ---- store_solution (auxil.c:527-562) + persistent state -----------------------------------------------------------
   const bool bad = status == GQ_ST_NON_CVX;
   const double cinv = 1.0 / c;
-  for (int j = lane; j < n; j += 32) {
+  LANE_LOOP(j, n) {
     d.x[(size_t)qp * n + j] = bad ? nan("") : sm.D[j] * sm.x[j];
     d.xs[(size_t)qp * n + j] = bad ? 0.0 : sm.x[j];
   }
-  for (int i = lane; i < m; i += 32) {
+  LANE_LOOP(i, m) {
     d.y[(size_t)qp * m + i] = bad ? nan("") : sm.E[i] * sm.y[i] * cinv;
     d.zs[(size_t)qp * m + i] = bad ? 0.0 : sm.z[i];
     d.ys[(size_t)qp * m + i] = bad ? 0.0 : sm.y[i];

