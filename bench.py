@@ -773,7 +773,7 @@ def main():
     if args.converged:
         kw.update(maxIter=4000, checkTermination=25, adaptiveRhoInterval=100)
         args.no_e2e = True
-    spl = 1 if args.converged else STEPS_PER_LAUNCH  # plant steps per launch
+    spl = 1 if args.converged else STEPS_PER_LAUNCH  # plant steps per launch (converged mode: one step per launch is its fastest shape, profiles/r02C_*)
     if args.hl_interval is not None:
         kw["hlInterval"] = args.hl_interval
         spl = int(np.floor(args.hl_interval / 0.2 + 1e-9)) + 1  # t - thlPrev > hlInterval on a 0.2 ms grid

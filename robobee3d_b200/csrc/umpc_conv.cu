@@ -392,7 +392,14 @@ int umpc_conv_launch_rollout(UmpcConv* c, const SimParams* sim, const DevState* 
     const int ntiles = s->B / 32;
     int grid = c->nsm < ntiles ? c->nsm : ntiles;
     if ((ntiles + grid - 1) / grid > UMPC_MAX_CHUNKED_TILES) grid = (ntiles + UMPC_MAX_CHUNKED_TILES - 1) / UMPC_MAX_CHUNKED_TILES;
-    umpc_rollout_kernel<CONV_TPB, SolverF64Tmem><<<grid, CONV_TPB, kConvSmem, stream>>>(kp, *s, *wlp, step0, nsteps, fire, tvals, lg, 1);
+    // Whole tiles per item by default.  Cutting a multi-step launch into (tile, chunk) items (UMPC_CONV_CHUNKS) was measured
+    // and is SLOWER here (25 steps per launch: 1 chunk 1.27 ms per step, 5 chunks 1.41, 25 chunks 1.41; one step per launch
+    // 1.185 -- profiles/r02C_conv_steps_per_launch.txt): launch boundaries keep the four warps of an SM in the same phase of
+    // the solve, and warps in different phases of this 690 KB kernel do not share the instruction cache.
+    int nch = 1;
+    if (const char* ev = getenv("UMPC_CONV_CHUNKS")) nch = atoi(ev);
+    if (nch < 1 || nch > nsteps) nch = 1;
+    umpc_rollout_kernel<CONV_TPB, SolverF64Tmem><<<grid, CONV_TPB, kConvSmem, stream>>>(kp, *s, *wlp, step0, nsteps, fire, tvals, lg, nch);
     return (int)cudaGetLastError();
   }
   const int grid = (s->B + c->tpb - 1) / c->tpb;
