@@ -224,7 +224,8 @@ int umpcBatchTimerStart(UmpcBatch *b);
 float umpcBatchTimerStopMs(UmpcBatch *b);
 /* Rollouts do not evaluate the per-solve residuals / status / un-scaled solution (GetSolve's info, x, y) by default:
  * nothing on the closed-loop path reads them (the reference never acts on them either, uprightmpc2.c:116-117; the
- * divergence guard of auxil.c:538-561 stays).  on = 1: evaluate them after every solve of a rollout, like Update does. */
+ * divergence guard of auxil.c:538-561 stays).  The same holds for umpcBatchEnvStep on pinned buffers (a step of a closed
+ * loop driven from the host).  on = 1: evaluate them after every solve of a rollout / env-step, like Update does. */
 int umpcBatchSetRolloutInfo(UmpcBatch *b, int on);
 /* launch configuration knobs (threads per block) for tuning/benchmarks */
 int umpcBatchSetLaunch(UmpcBatch *b, int threads_per_block);

@@ -623,7 +623,7 @@ static int batch_create_body(UmpcBatch* b, int nenv, const UmpcBatchParams* par)
     CK(cudaFuncSetAttribute(K<T, SolverF32<T, DefStore<T>, ##__VA_ARGS__>>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DefStore<T>::kSmemBytes));
   UMPC_SET_HYB(umpc_update_kernel, 128) UMPC_SET_HYB(umpc_update_kernel, 256) UMPC_SET_HYB(umpc_update_kernel, 128, true)
   UMPC_SET_HYB(umpc_rollout_kernel, 128) UMPC_SET_HYB(umpc_rollout_kernel, 256) UMPC_SET_HYB(umpc_rollout_kernel, 128, true)
-  UMPC_SET_HYB(umpc_hostio_kernel, 128)
+  UMPC_SET_HYB(umpc_hostio_kernel, 128) UMPC_SET_HYB(umpc_hostio_kernel, 128, false, false)
   {
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, b->device));
@@ -816,7 +816,12 @@ static int run_chunked(UmpcBatch* b, HostArr* in, int nin, HostArr* out, int nou
       io.pulled = b->d_pulled;
       CK(cudaMemsetAsync(b->d_pulled, 0, sizeof(unsigned), b->stream));
       CK(cudaEventRecord(b->ev0, b->stream));
-      umpc_hostio_kernel<128, SolverF32<128, DefStore<128>>><<<b->Bp / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
+      // an env-step (5 outputs: the plant moves on) is a step of a closed loop: like a rollout it skips the per-solve
+      // residual / status / solution block unless umpcBatchSetRolloutInfo(b, 1) asked for it; an update (2 outputs) keeps it
+      if (nout == 5 && !b->rollout_info)
+        umpc_hostio_kernel<128, SolverF32<128, DefStore<128>, false, false>><<<b->Bp / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
+      else
+        umpc_hostio_kernel<128, SolverF32<128, DefStore<128>>><<<b->Bp / 128, 128, DefStore<128>::kSmemBytes, b->stream>>>(b->kp, b->s, io, b->have_qpdata ? 1 : 0);
       CK(cudaGetLastError());
       CK(cudaEventRecord(b->ev1, b->stream));
       b->timed = true;

@@ -310,3 +310,31 @@ def test_c_program_links_and_runs(cuda_required, tmp_path, gold):
         uq, acc = up.update([1.0, -2.0, 3.0], np.eye(3), [0.1, 0, 0, 0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 1.0], 9.81e-3 if k == 0 else -1.0)
         got = np.array([float(v) for v in l[5:8]])
         assert np.array_equal(got.astype(np.float32), uq.astype(np.float32)), (k, got, uq)
+
+
+def test_env_step_on_pinned_buffers_follows_the_rollout_info_switch(cuda_required):
+    """umpcBatchEnvStep on pinned host buffers (one zero-copy kernel) is a closed-loop step: like a rollout it does not
+    evaluate the per-solve residuals / status unless umpcBatchSetRolloutInfo(b, 1) asks for them -- outputs are the same
+    bits either way, and equal to the pageable path's"""
+    import torch
+    from robobee3d_b200.batch import BatchUMPC
+    B = 1000
+    p, R, dq = util.config2_states(B, seed=11)
+    Rc = np.ascontiguousarray(R.transpose(0, 2, 1).reshape(B, 9), np.float32)
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    pin = lambda a: torch.from_numpy(np.array(a, np.float32, copy=True)).pin_memory()
+    z3, e3 = f(np.zeros((B, 3))), f(np.tile([0, 0, 1.0], (B, 1)))
+    outs = []
+    for info_on in (0, 1):
+        b = BatchUMPC(B)
+        b.set_rollout_info(info_on)
+        sp, sR, sdq = pin(p), pin(Rc), pin(dq)
+        uq, acc = pin(np.zeros((B, 3))), pin(np.zeros((B, 6)))
+        for _ in range(3):
+            b.env_step_raw(uq, acc, sp, sR, sdq, pin(z3), pin(z3), pin(e3))
+        st = b.solve_info()["status"]
+        assert (st == (1 if info_on else 0)).all() or (info_on and np.isin(st, (1, 2, -2)).all()), (info_on, np.unique(st))
+        outs.append((uq.numpy().copy(), acc.numpy().copy(), sp.numpy().copy(), sR.numpy().copy(), sdq.numpy().copy()))
+        b.close()
+    for a, c in zip(*outs):
+        assert np.array_equal(a, c)
