@@ -189,6 +189,20 @@ __global__ void __launch_bounds__(128) sweep_kernel(const __grid_constant__ FwPa
     }                                                                                     \
   } while (0)
 
+// device buffer / event that frees itself: the entry points below return early on any CUDA error
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes); }
+  template <class T> T* as() const { return (T*)p; }
+};
+struct EvPair {
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  ~EvPair() { if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); }
+};
+}  // namespace
+
 static int fw_need_device(const char* who) {
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -225,13 +239,13 @@ extern "C" int fwAerodynamics(const FwParams* p, int n, const double* theta, con
     return UMPC_ERR_ARG;
   }
   if (int rc = fw_need_device("fwAerodynamics")) return rc;
-  double *dth, *ddth, *dF, *dP;
-  FCK(cudaMalloc(&dth, (size_t)n * 16)); FCK(cudaMalloc(&ddth, (size_t)n * 16)); FCK(cudaMalloc(&dF, (size_t)n * 24)); FCK(cudaMalloc(&dP, (size_t)n * 24));
+  DevBuf bth, bdth, bF, bP;
+  FCK(bth.alloc((size_t)n * 16)); FCK(bdth.alloc((size_t)n * 16)); FCK(bF.alloc((size_t)n * 24)); FCK(bP.alloc((size_t)n * 24));
+  double *dth = bth.as<double>(), *ddth = bdth.as<double>(), *dF = bF.as<double>(), *dP = bP.as<double>();
   FCK(cudaMemcpy(dth, theta, (size_t)n * 16, cudaMemcpyHostToDevice)); FCK(cudaMemcpy(ddth, dtheta, (size_t)n * 16, cudaMemcpyHostToDevice));
   fw::aero_kernel<<<(n + 127) / 128, 128>>>(*p, n, dth, ddth, lrSign, dF, dP);
   FCK(cudaGetLastError());
   FCK(cudaMemcpy(F, dF, (size_t)n * 24, cudaMemcpyDeviceToHost)); FCK(cudaMemcpy(pcop, dP, (size_t)n * 24, cudaMemcpyDeviceToHost));
-  cudaFree(dth); cudaFree(ddth); cudaFree(dF); cudaFree(dP);
   return UMPC_OK;
 }
 
@@ -249,20 +263,19 @@ extern "C" int fwOpenLoopSweep(const FwParams* p, int nsim, const double* drive,
   }
   if (qw && (log_sim < 0 || log_sim >= nsim)) { umpc_internal_set_error("fwOpenLoopSweep: log_sim out of range"); return UMPC_ERR_ARG; }
   if (int rc = fw_need_device("fwOpenLoopSweep")) return rc;
-  double *dd = nullptr, *df = nullptr, *dq = nullptr;
-  FCK(cudaMalloc(&dd, (size_t)nsim * 5 * 8)); FCK(cudaMalloc(&df, (size_t)nsim * 15 * 8));
-  if (qw) FCK(cudaMalloc(&dq, (size_t)nsteps * 14 * 8));
+  DevBuf bd, bf, bq;
+  FCK(bd.alloc((size_t)nsim * 5 * 8)); FCK(bf.alloc((size_t)nsim * 15 * 8));
+  if (qw) FCK(bq.alloc((size_t)nsteps * 14 * 8));
+  double *dd = bd.as<double>(), *df = bf.as<double>(), *dq = bq.as<double>();
   FCK(cudaMemcpy(dd, drive, (size_t)nsim * 5 * 8, cudaMemcpyHostToDevice));
-  cudaEvent_t e0, e1;
-  FCK(cudaEventCreate(&e0)); FCK(cudaEventCreate(&e1));
-  FCK(cudaEventRecord(e0));
+  EvPair ev;
+  FCK(cudaEventCreate(&ev.e0)); FCK(cudaEventCreate(&ev.e1));
+  FCK(cudaEventRecord(ev.e0));
   fw::sweep_kernel<<<(2 * nsim + 127) / 128, 128>>>(*p, nsim, dd, nsteps, timestep, df, qw ? log_sim : -1, dq);
-  FCK(cudaEventRecord(e1));
+  FCK(cudaEventRecord(ev.e1));
   FCK(cudaGetLastError());
   FCK(cudaMemcpy(feat, df, (size_t)nsim * 15 * 8, cudaMemcpyDeviceToHost));
   if (qw) FCK(cudaMemcpy(qw, dq, (size_t)nsteps * 14 * 8, cudaMemcpyDeviceToHost));
-  if (kernel_ms) FCK(cudaEventElapsedTime(kernel_ms, e0, e1));
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
-  cudaFree(dd); cudaFree(df); cudaFree(dq);
+  if (kernel_ms) FCK(cudaEventElapsedTime(kernel_ms, ev.e0, ev.e1));
   return UMPC_OK;
 }

@@ -710,10 +710,14 @@ extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off,
   }
   GCK(cudaSetDevice(b->device));
   const size_t B = b->nqp;
-  double *dAd, *dBd, *dx0, *dul = nullptr, *dit = nullptr;
-  GCK(cudaMalloc(&dAd, (size_t)nx * nx * 8)); GCK(cudaMalloc(&dBd, (size_t)nx * nu * 8)); GCK(cudaMalloc(&dx0, B * nx * 8));
-  GCK(cudaMalloc(&dit, 8));
-  if (u_log) GCK(cudaMalloc(&dul, (size_t)nsteps * B * nu * 8));
+  struct Tmp {   // freed on every return path
+    double* p = nullptr;
+    ~Tmp() { if (p) cudaFree(p); }
+  } tAd, tBd, tx0, tul, tit;
+  GCK(cudaMalloc(&tAd.p, (size_t)nx * nx * 8)); GCK(cudaMalloc(&tBd.p, (size_t)nx * nu * 8)); GCK(cudaMalloc(&tx0.p, B * nx * 8));
+  GCK(cudaMalloc(&tit.p, 8));
+  if (u_log) GCK(cudaMalloc(&tul.p, (size_t)nsteps * B * nu * 8));
+  double *dAd = tAd.p, *dBd = tBd.p, *dx0 = tx0.p, *dul = tul.p, *dit = tit.p;
   GCK(cudaMemcpyAsync(dAd, Ad, (size_t)nx * nx * 8, cudaMemcpyHostToDevice, b->stream));
   GCK(cudaMemcpyAsync(dBd, Bd, (size_t)nx * nu * 8, cudaMemcpyHostToDevice, b->stream));
   GCK(cudaMemcpyAsync(dx0, x0, B * nx * 8, cudaMemcpyHostToDevice, b->stream));
@@ -734,8 +738,7 @@ extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off,
     if (u_log) cudaMemcpyAsync(u_log, dul, (size_t)nsteps * B * nu * 8, cudaMemcpyDeviceToHost, b->stream);
     if (iters_sum) cudaMemcpyAsync(iters_sum, dit, 8, cudaMemcpyDeviceToHost, b->stream);
   }
-  cudaStreamSynchronize(b->stream);
-  cudaFree(dAd); cudaFree(dBd); cudaFree(dx0); cudaFree(dit); cudaFree(dul);
+  if (cudaStreamSynchronize(b->stream) != cudaSuccess && !rc) rc = UMPC_ERR_CUDA;
   if (cudaGetLastError() != cudaSuccess && !rc) rc = UMPC_ERR_CUDA;
   return rc;
 }

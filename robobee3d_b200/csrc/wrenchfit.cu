@@ -276,6 +276,20 @@ __global__ void __launch_bounds__(128) fit_noalloc_kernel(int F, int M, const do
     }                                                                                     \
   } while (0)
 
+// device buffer / event that frees itself: the entry points below return early on any CUDA error
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes); }
+  template <class T> T* as() const { return (T*)p; }
+};
+struct EvPair {
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  ~EvPair() { if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); }
+};
+}  // namespace
+
 static int need_device(const char* who) {
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -290,14 +304,14 @@ extern "C" int wfitWrenchFromKinematics(int M, const double* kins, const double*
   if (M <= 0 || !kins || !freq || !par || !ws) { umpc_internal_set_error("wfitWrenchFromKinematics: bad argument"); return UMPC_ERR_ARG; }
   int rc = need_device("wfitWrenchFromKinematics");
   if (rc) return rc;
-  double *dk, *df, *dp, *dw;
-  WCK(cudaMalloc(&dk, (size_t)M * 9 * 8)); WCK(cudaMalloc(&df, (size_t)M * 8)); WCK(cudaMalloc(&dp, 17 * 8)); WCK(cudaMalloc(&dw, (size_t)M * 6 * 8));
+  DevBuf bk, bf, bp, bw;
+  WCK(bk.alloc((size_t)M * 9 * 8)); WCK(bf.alloc((size_t)M * 8)); WCK(bp.alloc(17 * 8)); WCK(bw.alloc((size_t)M * 6 * 8));
+  double *dk = bk.as<double>(), *df = bf.as<double>(), *dp = bp.as<double>(), *dw = bw.as<double>();
   WCK(cudaMemcpy(dk, kins, (size_t)M * 9 * 8, cudaMemcpyHostToDevice)); WCK(cudaMemcpy(df, freq, (size_t)M * 8, cudaMemcpyHostToDevice));
   WCK(cudaMemcpy(dp, par, 17 * 8, cudaMemcpyHostToDevice));
   wfit::wrench_kernel<<<(M + 127) / 128, 128>>>(M, dk, df, dp, dw);
   WCK(cudaGetLastError());
   WCK(cudaMemcpy(ws, dw, (size_t)M * 6 * 8, cudaMemcpyDeviceToHost));
-  cudaFree(dk); cudaFree(df); cudaFree(dp); cudaFree(dw);
   return UMPC_OK;
 }
 
@@ -308,24 +322,22 @@ extern "C" int wfitFit(int F, int M, const double* xdata, const double* ws, doub
   const size_t smem = ((size_t)M * wfit::NP + wfit::NP * wfit::NP + 8 + wfit::NP + wfit::NP * 6) * sizeof(double);
   if (smem > 200 * 1024) { umpc_internal_set_error("wfitFit: more than ~1,600 trials per dataset do not fit one CTA's shared memory"); return UMPC_ERR_ARG; }
   if (smem > 48 * 1024) WCK(cudaFuncSetAttribute(wfit::fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  double *dx, *dw, *dp, *dfit = nullptr;
-  int* dr = nullptr;
-  WCK(cudaMalloc(&dx, (size_t)F * M * 4 * 8)); WCK(cudaMalloc(&dw, (size_t)F * M * 6 * 8)); WCK(cudaMalloc(&dp, (size_t)F * 90 * 8));
-  WCK(cudaMalloc(&dr, (size_t)F * 4));
-  if (fit) WCK(cudaMalloc(&dfit, (size_t)F * M * 6 * 8));
+  DevBuf bx, bw, bp, br, bfit;
+  WCK(bx.alloc((size_t)F * M * 4 * 8)); WCK(bw.alloc((size_t)F * M * 6 * 8)); WCK(bp.alloc((size_t)F * 90 * 8)); WCK(br.alloc((size_t)F * 4));
+  if (fit) WCK(bfit.alloc((size_t)F * M * 6 * 8));
+  double *dx = bx.as<double>(), *dw = bw.as<double>(), *dp = bp.as<double>(), *dfit = bfit.as<double>();
+  int* dr = br.as<int>();
   WCK(cudaMemcpy(dx, xdata, (size_t)F * M * 4 * 8, cudaMemcpyHostToDevice)); WCK(cudaMemcpy(dw, ws, (size_t)F * M * 6 * 8, cudaMemcpyHostToDevice));
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0); cudaEventCreate(&e1);
-  cudaEventRecord(e0);
+  EvPair ev;
+  WCK(cudaEventCreate(&ev.e0)); WCK(cudaEventCreate(&ev.e1));
+  WCK(cudaEventRecord(ev.e0));
   wfit::fit_kernel<<<F, 128, smem>>>(M, dx, dw, dp, dfit, 1e-10, dr);
-  cudaEventRecord(e1);
+  WCK(cudaEventRecord(ev.e1));
   WCK(cudaGetLastError());
   WCK(cudaMemcpy(popts, dp, (size_t)F * 90 * 8, cudaMemcpyDeviceToHost));
   if (fit) WCK(cudaMemcpy(fit, dfit, (size_t)F * M * 6 * 8, cudaMemcpyDeviceToHost));
   if (rank) WCK(cudaMemcpy(rank, dr, (size_t)F * 4, cudaMemcpyDeviceToHost));
-  if (kernel_ms) cudaEventElapsedTime(kernel_ms, e0, e1);
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
-  cudaFree(dx); cudaFree(dw); cudaFree(dp); cudaFree(dfit); cudaFree(dr);
+  if (kernel_ms) WCK(cudaEventElapsedTime(kernel_ms, ev.e0, ev.e1));
   return UMPC_OK;
 }
 
