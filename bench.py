@@ -845,10 +845,10 @@ def main():
         # `spl` closed-loop steps on the device, final states + logMetric sums out (reported beside, not instead of, the above)
         if args.hl_interval is None and not args.tpb:
             from robobee3d_b200.batch import _vp
-            gp, gR, gdq, guq = (np.empty((nenv, 3), np.float32), np.empty((nenv, 9), np.float32), np.empty((nenv, 6), np.float32),
-                                np.empty((nenv, 3), np.float32))
-            gm = np.empty((nenv, 4), np.float32)
-            sp, sR, sdq = hp.numpy().copy(), hR.numpy().copy(), hdq.numpy().copy()
+            pz = lambda k: torch.zeros((nenv, k), dtype=torch.float32).pin_memory().numpy()   # pinned host arrays
+            gp, gR, gdq, guq, gm = pz(3), pz(9), pz(6), pz(3), pz(4)
+            sp, sR, sdq = pz(3), pz(9), pz(6)
+            sp[:], sR[:], sdq[:] = hp.numpy(), hR.numpy(), hdq.numpy()
 
             def flight():
                 L = b2.lib
@@ -869,7 +869,7 @@ def main():
             assert np.isfinite(gp).all()
             e2e["flight_call"] = {"value": nenv * world * args.steps * spl / float(tf[0]), "unit": UNIT, "ms_per_step": 1e3 * float(tf[0]) / args.steps,
                                   "h2d_bytes_per_step": 18 * 4 * nenv, "d2h_bytes_per_step": (21 + 4) * 4 * nenv,
-                                  "call": "umpcBatchSetState (host ICs) + umpcBatchRollout(%d) + umpcBatchGetState + umpcBatchGetMetrics (pageable host "
+                                  "call": "umpcBatchSetState (host ICs) + umpcBatchRollout(%d) + umpcBatchGetState + umpcBatchGetMetrics (pinned host "
                                           "arrays): the controlTest-shaped call, plant on the device" % spl}
         b2.close()
 
