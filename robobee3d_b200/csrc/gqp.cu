@@ -31,6 +31,12 @@ void umpc_internal_set_error(const char* msg);  // umpc_kernels.cu
 
 namespace gqp {
 
+// 1 (default): the factor is inverted once per factorisation and every ADMM iteration solves with two triangular
+// matrix-vector products; 0: two substitution sweeps with the pivot travelling by shuffle (A/B: build with -DGQP_EXPLICIT_INVERSE=0)
+#ifndef GQP_EXPLICIT_INVERSE
+#define GQP_EXPLICIT_INVERSE 1
+#endif
+
 // OSQP constants (constants.h:69-100)
 #define GQ_RHO_MIN 1e-6
 #define GQ_RHO_MAX 1e6
@@ -147,6 +153,31 @@ __device__ void form_and_factor(const Dev& d, const Smem& sm, const double* __re
     }
     __syncwarp();
   }
+#if GQP_EXPLICIT_INVERSE
+  // L <- L^-1 in place, row by row: Linv[i][j] = -(1 / L[i][i]) sum_{k = j}^{i-1} L[i][k] Linv[k][j].  Row i needs its own
+  // original entries (parked in sm.tmp) and the rows above it, which are already inverted; the entries of a row are
+  // independent, one lane each.  The ADMM loop then solves with two triangular MATRIX-VECTOR products (gqp_inv_solve)
+  // instead of two substitution sweeps: the same n^2 multiply-adds without the chain of n dependent pivot steps.
+  if (n <= 128) {
+    for (int i = 0; i < n; ++i) {
+      const double* rowc = sm.L + tri(i, 0);
+      LANE_LOOP(k, i) sm.tmp[k] = rowc[k];
+      __syncwarp();
+      const double di = sm.invd[i];
+      for (int jb = 0; jb < i; jb += 32) {
+        const int j = jb + lane;
+        if (j < i) {
+          double acc = 0.0;
+          int a = tri(j, j);                                  // Linv[k][j], k = j .. i-1: tri(k, j) = tri(k-1, j) + k
+          for (int k = j; k < i; ++k) { acc += sm.tmp[k] * sm.L[a]; a += k + 1; }
+          sm.L[tri(i, j)] = -di * acc;
+        }
+      }
+      if (lane == 0) sm.L[tri(i, i)] = di;
+      __syncwarp();
+    }
+  }
+#endif
 }
 
 // sm.xt <- K^-1 sm.xt
@@ -218,8 +249,49 @@ __device__ __forceinline__ void chol_solve_reg(const Smem& sm, int n, int lane) 
   }
   __syncwarp();
 }
+// sm.xt <- K^-1 sm.xt with sm.L = L^-1 (packed lower): y = Linv b (lane i: row i), x = Linv' y (lane j: column j, conflict-free)
+template <int NR>
+__device__ __forceinline__ void gqp_inv_solve(const Smem& sm, int n, int lane) {
+  double acc[NR];
+  int base[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) { const int i = lane + 32 * r; acc[r] = 0.0; base[r] = (i * (i + 1)) / 2; }
+  for (int j = 0; j < n; ++j) {
+    const double bj = sm.xt[j];                             // broadcast
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const int i = lane + 32 * r;
+      if (j <= i && i < n) acc[r] += sm.L[base[r] + j] * bj;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) { const int i = lane + 32 * r; if (i < n) sm.wv[i] = acc[r]; acc[r] = 0.0; }
+  __syncwarp();
+  int rowbase = 0;                                          // tri(i, 0)
+  for (int i = 0; i < n; ++i) {
+    const double yi = sm.wv[i];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const int j = lane + 32 * r;
+      if (j <= i) acc[r] += sm.L[rowbase + j] * yi;
+    }
+    rowbase += i + 1;
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) { const int j = lane + 32 * r; if (j < n) sm.xt[j] = acc[r]; }
+  __syncwarp();
+}
 __device__ __forceinline__ void chol_solve_any(const Smem& sm, int n, int lane) {
   __syncwarp();
+#if GQP_EXPLICIT_INVERSE
+  switch ((n + 31) >> 5) {
+    case 1: gqp_inv_solve<1>(sm, n, lane); return;
+    case 2: gqp_inv_solve<2>(sm, n, lane); return;
+    case 3: gqp_inv_solve<3>(sm, n, lane); return;
+    case 4: gqp_inv_solve<4>(sm, n, lane); return;
+    default: break;
+  }
+#endif
   switch ((n + 31) >> 5) {
     case 1: chol_solve_reg<1>(sm, n, lane); break;
     case 2: chol_solve_reg<2>(sm, n, lane); break;
