@@ -59,7 +59,8 @@ void *gqpBatchDevPtr(GqpBatch *b, const char *name);
 
 /* ---- LTI model-predictive loop on top (planar/mpc_osqp.py:117-140) --------------------------------------------
  * x0 <- Ad x0 + Bd u0*, l[:nx] = u[:nx] = -x0, solve again: nsteps closed-loop steps of every QP of the batch on the
- * device.  Ad[nx*nx], Bd[nx*nu] row-major; x0[nqp][nx] in/out; the first-input block of x sits at u_off. */
+ * device.  Ad[nx*nx], Bd[nx*nu] row-major; x0[nqp][nx] in/out; the first-input block of x sits at u_off.  From its first call on
+ * the batch keeps every QP's factor between solves (n (n + 1) / 2 + n doubles per QP) and reuses it while only bounds change. */
 int gqpLtiRollout(GqpBatch *b, int nsteps, int nx, int nu, int u_off, const double *Ad, const double *Bd, double *x0,
                   double *u_log /* [nsteps][nqp][nu] or NULL */, double *iters_sum /* or NULL */,
                   int rescale_first /* 1: the first solve equilibrates (prob.setup + first solve) */);

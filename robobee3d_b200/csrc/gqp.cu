@@ -62,6 +62,9 @@ struct Dev {
   int* ctype;
   // results
   double *x, *y, *info;
+  // factor kept between solves (LTI loop: only the bounds change): [nqp][n (n + 1) / 2 + n] and a validity flag per QP; NULL = off
+  double* Lc;
+  int* lvalid;
 };
 
 __device__ __forceinline__ double warp_max(double v) {
@@ -366,6 +369,7 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   double c = d.c[qp], rho = d.rho[qp];
   const double INF = d.s.infty;
   // ---- osqp_update_bounds with the OLD scaling: constraint types (auxil.c:103-146) ---------------------------------
+  int types_changed = 0;
   LANE_LOOP(i, m) {
     const double eo = gE[i];
     const double lo = fmax(l0[i], -INF), hi = fmin(u0[i], INF);
@@ -374,9 +378,11 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
     if (ls < -INF * GQ_MIN_SCALING && us > INF * GQ_MIN_SCALING) type = -1;
     else if (us - ls < GQ_RHO_TOL) type = 1;
     else type = 0;
+    types_changed |= gct[i] != type;
     gct[i] = type;
     sm.E[i] = eo;
   }
+  types_changed = __any_sync(0xffffffffu, types_changed);
   LANE_LOOP(j, n) sm.D[j] = gD[j];
   __syncwarp();
   // ---- osqp_update_P_A: re-equilibrate (scale_data, scaling.c:44-156) ------------------------------------------------
@@ -435,7 +441,21 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
   }
   LANE_LOOP(j, n) { sm.qs[j] = c * sm.D[j] * q0[j]; sm.x[j] = d.xs[(size_t)qp * n + j]; }
   __syncwarp();
-  form_and_factor(d, sm, P, c, lane);
+  // The factor depends on P, A, the scaling, rho and the constraint types only: when the caller says that just q / l / u
+  // changed (rescale = 0: prob.update(l=, u=), the LTI loop of mpc_osqp.py:137-140) and neither a type nor rho moved, the
+  // factor of the previous solve is loaded back instead of being formed, factorised and inverted again (OSQP itself only
+  // refactors on update_P_A / update_rho).
+  const int ntri = (n * (n + 1)) / 2;
+  double* Lq = d.Lc ? d.Lc + (size_t)qp * (ntri + n) : nullptr;
+  bool factor_dirty = true;
+  if (Lq && !rescale && !types_changed && d.lvalid[qp]) {
+    LANE_LOOP(k, ntri) sm.L[k] = Lq[k];
+    LANE_LOOP(k, n) sm.invd[k] = Lq[ntri + k];
+    __syncwarp();
+    factor_dirty = false;
+  } else {
+    form_and_factor(d, sm, P, c, lane);
+  }
   // ---- ADMM (osqp.c:352-500) -----------------------------------------------------------------------------------------
   const double alpha = d.s.alpha, sigma = d.s.sigma;
   int iter = 0, status = GQ_ST_UNSOLVED, rho_updates = 0;
@@ -490,6 +510,7 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
         LANE_LOOP(i, m) sm.rv[i] = rho_of(gct[i], rho);
         __syncwarp();
         form_and_factor(d, sm, P, c, lane);
+        factor_dirty = true;
       }
     }
   }
@@ -513,6 +534,11 @@ __global__ void __launch_bounds__(32) gqp_solve_kernel(const __grid_constant__ D
     d.y[(size_t)qp * m + i] = bad ? nan("") : sm.E[i] * sm.y[i] * cinv;
     d.zs[(size_t)qp * m + i] = bad ? 0.0 : sm.z[i];
     d.ys[(size_t)qp * m + i] = bad ? 0.0 : sm.y[i];
+  }
+  if (Lq && factor_dirty) {
+    LANE_LOOP(k, ntri) Lq[k] = sm.L[k];
+    LANE_LOOP(k, n) Lq[ntri + k] = sm.invd[k];
+    if (lane == 0) d.lvalid[qp] = 1;
   }
   if (lane == 0) {
     d.c[qp] = c; d.rho[qp] = rho;
@@ -616,6 +642,7 @@ extern "C" int gqpBatchReset(GqpBatch* b) {
   GCK(cudaMemsetAsync(d.zs, 0, B * d.s.m * 8, b->stream));
   GCK(cudaMemsetAsync(d.ys, 0, B * d.s.m * 8, b->stream));
   GCK(cudaMemsetAsync(d.ctype, 0, B * d.s.m * 4, b->stream));
+  if (d.lvalid) GCK(cudaMemsetAsync(d.lvalid, 0, B * 4, b->stream));
   int rc;
   if ((rc = gqp_fill(b, d.D, B * d.s.n, 1.0))) return rc;
   if ((rc = gqp_fill(b, d.E, B * d.s.m, 1.0))) return rc;
@@ -709,6 +736,7 @@ extern "C" int gqpBatchSetData(GqpBatch* b, const double* P, const double* Av, c
   const Dev& d = b->d;
   struct { const double* h; double* dv; size_t per; } arr[5] = {{P, d.P, (size_t)d.s.n * d.s.n}, {Av, d.Av, (size_t)d.s.nnz},
                                                                  {q, d.q, (size_t)d.s.n}, {l, d.l, (size_t)d.s.m}, {u, d.u, (size_t)d.s.m}};
+  if ((P || Av) && d.lvalid) GCK(cudaMemsetAsync(d.lvalid, 0, (size_t)b->nqp * 4, b->stream));   // kept factors are stale
   for (auto& a : arr) {
     if (!a.h) continue;
     GCK(cudaMemcpyAsync(a.dv, a.h, a.per * (broadcast ? 1 : (size_t)b->nqp) * 8, cudaMemcpyHostToDevice, b->stream));
@@ -782,6 +810,11 @@ extern "C" int gqpLtiRollout(GqpBatch* b, int nsteps, int nx, int nu, int u_off,
   }
   GCK(cudaSetDevice(b->device));
   const size_t B = b->nqp;
+  if (!b->d.Lc) {   // closed loop = many solves of the same P, A: keep every QP's factor between them
+    const size_t per = (size_t)b->d.s.n * (b->d.s.n + 1) / 2 + b->d.s.n;
+    int rc0;
+    if ((rc0 = galloc(b, &b->d.lvalid, B)) || (rc0 = galloc(b, &b->d.Lc, B * per))) { b->d.Lc = nullptr; return rc0; }
+  }
   struct Tmp {   // freed on every return path
     double* p = nullptr;
     ~Tmp() { if (p) cudaFree(p); }
